@@ -1,0 +1,124 @@
+/* xgpr_b200.h -- C ABI of the B200-native replacement for xGPR's CUDA random-feature extension.
+ *
+ * Drop-in boundary: every entry point below replaces one callable of the
+ * reference's nanobind module `xgpr_cuda_rfgen_cpp_ext`
+ * (/root/reference/src/xGPR/random_feature_generation/gpu_rf_gen/xgpr_cuda_rfgen_cpp_ext.cpp:20-93),
+ * one symbol per dtype overload (`_f32` = float FHT, `_f64` = double FHT).  Argument meaning,
+ * validation and error behaviour follow the reference wrappers cited per function; numerics follow
+ * the reference's CPU extension (the oracle), see DESIGN.md.
+ *
+ * Conventions
+ *   - All array arguments are DEVICE pointers to C-contiguous arrays owned by the caller, except
+ *     `seqlengths`, which is a HOST int32 array exactly as in the reference
+ *     (gpu_rf_gen/convolution_ops/convolution.cu:145, rbf_convolution.cu:314).
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  Calls are
+ *     asynchronous with respect to the host; nothing is allocated or freed per call.
+ *   - Return value: 0 on success; XGPR_B200_EINVAL for the shape/size violations the reference
+ *     reports as std::runtime_error; XGPR_B200_ECUDA for a CUDA launch/runtime error.
+ *     xgpr_b200_last_error() returns the message (thread-local, valid until the next call).
+ *   - No torch / DLPack / Python types cross this boundary.
+ */
+#ifndef XGPR_B200_H
+#define XGPR_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define XGPR_B200_OK      0
+#define XGPR_B200_EINVAL -1
+#define XGPR_B200_ECUDA  -2
+
+/* library info */
+int         xgpr_b200_abi_version(void);
+const char* xgpr_b200_last_error(void);
+/* number of kernel launches issued by this library in this process (bench.py's gpu_launches) */
+int64_t     xgpr_b200_launch_count(void);
+
+/* ---- cudaFastHadamardTransform2D  (xgpr_cuda_rfgen_cpp_ext.cpp:21-24;
+ *      gpu_rf_gen/basic_ops/basic_array_operations.cu:187-216)
+ * In-place unnormalised FWHT of every row of x (n, p); p a power of two >= 2. */
+int xgpr_b200_fht2d_f32(float*  x, int64_t n, int64_t p, void* stream);
+int xgpr_b200_fht2d_f64(double* x, int64_t n, int64_t p, void* stream);
+
+/* ---- cudaSRHT  (xgpr_cuda_rfgen_cpp_ext.cpp:25-30; basic_array_operations.cu:226-265)
+ * x <- FWHT(x * radem * p^-1/2) row-wise; radem (p) int8 in {-1,+1}. */
+int xgpr_b200_srht_f32(float*  x, int64_t n, int64_t p, const int8_t* radem, int64_t radem_len, void* stream);
+int xgpr_b200_srht_f64(double* x, int64_t n, int64_t p, const int8_t* radem, int64_t radem_len, void* stream);
+
+/* ---- cudaRBFFeatureGen  (xgpr_cuda_rfgen_cpp_ext.cpp:32-39; gpu_rf_gen/rbf_ops/rbf_ops.cu:261-326)
+ * x (n, d); out (n, num_rffs) f64, OVERWRITTEN with interleaved [cos, sin] pairs;
+ * radem (3, 1, radem_len) int8; chi (num_freqs); num_rffs == 2 * num_freqs. */
+int xgpr_b200_rbf_feature_gen_f32(const float*  x, int64_t n, int64_t d, double* out, int64_t num_rffs,
+                                  const int8_t* radem, int64_t radem_len, const float*  chi,
+                                  int64_t num_freqs, int fit_intercept, void* stream);
+int xgpr_b200_rbf_feature_gen_f64(const double* x, int64_t n, int64_t d, double* out, int64_t num_rffs,
+                                  const int8_t* radem, int64_t radem_len, const double* chi,
+                                  int64_t num_freqs, int fit_intercept, void* stream);
+
+/* ---- cudaRBFGrad  (xgpr_cuda_rfgen_cpp_ext.cpp:41-48; rbf_ops.cu:342-413)
+ * As above on the raw (not sigma-scaled) input; grad (n, num_rffs, 1) f64 = dZ/dsigma. */
+int xgpr_b200_rbf_grad_f32(const float*  x, int64_t n, int64_t d, double* out, double* grad, int64_t num_rffs,
+                           const int8_t* radem, int64_t radem_len, const float*  chi, int64_t num_freqs,
+                           double sigma, int fit_intercept, void* stream);
+int xgpr_b200_rbf_grad_f64(const double* x, int64_t n, int64_t d, double* out, double* grad, int64_t num_rffs,
+                           const int8_t* radem, int64_t radem_len, const double* chi, int64_t num_freqs,
+                           double sigma, int fit_intercept, void* stream);
+
+/* ---- cudaMiniARDGrad  (xgpr_cuda_rfgen_cpp_ext.cpp:50-59; gpu_rf_gen/rbf_ops/ard_ops.cu:87-148)
+ * x (n, d); out (n, 2*num_freqs) f64; w (num_freqs, d) precomputed weights; sigma_map (d) i32;
+ * sigma_vals (d) f64; grad (n, 2*num_freqs, num_lengthscales) f64.  All device pointers. */
+int xgpr_b200_ard_grad_f32(const float*  x, int64_t n, int64_t d, double* out, const float*  w,
+                           int64_t num_freqs, const int32_t* sigma_map, const double* sigma_vals,
+                           double* grad, int64_t num_lengthscales, int fit_intercept, void* stream);
+int xgpr_b200_ard_grad_f64(const double* x, int64_t n, int64_t d, double* out, const double* w,
+                           int64_t num_freqs, const int32_t* sigma_map, const double* sigma_vals,
+                           double* grad, int64_t num_lengthscales, int fit_intercept, void* stream);
+
+/* ---- cudaConv1dMaxpool  (xgpr_cuda_rfgen_cpp_ext.cpp:61-68; gpu_rf_gen/convolution_ops/convolution.cu:140-241)
+ * x (n, m, c); out (n, num_freqs) f32, out = max(out, .) (caller zero-fills => ReLU);
+ * seqlengths: HOST int32 (n). */
+int xgpr_b200_conv1d_maxpool_f32(const float*  x, int64_t n, int64_t m, int64_t c, float* out, int64_t num_rffs,
+                                 const int8_t* radem, int64_t radem_len, const float*  chi, int64_t num_freqs,
+                                 const int32_t* seqlengths_host, int conv_width, void* stream);
+int xgpr_b200_conv1d_maxpool_f64(const double* x, int64_t n, int64_t m, int64_t c, float* out, int64_t num_rffs,
+                                 const int8_t* radem, int64_t radem_len, const double* chi, int64_t num_freqs,
+                                 const int32_t* seqlengths_host, int conv_width, void* stream);
+
+/* ---- cudaConv1dFGen  (xgpr_cuda_rfgen_cpp_ext.cpp:70-79; gpu_rf_gen/convolution_ops/rbf_convolution.cu:309-406)
+ * out (n, num_rffs) f64, out += sum over windows; scaling_type 0 none / 1 sqrt / 2 full. */
+int xgpr_b200_conv1d_fgen_f32(const float*  x, int64_t n, int64_t m, int64_t c, double* out, int64_t num_rffs,
+                              const int8_t* radem, int64_t radem_len, const float*  chi, int64_t num_freqs,
+                              const int32_t* seqlengths_host, int conv_width, int scaling_type, void* stream);
+int xgpr_b200_conv1d_fgen_f64(const double* x, int64_t n, int64_t m, int64_t c, double* out, int64_t num_rffs,
+                              const int8_t* radem, int64_t radem_len, const double* chi, int64_t num_freqs,
+                              const int32_t* seqlengths_host, int conv_width, int scaling_type, void* stream);
+
+/* ---- cudaConvGrad  (xgpr_cuda_rfgen_cpp_ext.cpp:81-92; rbf_convolution.cu:431-535)
+ * as cudaConv1dFGen on the raw input plus grad (n, num_rffs, 1) f64 += dZ/dsigma. */
+int xgpr_b200_conv1d_grad_f32(const float*  x, int64_t n, int64_t m, int64_t c, double* out, int64_t num_rffs,
+                              const int8_t* radem, int64_t radem_len, const float*  chi, int64_t num_freqs,
+                              const int32_t* seqlengths_host, double* grad, double sigma,
+                              int conv_width, int scaling_type, void* stream);
+int xgpr_b200_conv1d_grad_f64(const double* x, int64_t n, int64_t m, int64_t c, double* out, int64_t num_rffs,
+                              const int8_t* radem, int64_t radem_len, const double* chi, int64_t num_freqs,
+                              const int32_t* seqlengths_host, double* grad, double sigma,
+                              int conv_width, int scaling_type, void* stream);
+
+/* ---- downstream consumers of Z: the `@` expressions of
+ *      src/xGPR/scoring_toolkit/exact_nmll_calcs.py:68-72 and src/xGPR/fitting_toolkit/cg_tools.py:42-44.
+ * z (n, m) f64 row-major; all accumulators f64, device, ACCUMULATED INTO (+=). */
+/* zty (m) += Z^T y ;  y (n) */
+int xgpr_b200_zty_accum_f64(const double* z, int64_t n, int64_t m, const double* y, double* zty, void* stream);
+/* ztz (m, m) += Z^T Z (full symmetric matrix written) */
+int xgpr_b200_ztz_accum_f64(const double* z, int64_t n, int64_t m, double* ztz, void* stream);
+/* w (m, r) += Z^T (Z v) ;  v (m, r) row-major; scratch (n, r) f64 device workspace */
+int xgpr_b200_cg_matvec_accum_f64(const double* z, int64_t n, int64_t m, const double* v, int64_t r,
+                                  double* w, double* scratch, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* XGPR_B200_H */

@@ -1,0 +1,68 @@
+"""ctypes loader for libxgpr_b200.so (the C ABI of include/xgpr_b200.h).
+
+There is NO fallback: if the library has not been built, importing this module raises, and every
+op in xgpr_b200 fails loudly (the product path never routes through oracle/ or the CPU).
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libxgpr_b200.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: build it with `python -m xgpr_b200.build_native` "
+        "(or __graft_entry__.build()). xgpr_b200 has no CPU / PyTorch fallback.")
+
+lib = ctypes.CDLL(LIB_PATH)
+
+_i64, _int, _dbl, _ptr = ctypes.c_int64, ctypes.c_int, ctypes.c_double, ctypes.c_void_p
+
+# name -> argtypes (all return int unless noted); mirrors include/xgpr_b200.h one to one
+SIGNATURES = {
+    "xgpr_b200_fht2d": [_ptr, _i64, _i64, _ptr],
+    "xgpr_b200_srht": [_ptr, _i64, _i64, _ptr, _i64, _ptr],
+    "xgpr_b200_rbf_feature_gen": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _int, _ptr],
+    "xgpr_b200_rbf_grad": [_ptr, _i64, _i64, _ptr, _ptr, _i64, _ptr, _i64, _ptr, _i64, _dbl, _int, _ptr],
+    "xgpr_b200_ard_grad": [_ptr, _i64, _i64, _ptr, _ptr, _i64, _ptr, _ptr, _ptr, _i64, _int, _ptr],
+    "xgpr_b200_conv1d_maxpool": [_ptr, _i64, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr, _int, _ptr],
+    "xgpr_b200_conv1d_fgen": [_ptr, _i64, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr, _int, _int, _ptr],
+    "xgpr_b200_conv1d_grad": [_ptr, _i64, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr, _ptr, _dbl,
+                              _int, _int, _ptr],
+}
+F64_ONLY = {
+    "xgpr_b200_zty_accum_f64": [_ptr, _i64, _i64, _ptr, _ptr, _ptr],
+    "xgpr_b200_ztz_accum_f64": [_ptr, _i64, _i64, _ptr, _ptr],
+    "xgpr_b200_cg_matvec_accum_f64": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _ptr, _ptr],
+}
+
+EXPORTED = ["xgpr_b200_abi_version", "xgpr_b200_last_error", "xgpr_b200_launch_count"]
+for _name, _args in SIGNATURES.items():
+    for _sfx in ("_f32", "_f64"):
+        _fn = getattr(lib, _name + _sfx)
+        _fn.argtypes = _args
+        _fn.restype = _int
+        EXPORTED.append(_name + _sfx)
+for _name, _args in F64_ONLY.items():
+    _fn = getattr(lib, _name)
+    _fn.argtypes = _args
+    _fn.restype = _int
+    EXPORTED.append(_name)
+
+lib.xgpr_b200_abi_version.restype = _int
+lib.xgpr_b200_last_error.restype = ctypes.c_char_p
+lib.xgpr_b200_launch_count.restype = _i64
+
+
+def last_error() -> str:
+    return lib.xgpr_b200_last_error().decode("utf-8", "replace")
+
+
+def launch_count() -> int:
+    return int(lib.xgpr_b200_launch_count())
+
+
+def check(rc: int) -> None:
+    """Maps the C return code to the reference's exception type (std::runtime_error -> RuntimeError)."""
+    if rc != 0:
+        raise RuntimeError(last_error())

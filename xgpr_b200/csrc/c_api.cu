@@ -1,0 +1,125 @@
+// c_api.cu -- the extern "C" boundary declared in include/xgpr_b200.h.
+#include "common.cuh"
+
+#include <atomic>
+
+namespace xb {
+
+static thread_local char g_err[512] = "";
+static std::atomic<int64_t> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+int check_launch(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_error("%s: %s", what, cudaGetErrorString(e));
+        return XGPR_B200_ECUDA;
+    }
+    return XGPR_B200_OK;
+}
+
+// implemented in the kernel translation units
+template <typename T, bool SRHT>
+int fht_dispatch(T* x, int64_t n, int64_t P, const int8_t* radem, int64_t radem_len, cudaStream_t st);
+template <typename T, bool GRAD>
+int rbf_dispatch(const T* x, int64_t n, int64_t d, double* out, double* grad, int64_t num_rffs,
+                 const int8_t* radem, int64_t R, const T* chi, int64_t F, double sigma, int fit_intercept,
+                 cudaStream_t st);
+template <typename T, int MODE>
+int conv_dispatch(const T* x, int64_t n, int64_t m, int64_t c, void* out, int64_t num_rffs, double* grad,
+                  const int8_t* radem, int64_t R, const T* chi, int64_t F, const int32_t* seq_host,
+                  double sigma, int conv_width, int scaling_type, cudaStream_t st);
+template <typename T>
+int ard_dispatch(const T* x, int64_t n, int64_t d, double* out, const T* w, int64_t F,
+                 const int32_t* sigma_map, const double* sigma_vals, double* grad, int64_t L,
+                 int fit_intercept, cudaStream_t st);
+int zty_accum(const double* z, int64_t n, int64_t m, const double* y, double* zty, cudaStream_t st);
+int ztz_accum(const double* z, int64_t n, int64_t m, double* ztz, cudaStream_t st);
+int cg_matvec_accum(const double* z, int64_t n, int64_t m, const double* v, int64_t r, double* w,
+                    double* scratch, cudaStream_t st);
+
+}  // namespace xb
+
+using namespace xb;
+#define ST(s) reinterpret_cast<cudaStream_t>(s)
+
+extern "C" {
+
+int xgpr_b200_abi_version(void) { return 1; }
+const char* xgpr_b200_last_error(void) { return g_err; }
+int64_t xgpr_b200_launch_count(void) { return g_launches.load(); }
+
+int xgpr_b200_fht2d_f32(float* x, int64_t n, int64_t p, void* s) { return fht_dispatch<float, false>(x, n, p, nullptr, 0, ST(s)); }
+int xgpr_b200_fht2d_f64(double* x, int64_t n, int64_t p, void* s) { return fht_dispatch<double, false>(x, n, p, nullptr, 0, ST(s)); }
+int xgpr_b200_srht_f32(float* x, int64_t n, int64_t p, const int8_t* radem, int64_t rl, void* s) { return fht_dispatch<float, true>(x, n, p, radem, rl, ST(s)); }
+int xgpr_b200_srht_f64(double* x, int64_t n, int64_t p, const int8_t* radem, int64_t rl, void* s) { return fht_dispatch<double, true>(x, n, p, radem, rl, ST(s)); }
+
+int xgpr_b200_rbf_feature_gen_f32(const float* x, int64_t n, int64_t d, double* out, int64_t num_rffs, const int8_t* radem,
+                                  int64_t rl, const float* chi, int64_t nf, int fi, void* s) {
+    return rbf_dispatch<float, false>(x, n, d, out, nullptr, num_rffs, radem, rl, chi, nf, 0.0, fi, ST(s));
+}
+int xgpr_b200_rbf_feature_gen_f64(const double* x, int64_t n, int64_t d, double* out, int64_t num_rffs, const int8_t* radem,
+                                  int64_t rl, const double* chi, int64_t nf, int fi, void* s) {
+    return rbf_dispatch<double, false>(x, n, d, out, nullptr, num_rffs, radem, rl, chi, nf, 0.0, fi, ST(s));
+}
+int xgpr_b200_rbf_grad_f32(const float* x, int64_t n, int64_t d, double* out, double* grad, int64_t num_rffs, const int8_t* radem,
+                           int64_t rl, const float* chi, int64_t nf, double sigma, int fi, void* s) {
+    return rbf_dispatch<float, true>(x, n, d, out, grad, num_rffs, radem, rl, chi, nf, sigma, fi, ST(s));
+}
+int xgpr_b200_rbf_grad_f64(const double* x, int64_t n, int64_t d, double* out, double* grad, int64_t num_rffs, const int8_t* radem,
+                           int64_t rl, const double* chi, int64_t nf, double sigma, int fi, void* s) {
+    return rbf_dispatch<double, true>(x, n, d, out, grad, num_rffs, radem, rl, chi, nf, sigma, fi, ST(s));
+}
+
+int xgpr_b200_ard_grad_f32(const float* x, int64_t n, int64_t d, double* out, const float* w, int64_t nf, const int32_t* smap,
+                           const double* svals, double* grad, int64_t L, int fi, void* s) {
+    return ard_dispatch<float>(x, n, d, out, w, nf, smap, svals, grad, L, fi, ST(s));
+}
+int xgpr_b200_ard_grad_f64(const double* x, int64_t n, int64_t d, double* out, const double* w, int64_t nf, const int32_t* smap,
+                           const double* svals, double* grad, int64_t L, int fi, void* s) {
+    return ard_dispatch<double>(x, n, d, out, w, nf, smap, svals, grad, L, fi, ST(s));
+}
+
+int xgpr_b200_conv1d_maxpool_f32(const float* x, int64_t n, int64_t m, int64_t c, float* out, int64_t num_rffs, const int8_t* radem,
+                                 int64_t rl, const float* chi, int64_t nf, const int32_t* sl, int cw, void* s) {
+    return conv_dispatch<float, 2>(x, n, m, c, out, num_rffs, nullptr, radem, rl, chi, nf, sl, 0.0, cw, 0, ST(s));
+}
+int xgpr_b200_conv1d_maxpool_f64(const double* x, int64_t n, int64_t m, int64_t c, float* out, int64_t num_rffs, const int8_t* radem,
+                                 int64_t rl, const double* chi, int64_t nf, const int32_t* sl, int cw, void* s) {
+    return conv_dispatch<double, 2>(x, n, m, c, out, num_rffs, nullptr, radem, rl, chi, nf, sl, 0.0, cw, 0, ST(s));
+}
+int xgpr_b200_conv1d_fgen_f32(const float* x, int64_t n, int64_t m, int64_t c, double* out, int64_t num_rffs, const int8_t* radem,
+                              int64_t rl, const float* chi, int64_t nf, const int32_t* sl, int cw, int stype, void* s) {
+    return conv_dispatch<float, 0>(x, n, m, c, out, num_rffs, nullptr, radem, rl, chi, nf, sl, 0.0, cw, stype, ST(s));
+}
+int xgpr_b200_conv1d_fgen_f64(const double* x, int64_t n, int64_t m, int64_t c, double* out, int64_t num_rffs, const int8_t* radem,
+                              int64_t rl, const double* chi, int64_t nf, const int32_t* sl, int cw, int stype, void* s) {
+    return conv_dispatch<double, 0>(x, n, m, c, out, num_rffs, nullptr, radem, rl, chi, nf, sl, 0.0, cw, stype, ST(s));
+}
+int xgpr_b200_conv1d_grad_f32(const float* x, int64_t n, int64_t m, int64_t c, double* out, int64_t num_rffs, const int8_t* radem,
+                              int64_t rl, const float* chi, int64_t nf, const int32_t* sl, double* grad, double sigma, int cw,
+                              int stype, void* s) {
+    return conv_dispatch<float, 1>(x, n, m, c, out, num_rffs, grad, radem, rl, chi, nf, sl, sigma, cw, stype, ST(s));
+}
+int xgpr_b200_conv1d_grad_f64(const double* x, int64_t n, int64_t m, int64_t c, double* out, int64_t num_rffs, const int8_t* radem,
+                              int64_t rl, const double* chi, int64_t nf, const int32_t* sl, double* grad, double sigma, int cw,
+                              int stype, void* s) {
+    return conv_dispatch<double, 1>(x, n, m, c, out, num_rffs, grad, radem, rl, chi, nf, sl, sigma, cw, stype, ST(s));
+}
+
+int xgpr_b200_zty_accum_f64(const double* z, int64_t n, int64_t m, const double* y, double* zty, void* s) {
+    return zty_accum(z, n, m, y, zty, ST(s));
+}
+int xgpr_b200_ztz_accum_f64(const double* z, int64_t n, int64_t m, double* ztz, void* s) { return ztz_accum(z, n, m, ztz, ST(s)); }
+int xgpr_b200_cg_matvec_accum_f64(const double* z, int64_t n, int64_t m, const double* v, int64_t r, double* w, double* scratch,
+                                  void* s) {
+    return cg_matvec_accum(z, n, m, v, r, w, scratch, ST(s));
+}
+
+}  // extern "C"

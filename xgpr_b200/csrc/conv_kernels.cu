@@ -1,0 +1,328 @@
+// conv_kernels.cu -- sliding-window SORF for Conv1d* / Graph* kernels with IN-KERNEL pooling.
+//
+// Replaces convRBFFeatureGenKernel / convRBFFeatureGradKernel
+// (gpu_rf_gen/convolution_ops/rbf_convolution.cu:18-153, :162-301) and convMaxpoolFeatureGenKernel
+// (gpu_rf_gen/convolution_ops/convolution.cu:16-136).  Numerics follow the CPU oracle:
+// cpu_rf_gen/convolution_ops/rbf_convolution.cpp:22-139, :159-282 and conv1d_operations.cpp:22-168.
+//
+// Each slot (K lanes) owns one (sequence, repeat) pair: signs and chi stay in registers, the
+// slot slides over the sequence's windows, pools in fp64 (sum) or fp32 (max) registers in the same
+// window order as the oracle, and touches the output row exactly once -- instead of the
+// reference's global read-modify-write per window per repeat and its N*(M-w+1)*P scratch buffer.
+#include "sorf_warp.cuh"
+
+#include <mutex>
+#include <unordered_map>
+
+namespace xb {
+
+enum ConvMode { CONV_FGEN = 0, CONV_GRAD = 1, CONV_MAXPOOL = 2 };
+
+// rowScaler of rbf_convolution.cpp:100-111 (double)
+__device__ __forceinline__ double conv_row_scale(double base, int nk, int scaling_type) {
+    if (scaling_type == 1) return base / sqrt((double)nk);
+    if (scaling_type == 2) return base / (double)nk;
+    return base;
+}
+
+template <typename T, int P, int K, int MODE, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
+conv_warp_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __restrict__ grad,
+                 const int8_t* __restrict__ radem, const T* __restrict__ chi,
+                 const int32_t* __restrict__ seqlen, int N, int M, int C, int F, int64_t R,
+                 int reps, int RC, int conv_width, int scaling_type, T cnorm, double base_scale,
+                 double sigma) {
+    constexpr int E = P / K;
+    constexpr int V = 32 / K;
+    constexpr int S = WARPS * V;
+    constexpr bool FS = (sizeof(T) == 4) && (E <= 8);
+    constexpr int NACC = (MODE == CONV_GRAD) ? 4 : 2;
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = lane % K, q = lane / K;
+    const int g = warp * V + q;
+    const int rep = blockIdx.y * RC + (g % RC);
+    const int rowlane = g / RC;
+    const int nrl = S / RC;
+    const int row = blockIdx.x * nrl + rowlane;
+    const bool ok = (rep < reps) && (row < N);
+    const int64_t base = (int64_t)rep * P;
+    const int wlen = conv_width * C;
+
+    Signs<T, E, K, FS> sg;
+    sg.load(radem, R, base, sub, ok, cnorm);
+    T ch[E];
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        const int64_t idx = base + sub + K * r;
+        ch[r] = (ok && idx < F) ? chi[idx] : T(0);
+    }
+
+    const int nk = ok ? (seqlen[row] - conv_width + 1) : 0;
+    int nk_max = nk;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) nk_max = max(nk_max, __shfl_xor_sync(0xffffffffu, nk_max, o));
+    const double scale = conv_row_scale(base_scale, nk > 0 ? nk : 1, scaling_type);
+
+    double acc[E][NACC];
+    float  mx[E];
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        mx[r] = 0.f;
+#pragma unroll
+        for (int a = 0; a < NACC; ++a) acc[r][a] = 0.0;
+    }
+
+    const T* xrow = x + (size_t)row * M * C;
+    for (int j = 0; j < nk_max; ++j) {
+        const bool act = j < nk;
+        const T* win = xrow + (size_t)j * C;
+        T v[E];
+#pragma unroll
+        for (int r = 0; r < E; ++r) {
+            const int e = sub + K * r;
+            v[r] = (act && e < wlen) ? __ldg(win + e) : T(0);
+        }
+        warp_sorf<T, E, K, FS>(v, sg, sub, cnorm);
+        if (act) {
+#pragma unroll
+            for (int r = 0; r < E; ++r) {
+                if (MODE == CONV_MAXPOOL) {
+                    // conv1d_operations.cpp:161-167: float prodVal = x * chi; out = max(out, prodVal)
+                    const float pv = (float)mul_rn(v[r], ch[r]);
+                    mx[r] = fmaxf(mx[r], pv);
+                } else if (MODE == CONV_FGEN) {
+                    const T a = mul_rn(v[r], ch[r]);
+                    T sn, cs;
+                    sincos_t(a, &sn, &cs);
+                    acc[r][0] = __dadd_rn(acc[r][0], __dmul_rn((double)cs, scale));
+                    acc[r][1] = __dadd_rn(acc[r][1], __dmul_rn((double)sn, scale));
+                } else {
+                    const T gv = mul_rn(v[r], ch[r]);
+                    const T p = (T)((double)gv * sigma);
+                    T sn, cs;
+                    sincos_t(p, &sn, &cs);
+                    const T cv = (T)((double)cs * scale);
+                    const T sv = (T)((double)sn * scale);
+                    acc[r][0] = __dadd_rn(acc[r][0], (double)cv);
+                    acc[r][1] = __dadd_rn(acc[r][1], (double)sv);
+                    acc[r][2] = __dsub_rn(acc[r][2], (double)mul_rn(sv, gv));
+                    acc[r][3] = __dadd_rn(acc[r][3], (double)mul_rn(cv, gv));
+                }
+            }
+        }
+    }
+
+    if (!ok) return;
+    if (MODE == CONV_MAXPOOL) {
+        float* orow = reinterpret_cast<float*>(out_v) + (size_t)row * F;
+#pragma unroll
+        for (int r = 0; r < E; ++r) {
+            const int64_t idx = base + sub + K * r;
+            if (idx < F) orow[idx] = fmaxf(orow[idx], mx[r]);
+        }
+    } else {
+        double2* orow = reinterpret_cast<double2*>(reinterpret_cast<double*>(out_v) + (size_t)row * 2 * F);
+        double2* grow = (MODE == CONV_GRAD) ? reinterpret_cast<double2*>(grad + (size_t)row * 2 * F) : nullptr;
+#pragma unroll
+        for (int r = 0; r < E; ++r) {
+            const int64_t idx = base + sub + K * r;
+            if (idx < F) {
+                double2 o = orow[idx];          // `+=` semantics of the reference API
+                o.x += acc[r][0];
+                o.y += acc[r][1];
+                orow[idx] = o;
+                if (MODE == CONV_GRAD) {
+                    double2 go = grow[idx];
+                    go.x += acc[r][2];
+                    go.y += acc[r][3];
+                    grow[idx] = go;
+                }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ P > 1024 (conv_width * C > 1024)
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256)
+conv_cta_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __restrict__ grad,
+                const int8_t* __restrict__ radem, const T* __restrict__ chi,
+                const int32_t* __restrict__ seqlen, int N, int M, int C, int P, int F, int64_t R,
+                int reps, int conv_width, int scaling_type, T cnorm, double base_scale, double sigma) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T* buf = reinterpret_cast<T*>(smem_raw);
+    const int wlen = conv_width * C;
+    for (int row = blockIdx.x; row < N; row += gridDim.x) {
+        const int nk = seqlen[row] - conv_width + 1;
+        const double scale = conv_row_scale(base_scale, nk, scaling_type);
+        const T* xrow = x + (size_t)row * M * C;
+        for (int j = 0; j < nk; ++j) {
+            const T* win = xrow + (size_t)j * C;
+            for (int rep = 0; rep < reps; ++rep) {
+                const int64_t base = (int64_t)rep * P;
+                for (int e = threadIdx.x; e < P; e += blockDim.x) buf[e] = (e < wlen) ? win[e] : T(0);
+                __syncthreads();
+                cta_sorf<T>(buf, P, radem, R, base, cnorm);
+                for (int e = threadIdx.x; e < P; e += blockDim.x) {
+                    const int64_t idx = base + e;
+                    if (idx >= F) continue;
+                    if (MODE == CONV_MAXPOOL) {
+                        float* o = reinterpret_cast<float*>(out_v) + (size_t)row * F + idx;
+                        *o = fmaxf(*o, (float)mul_rn(buf[e], chi[idx]));
+                    } else if (MODE == CONV_FGEN) {
+                        double* o = reinterpret_cast<double*>(out_v) + (size_t)row * 2 * F + 2 * idx;
+                        const T a = mul_rn(buf[e], chi[idx]);
+                        T sn, cs;
+                        sincos_t(a, &sn, &cs);
+                        o[0] = __dadd_rn(o[0], __dmul_rn((double)cs, scale));
+                        o[1] = __dadd_rn(o[1], __dmul_rn((double)sn, scale));
+                    } else {
+                        double* o = reinterpret_cast<double*>(out_v) + (size_t)row * 2 * F + 2 * idx;
+                        double* go = grad + (size_t)row * 2 * F + 2 * idx;
+                        const T gv = mul_rn(buf[e], chi[idx]);
+                        const T p = (T)((double)gv * sigma);
+                        T sn, cs;
+                        sincos_t(p, &sn, &cs);
+                        const T cv = (T)((double)cs * scale);
+                        const T sv = (T)((double)sn * scale);
+                        o[0] = __dadd_rn(o[0], (double)cv);
+                        o[1] = __dadd_rn(o[1], (double)sv);
+                        go[0] = __dsub_rn(go[0], (double)mul_rn(sv, gv));
+                        go[1] = __dadd_rn(go[1], (double)mul_rn(cv, gv));
+                    }
+                }
+                __syncthreads();
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ host side
+// seqlengths arrive on the HOST (reference API).  They are validated here, then staged into a
+// grow-only per-stream device buffer (no cudaMalloc / cudaFree per call, no blocking copy).
+struct SeqBuf { int32_t* dev = nullptr; size_t cap = 0; };
+static std::mutex g_seq_mu;
+static std::unordered_map<void*, SeqBuf> g_seq;
+
+static int stage_seqlen(const int32_t* host, int64_t n, cudaStream_t st, const int32_t** dev_out) {
+    std::lock_guard<std::mutex> lk(g_seq_mu);
+    SeqBuf& b = g_seq[(void*)st];
+    if (b.cap < (size_t)n) {
+        if (b.dev) {
+            cudaStreamSynchronize(st);
+            cudaFree(b.dev);
+        }
+        size_t cap = 1024;
+        while (cap < (size_t)n) cap <<= 1;
+        if (cudaMalloc(&b.dev, cap * sizeof(int32_t)) != cudaSuccess) {
+            b.dev = nullptr; b.cap = 0;
+            cudaGetLastError();
+            set_error("out of memory on cuda");
+            return XGPR_B200_ECUDA;
+        }
+        b.cap = cap;
+    }
+    if (cudaMemcpyAsync(b.dev, host, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st) != cudaSuccess) {
+        set_error("seqlengths copy failed: %s", cudaGetErrorString(cudaGetLastError()));
+        return XGPR_B200_ECUDA;
+    }
+    *dev_out = b.dev;
+    return XGPR_B200_OK;
+}
+
+static inline int pow2_ceil(int v) { int p = 1; while (p < v) p *= 2; return p; }
+
+template <typename T, int P, int K, int MODE>
+static int launch_conv_warp(const T* x, int64_t n, int64_t m, int64_t c, void* out, double* grad,
+                            const int8_t* radem, int64_t R, const T* chi, int64_t F, const int32_t* seq_dev,
+                            int conv_width, int scaling_type, double base_scale, double sigma, cudaStream_t st) {
+    constexpr int WARPS = (MODE == CONV_GRAD) ? 4 : 8;
+    constexpr int V = 32 / K;
+    constexpr int S = WARPS * V;
+    const int reps = (int)((F + P - 1) / P);
+    int RC = pow2_ceil(reps);
+    if (RC > S) RC = S;
+    const int nrl = S / RC;
+    dim3 grid((unsigned)((n + nrl - 1) / nrl), (unsigned)((reps + RC - 1) / RC));
+    conv_warp_kernel<T, P, K, MODE, WARPS><<<grid, WARPS * 32, 0, st>>>(
+        x, out, grad, radem, chi, seq_dev, (int)n, (int)m, (int)c, (int)F, R, reps, RC, conv_width,
+        scaling_type, norm_constant<T>(P), base_scale, sigma);
+    count_launch();
+    return check_launch("conv_warp_kernel");
+}
+
+template <typename T, int MODE>
+int conv_dispatch(const T* x, int64_t n, int64_t m, int64_t c, void* out, int64_t num_rffs, double* grad,
+                  const int8_t* radem, int64_t R, const T* chi, int64_t F, const int32_t* seq_host,
+                  double sigma, int conv_width, int scaling_type, cudaStream_t st) {
+    // validation: cpu_rf_gen/convolution_ops/rbf_convolution.cpp:47-82, conv1d_operations.cpp:45-79
+    XB_REQUIRE(n > 0, "no datapoints");
+    XB_REQUIRE(num_rffs >= 2 && (num_rffs & 1) == 0, "last dim of output must be even number");
+    if (MODE == CONV_MAXPOOL) XB_REQUIRE(F == num_rffs && F <= R, "incorrect number of rffs and or freqs.");
+    else XB_REQUIRE(2 * F == num_rffs && F <= R, "incorrect number of rffs and or freqs.");
+    XB_REQUIRE(m >= conv_width && conv_width > 0, "invalid conv_width");
+    XB_REQUIRE(c > 0, "no datapoints");
+    const int64_t P = padded_width((int64_t)conv_width * c);
+    XB_REQUIRE(R % P == 0, "incorrect number of rffs and or freqs.");
+    const int64_t reps64 = (F + P - 1) / P;
+    if (MODE == CONV_MAXPOOL) XB_REQUIRE(R == reps64 * P, "incorrect number of rffs and or freqs.");
+    XB_REQUIRE(x && out && radem && chi && seq_host && (MODE != CONV_GRAD || grad), "null pointer");
+    XB_REQUIRE(n < (1ll << 31) && F < (1ll << 30) && n * m * c < (1ll << 40), "array too large");
+    int32_t mn = 2147483647, mxl = 0;
+    for (int64_t i = 0; i < n; ++i) {
+        if (seq_host[i] > mxl) mxl = seq_host[i];
+        if (seq_host[i] < mn) mn = seq_host[i];
+    }
+    XB_REQUIRE(!(mxl > (int32_t)m || mn < conv_width),
+               "All sequence lengths must be >= conv width and < array size.");
+
+    const int32_t* seq_dev = nullptr;
+    int rc = stage_seqlen(seq_host, n, st, &seq_dev);
+    if (rc != XGPR_B200_OK) return rc;
+    const double base_scale = sqrt(1.0 / (double)F);   // rbf_convolution.cpp:40
+
+#define XB_CASE(PP, KK)                                                                                   \
+    case PP: return launch_conv_warp<T, PP, KK, MODE>(x, n, m, c, out, grad, radem, R, chi, F, seq_dev,   \
+                                                      conv_width, scaling_type, base_scale, sigma, st);
+    switch (P) {
+        XB_CASE(2, 2)
+        XB_CASE(4, 4)
+        XB_CASE(8, 8)
+        XB_CASE(16, 8)
+        XB_CASE(32, 8)
+        XB_CASE(64, 8)
+        XB_CASE(128, 16)
+        XB_CASE(256, 32)
+        XB_CASE(512, 32)
+        XB_CASE(1024, 32)
+        default: break;
+    }
+#undef XB_CASE
+    const size_t smem = (size_t)P * sizeof(T);
+    if (smem > 200 * 1024) {
+        set_error("conv_width * channels too large for the shared-memory SORF path");
+        return XGPR_B200_EINVAL;
+    }
+    auto kern = conv_cta_kernel<T, MODE>;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const int grid = (int)(n < 148 * 16 ? n : 148 * 16);
+    kern<<<grid, 256, smem, st>>>(x, out, grad, radem, chi, seq_dev, (int)n, (int)m, (int)c, (int)P, (int)F, R,
+                                  (int)reps64, conv_width, scaling_type, norm_constant<T>(P), base_scale, sigma);
+    count_launch();
+    return check_launch("conv_cta_kernel");
+}
+
+#define XB_INST(T, MODE)                                                                                      \
+    template int conv_dispatch<T, MODE>(const T*, int64_t, int64_t, int64_t, void*, int64_t, double*,         \
+                                        const int8_t*, int64_t, const T*, int64_t, const int32_t*, double,    \
+                                        int, int, cudaStream_t);
+XB_INST(float, CONV_FGEN)
+XB_INST(float, CONV_GRAD)
+XB_INST(float, CONV_MAXPOOL)
+XB_INST(double, CONV_FGEN)
+XB_INST(double, CONV_GRAD)
+XB_INST(double, CONV_MAXPOOL)
+#undef XB_INST
+
+}  // namespace xb

@@ -1,0 +1,204 @@
+// fht_kernels.cu -- in-place row-wise FWHT and SRHT (x <- FWHT(x * radem * P^-1/2)).
+//
+// Replaces hadamardTransform / hadamardTransformRadMult
+// (gpu_rf_gen/basic_ops/basic_array_operations.cu:15-74, :77-145) and their wrappers (:187-265).
+// Numerics follow the CPU oracle: cpu_rf_gen/basic_ops/transform_functions.cpp:58-80, :94-121,
+// cpu_rf_gen/shared_fht_functions/hadamard_transforms.cpp:16-71 (ascending radix-2 stages) and
+// shared_rfgen_ops.cpp:18-34 (one rounding for x * (radem * c)).
+#include "sorf_warp.cuh"
+
+namespace xb {
+
+// ------------------------------------------------------------------ P <= 1024: registers + shuffles
+template <typename T, int P, int K, bool SRHT, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
+fht_warp_kernel(T* __restrict__ x, const int8_t* __restrict__ radem, int64_t N, T cnorm) {
+    constexpr int E = P / K;
+    constexpr int V = 32 / K;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = lane % K, q = lane / K;
+    T sc[E];
+    if (SRHT) {
+#pragma unroll
+        for (int r = 0; r < E; ++r) sc[r] = (T)radem[sub + K * r] * cnorm;
+    }
+    const int64_t rows_per_iter = (int64_t)gridDim.x * WARPS * V;
+    const int64_t first = ((int64_t)blockIdx.x * WARPS + warp) * V + q;
+    // uniform trip count for the whole warp (shuffles need all 32 lanes)
+    const int64_t iters = (N + rows_per_iter - 1) / rows_per_iter;
+    for (int64_t it = 0; it < iters; ++it) {
+        const int64_t row = first + it * rows_per_iter;
+        const bool ok = row < N;
+        T* xr = x + row * P;
+        T v[E];
+#pragma unroll
+        for (int r = 0; r < E; ++r) v[r] = ok ? xr[sub + K * r] : T(0);
+        if (SRHT) {
+#pragma unroll
+            for (int r = 0; r < E; ++r) v[r] = mul_rn(v[r], sc[r]);
+        }
+        warp_fwht<T, E, K>(v, sub);
+        if (ok) {
+#pragma unroll
+            for (int r = 0; r < E; ++r) xr[sub + K * r] = v[r];
+        }
+    }
+}
+
+// ------------------------------------------------------------------ 1024 < P, row fits shared memory
+// Phase 1: each warp transforms 1024-element segments in registers (strides 1..512);
+// Phase 2: strides 1024..P/2 in shared memory.  One row per CTA iteration.
+template <typename T, bool SRHT>
+__global__ void __launch_bounds__(512)
+fht_cta_kernel(T* __restrict__ x, const int8_t* __restrict__ radem, int64_t N, int P, T cnorm) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T* buf = reinterpret_cast<T*>(smem_raw);
+    constexpr int E = 32, K = 32, SEG = 1024;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    for (int64_t row = blockIdx.x; row < N; row += gridDim.x) {
+        T* xr = x + row * (int64_t)P;
+        for (int seg = warp; seg < P / SEG; seg += nwarps) {
+            T v[E];
+            const int off = seg * SEG;
+#pragma unroll
+            for (int r = 0; r < E; ++r) {
+                const int j = off + lane + K * r;
+                T t = xr[j];
+                if (SRHT) t = mul_rn(t, (T)radem[j] * cnorm);
+                v[r] = t;
+            }
+            warp_fwht<T, E, K>(v, lane);
+#pragma unroll
+            for (int r = 0; r < E; ++r) buf[off + lane + K * r] = v[r];
+        }
+        __syncthreads();
+        const int half = P >> 1;
+        for (int h = SEG; h < P; h <<= 1) {
+            for (int t = threadIdx.x; t < half; t += blockDim.x) {
+                const int i = ((t & ~(h - 1)) << 1) | (t & (h - 1));
+                const T a = buf[i], b = buf[i + h];
+                buf[i]     = add_rn(a, b);
+                buf[i + h] = sub_rn(a, b);
+            }
+            __syncthreads();
+        }
+        for (int j = threadIdx.x; j < P; j += blockDim.x) xr[j] = buf[j];
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------ row larger than shared memory
+// Pass A: the CTA kernel above on SEGP-element segments (treated as rows).  Pass B: the remaining
+// strides SEGP..P/2 across segments, element-wise (each thread owns one offset within a segment and
+// runs a small FWHT over the P/SEGP segment values; values stay in L2 between the passes).
+template <typename T, int NSEG>
+__global__ void __launch_bounds__(256)
+fht_cross_kernel(T* __restrict__ x, int64_t N, int64_t P, int64_t SEGP) {
+    const int64_t total = N * SEGP;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = t / SEGP, off = t % SEGP;
+        T* base = x + row * P + off;
+        T v[NSEG];
+#pragma unroll
+        for (int s = 0; s < NSEG; ++s) v[s] = base[s * SEGP];
+#pragma unroll
+        for (int h = 1; h < NSEG; h <<= 1)
+#pragma unroll
+            for (int i = 0; i < NSEG; ++i)
+                if ((i & h) == 0) {
+                    const T a = v[i], b = v[i + h];
+                    v[i]     = add_rn(a, b);
+                    v[i + h] = sub_rn(a, b);
+                }
+#pragma unroll
+        for (int s = 0; s < NSEG; ++s) base[s * SEGP] = v[s];
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+radem_scale_kernel(T* __restrict__ x, const int8_t* __restrict__ radem, int64_t N, int64_t P, T cnorm) {
+    const int64_t total = N * P;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (int64_t)gridDim.x * blockDim.x)
+        x[t] = mul_rn(x[t], (T)radem[t % P] * cnorm);
+}
+
+// ------------------------------------------------------------------ host dispatch
+template <typename T, int P, int K, bool SRHT>
+static int launch_fht_warp(T* x, int64_t n, const int8_t* radem, cudaStream_t st) {
+    constexpr int WARPS = 8;
+    constexpr int V = 32 / K;
+    int64_t blocks = (n + WARPS * V - 1) / (WARPS * V);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    fht_warp_kernel<T, P, K, SRHT, WARPS><<<(unsigned)blocks, WARPS * 32, 0, st>>>(x, radem, n, norm_constant<T>(P));
+    count_launch();
+    return check_launch("fht_warp_kernel");
+}
+
+template <typename T, bool SRHT>
+static int launch_fht_cta(T* x, int64_t n, int64_t P, const int8_t* radem, cudaStream_t st) {
+    const size_t smem = (size_t)P * sizeof(T);
+    auto kern = fht_cta_kernel<T, SRHT>;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int64_t blocks = n < 148 * 4 ? n : 148 * 4;
+    kern<<<(unsigned)blocks, 512, smem, st>>>(x, radem, n, (int)P, norm_constant<T>(P));
+    count_launch();
+    return check_launch("fht_cta_kernel");
+}
+
+template <typename T, bool SRHT>
+int fht_dispatch(T* x, int64_t n, int64_t P, const int8_t* radem, int64_t radem_len, cudaStream_t st) {
+    // validation: cpu_rf_gen/basic_ops/transform_functions.cpp:69-74, :107-114
+    XB_REQUIRE(n > 0, "no datapoints");
+    if (SRHT) XB_REQUIRE(P == radem_len, "incorrect array dims passed");
+    XB_REQUIRE(P >= 2, "last dim not power of 2 > 1");
+    XB_REQUIRE((P & (P - 1)) == 0, "last dim not power of 2");
+    XB_REQUIRE(x && (!SRHT || radem), "null pointer");
+#define XB_CASE(PP, KK) case PP: return launch_fht_warp<T, PP, KK, SRHT>(x, n, radem, st);
+    switch (P) {
+        XB_CASE(2, 2)
+        XB_CASE(4, 4)
+        XB_CASE(8, 8)
+        XB_CASE(16, 8)
+        XB_CASE(32, 8)
+        XB_CASE(64, 8)
+        XB_CASE(128, 16)
+        XB_CASE(256, 32)
+        XB_CASE(512, 32)
+        XB_CASE(1024, 32)
+        default: break;
+    }
+#undef XB_CASE
+    constexpr int64_t SMEM_MAX = 128 * 1024;
+    if (P * (int64_t)sizeof(T) <= SMEM_MAX) return launch_fht_cta<T, SRHT>(x, n, P, radem, st);
+
+    // two passes through L2: segments of SEGP elements in shared memory, then the cross-segment strides
+    const int64_t SEGP = SMEM_MAX / (int64_t)sizeof(T);
+    const int64_t nseg = P / SEGP;
+    XB_REQUIRE(nseg <= 64, "row too long for the FWHT");
+    if (SRHT) {
+        radem_scale_kernel<T><<<148 * 8, 256, 0, st>>>(x, radem, n, P, norm_constant<T>(P));
+        count_launch();
+    }
+    int rc = launch_fht_cta<T, false>(x, n * nseg, SEGP, nullptr, st);
+    if (rc != XGPR_B200_OK) return rc;
+    switch (nseg) {
+        case 2:  fht_cross_kernel<T, 2><<<148 * 8, 256, 0, st>>>(x, n, P, SEGP); break;
+        case 4:  fht_cross_kernel<T, 4><<<148 * 8, 256, 0, st>>>(x, n, P, SEGP); break;
+        case 8:  fht_cross_kernel<T, 8><<<148 * 8, 256, 0, st>>>(x, n, P, SEGP); break;
+        case 16: fht_cross_kernel<T, 16><<<148 * 8, 256, 0, st>>>(x, n, P, SEGP); break;
+        case 32: fht_cross_kernel<T, 32><<<148 * 8, 256, 0, st>>>(x, n, P, SEGP); break;
+        default: fht_cross_kernel<T, 64><<<148 * 8, 256, 0, st>>>(x, n, P, SEGP); break;
+    }
+    count_launch();
+    return check_launch("fht_cross_kernel");
+}
+
+template int fht_dispatch<float, false>(float*, int64_t, int64_t, const int8_t*, int64_t, cudaStream_t);
+template int fht_dispatch<float, true>(float*, int64_t, int64_t, const int8_t*, int64_t, cudaStream_t);
+template int fht_dispatch<double, false>(double*, int64_t, int64_t, const int8_t*, int64_t, cudaStream_t);
+template int fht_dispatch<double, true>(double*, int64_t, int64_t, const int8_t*, int64_t, cudaStream_t);
+
+}  // namespace xb

@@ -1,0 +1,206 @@
+// gram_kernels.cu -- downstream consumers of Z: Z^T y, Z^T Z and the CG matvec Z^T (Z v), fp64.
+//
+// These replace the NumPy/CuPy `@` expressions of the reference's L4 loops
+// (src/xGPR/scoring_toolkit/exact_nmll_calcs.py:68-72, src/xGPR/fitting_toolkit/cg_tools.py:42-44,
+// src/xGPR/preconditioners/rand_nys_constructors.py:117-119).  All accumulate (+=) into
+// caller-owned fp64 device arrays so that chunks and (after an all-reduce) GPUs can be summed.
+//
+// Round-1 implementation: fp64 FMA-pipe kernels (exact analogue of the reference's DGEMM/DGEMV
+// arithmetic).  The tcgen05 split-precision Gram build is the next step.
+#include "common.cuh"
+
+namespace xb {
+
+// ------------------------------------------------------------------ zty[m] += sum_n Z[n,m] * y[n]
+// Also used for w[m, 0:RB] += sum_n Z[n,m] * t[n, 0:RB].
+template <int RB>
+__global__ void __launch_bounds__(256)
+zt_times_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double* __restrict__ t, int64_t ldt,
+                int r0, int rcount, double* __restrict__ w, int64_t ldw, int64_t rows_per_block) {
+    const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t n0 = (int64_t)blockIdx.y * rows_per_block;
+    const int64_t n1 = (n0 + rows_per_block < n) ? n0 + rows_per_block : n;
+    __shared__ double ts[64][RB];
+    double acc[RB];
+#pragma unroll
+    for (int j = 0; j < RB; ++j) acc[j] = 0.0;
+    for (int64_t nb = n0; nb < n1; nb += 64) {
+        const int cnt = (int)((n1 - nb < 64) ? (n1 - nb) : 64);
+        __syncthreads();
+        for (int i = threadIdx.x; i < cnt * RB; i += blockDim.x) {
+            const int rr = i / RB, j = i % RB;
+            ts[rr][j] = (j < rcount) ? t[(nb + rr) * ldt + r0 + j] : 0.0;
+        }
+        __syncthreads();
+        if (col < m) {
+            const double* zp = z + nb * m + col;
+#pragma unroll 4
+            for (int rr = 0; rr < cnt; ++rr) {
+                const double zv = zp[(int64_t)rr * m];
+#pragma unroll
+                for (int j = 0; j < RB; ++j) acc[j] = fma(zv, ts[rr][j], acc[j]);
+            }
+        }
+    }
+    if (col < m) {
+#pragma unroll
+        for (int j = 0; j < RB; ++j)
+            if (j < rcount) atomicAdd(w + col * ldw + r0 + j, acc[j]);
+    }
+}
+
+// ------------------------------------------------------------------ t[n, r0:r0+RB] = Z[n,:] . v[:, r0:r0+RB]
+template <int RB>
+__global__ void __launch_bounds__(256)
+z_times_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double* __restrict__ v, int64_t ldv,
+               int r0, int rcount, double* __restrict__ t, int64_t ldt) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t row = warp; row < n; row += nwarps) {
+        const double* zr = z + row * m;
+        double acc[RB];
+#pragma unroll
+        for (int j = 0; j < RB; ++j) acc[j] = 0.0;
+        for (int64_t c = lane; c < m; c += 32) {
+            const double zv = zr[c];
+#pragma unroll
+            for (int j = 0; j < RB; ++j)
+                if (j < rcount) acc[j] = fma(zv, __ldg(v + c * ldv + r0 + j), acc[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < RB; ++j) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], o);
+        }
+        if (lane == 0) {
+#pragma unroll
+            for (int j = 0; j < RB; ++j)
+                if (j < rcount) t[row * ldt + r0 + j] = acc[j];
+        }
+    }
+}
+
+// ------------------------------------------------------------------ ztz += Z^T Z  (upper tiles, mirrored)
+// 64x64 output tile per CTA, 256 threads, 4x4 register micro-tile, k-chunks of 16 rows staged in smem.
+constexpr int GT = 64, GK = 16;
+__global__ void __launch_bounds__(256)
+ztz_kernel(const double* __restrict__ z, int64_t n, int64_t m, double* __restrict__ c, int tiles,
+           int64_t rows_per_split) {
+    // linear tile id -> (ti <= tj)
+    int tid_lin = blockIdx.x;
+    int ti = 0;
+    while (tid_lin >= tiles - ti) { tid_lin -= tiles - ti; ++ti; }
+    const int tj = ti + tid_lin;
+    const int64_t i0 = (int64_t)ti * GT, j0 = (int64_t)tj * GT;
+    const int64_t n0 = (int64_t)blockIdx.y * rows_per_split;
+    const int64_t n1 = (n0 + rows_per_split < n) ? n0 + rows_per_split : n;
+
+    __shared__ double as[GK][GT];
+    __shared__ double bs[GK][GT];
+    const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;
+    double acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+
+    for (int64_t k0 = n0; k0 < n1; k0 += GK) {
+        __syncthreads();
+        for (int t = threadIdx.x; t < GK * GT; t += 256) {
+            const int kk = t / GT, cc = t % GT;
+            const int64_t row = k0 + kk;
+            as[kk][cc] = (row < n1 && i0 + cc < m) ? z[row * m + i0 + cc] : 0.0;
+            bs[kk][cc] = (row < n1 && j0 + cc < m) ? z[row * m + j0 + cc] : 0.0;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < GK; ++kk) {
+            double av[4], bv[4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) av[a] = as[kk][ty + 16 * a];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) bv[b] = bs[kk][tx + 16 * b];
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) acc[a][b] = fma(av[a], bv[b], acc[a][b]);
+        }
+    }
+    const bool split = gridDim.y > 1;
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int64_t i = i0 + ty + 16 * a, j = j0 + tx + 16 * b;
+            if (i < m && j < m) {
+                if (ti == tj && j < i) continue;   // diagonal tile: upper part only, mirrored below
+                if (split) {
+                    atomicAdd(c + i * m + j, acc[a][b]);
+                    if (i != j) atomicAdd(c + j * m + i, acc[a][b]);
+                } else {
+                    c[i * m + j] += acc[a][b];
+                    if (i != j) c[j * m + i] += acc[a][b];
+                }
+            }
+        }
+}
+
+// ------------------------------------------------------------------ host
+int zty_accum(const double* z, int64_t n, int64_t m, const double* y, double* zty, cudaStream_t st) {
+    XB_REQUIRE(n > 0 && m > 0, "no datapoints");
+    XB_REQUIRE(z && y && zty, "null pointer");
+    const int64_t colblocks = (m + 255) / 256;
+    int64_t splits = (148 * 4 + colblocks - 1) / colblocks;
+    int64_t rows_per = (n + splits - 1) / splits;
+    rows_per = ((rows_per + 63) / 64) * 64;
+    splits = (n + rows_per - 1) / rows_per;
+    dim3 grid((unsigned)colblocks, (unsigned)splits);
+    zt_times_kernel<1><<<grid, 256, 0, st>>>(z, n, m, y, 1, 0, 1, zty, 1, rows_per);
+    count_launch();
+    return check_launch("zt_times_kernel");
+}
+
+int ztz_accum(const double* z, int64_t n, int64_t m, double* ztz, cudaStream_t st) {
+    XB_REQUIRE(n > 0 && m > 0, "no datapoints");
+    XB_REQUIRE(z && ztz, "null pointer");
+    const int tiles = (int)((m + GT - 1) / GT);
+    const int64_t ntile = (int64_t)tiles * (tiles + 1) / 2;
+    int64_t splits = 1;
+    if (ntile < 148 * 2) splits = (148 * 2 + ntile - 1) / ntile;
+    int64_t rows_per = (n + splits - 1) / splits;
+    rows_per = ((rows_per + GK - 1) / GK) * GK;
+    splits = (n + rows_per - 1) / rows_per;
+    dim3 grid((unsigned)ntile, (unsigned)splits);
+    ztz_kernel<<<grid, 256, 0, st>>>(z, n, m, ztz, tiles, rows_per);
+    count_launch();
+    return check_launch("ztz_kernel");
+}
+
+int cg_matvec_accum(const double* z, int64_t n, int64_t m, const double* v, int64_t r, double* w,
+                    double* scratch, cudaStream_t st) {
+    XB_REQUIRE(n > 0 && m > 0 && r > 0, "no datapoints");
+    XB_REQUIRE(z && v && w && scratch, "null pointer");
+    const int64_t colblocks = (m + 255) / 256;
+    int64_t splits = (148 * 4 + colblocks - 1) / colblocks;
+    int64_t rows_per = (n + splits - 1) / splits;
+    rows_per = ((rows_per + 63) / 64) * 64;
+    splits = (n + rows_per - 1) / rows_per;
+    dim3 grid2((unsigned)colblocks, (unsigned)splits);
+    int64_t wblocks = (n + 7) / 8;
+    if (wblocks > 148 * 16) wblocks = 148 * 16;
+    for (int r0 = 0; r0 < r; r0 += 8) {
+        const int rc = (int)((r - r0 < 8) ? (r - r0) : 8);
+        if (rc == 1) {
+            z_times_kernel<1><<<(unsigned)wblocks, 256, 0, st>>>(z, n, m, v, r, r0, rc, scratch, r);
+            zt_times_kernel<1><<<grid2, 256, 0, st>>>(z, n, m, scratch, r, r0, rc, w, r, rows_per);
+        } else {
+            z_times_kernel<8><<<(unsigned)wblocks, 256, 0, st>>>(z, n, m, v, r, r0, rc, scratch, r);
+            zt_times_kernel<8><<<grid2, 256, 0, st>>>(z, n, m, scratch, r, r0, rc, w, r, rows_per);
+        }
+        count_launch(2);
+    }
+    return check_launch("cg_matvec");
+}
+
+}  // namespace xb

@@ -1,0 +1,198 @@
+"""Python face of the C ABI: the eight callables of the reference's `xgpr_cuda_rfgen_cpp_ext`
+(gpu_rf_gen/xgpr_cuda_rfgen_cpp_ext.cpp:20-93) with the same names, keyword names and argument
+order, taking torch CUDA tensors instead of CuPy arrays.
+
+Like nanobind's ``.noconvert()`` ndarray arguments, a dtype / rank / device / contiguity mismatch
+raises TypeError before the native call; shape violations raise RuntimeError from the native side.
+Kernels are launched on ``torch.cuda.current_stream()``; nothing synchronises.
+"""
+import numpy as np
+import torch
+
+from . import _native
+from ._native import lib, check
+
+_SFX = {torch.float32: "_f32", torch.float64: "_f64"}
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _dev(t, name, dtypes, ndim):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise TypeError(f"{name}: expected a CUDA torch.Tensor")
+    if t.dtype not in dtypes:
+        raise TypeError(f"{name}: dtype {t.dtype} not accepted (expected one of {dtypes})")
+    if t.dim() != ndim:
+        raise TypeError(f"{name}: expected {ndim} dims, got {t.dim()}")
+    if not t.is_contiguous():
+        raise TypeError(f"{name}: must be C-contiguous")
+    return t
+
+
+def _radem3(t):
+    _dev(t, "radem", (torch.int8,), 3)
+    if t.shape[0] != 3 or t.shape[1] != 1:
+        raise TypeError("radem: expected shape (3, 1, R)")
+    return t
+
+
+def _host_i32(a, name):
+    if isinstance(a, torch.Tensor):
+        if a.is_cuda:
+            raise TypeError(f"{name}: must live on the host (as in the reference API)")
+        a = a.numpy()
+    if not isinstance(a, np.ndarray) or a.dtype != np.int32 or a.ndim != 1 or not a.flags["C_CONTIGUOUS"]:
+        raise TypeError(f"{name}: expected a C-contiguous 1-d host int32 array")
+    return a
+
+
+def _same(a, b, an, bn):
+    if a.dtype != b.dtype:
+        raise TypeError(f"{an} and {bn} must share a dtype")
+
+
+def cudaFastHadamardTransform2D(inputArr):
+    x = _dev(inputArr, "inputArr", _SFX, 2)
+    check(getattr(lib, "xgpr_b200_fht2d" + _SFX[x.dtype])(x.data_ptr(), x.shape[0], x.shape[1], _stream()))
+    return 0
+
+
+def cudaSRHT(inputArr, radem):
+    x = _dev(inputArr, "inputArr", _SFX, 2)
+    r = _dev(radem, "radem", (torch.int8,), 1)
+    check(getattr(lib, "xgpr_b200_srht" + _SFX[x.dtype])(x.data_ptr(), x.shape[0], x.shape[1], r.data_ptr(),
+                                                         r.shape[0], _stream()))
+    return 0
+
+
+def cudaRBFFeatureGen(inputArr, outputArr, radem, chiArr, fitIntercept):
+    x = _dev(inputArr, "inputArr", _SFX, 2)
+    o = _dev(outputArr, "outputArr", (torch.float64,), 2)
+    r = _radem3(radem)
+    c = _dev(chiArr, "chiArr", _SFX, 1)
+    _same(x, c, "inputArr", "chiArr")
+    if o.shape[0] != x.shape[0]:
+        raise RuntimeError("no datapoints")
+    check(getattr(lib, "xgpr_b200_rbf_feature_gen" + _SFX[x.dtype])(
+        x.data_ptr(), x.shape[0], x.shape[1], o.data_ptr(), o.shape[1], r.data_ptr(), r.shape[2],
+        c.data_ptr(), c.shape[0], int(bool(fitIntercept)), _stream()))
+    return 0
+
+
+def cudaRBFGrad(inputArr, outputArr, gradArr, radem, chiArr, sigma, fitIntercept):
+    x = _dev(inputArr, "inputArr", _SFX, 2)
+    o = _dev(outputArr, "outputArr", (torch.float64,), 2)
+    g = _dev(gradArr, "gradArr", (torch.float64,), 3)
+    r = _radem3(radem)
+    c = _dev(chiArr, "chiArr", _SFX, 1)
+    _same(x, c, "inputArr", "chiArr")
+    if o.shape[0] != x.shape[0]:
+        raise RuntimeError("no datapoints")
+    if g.shape[0] != o.shape[0] or g.shape[1] != o.shape[1] or g.shape[2] != 1:
+        raise RuntimeError("Wrong array sizes.")
+    check(getattr(lib, "xgpr_b200_rbf_grad" + _SFX[x.dtype])(
+        x.data_ptr(), x.shape[0], x.shape[1], o.data_ptr(), g.data_ptr(), o.shape[1], r.data_ptr(), r.shape[2],
+        c.data_ptr(), c.shape[0], float(sigma), int(bool(fitIntercept)), _stream()))
+    return 0
+
+
+def cudaMiniARDGrad(inputArr, outputArr, precompWeights, sigmaMap, sigmaVals, gradArr, fitIntercept):
+    x = _dev(inputArr, "inputArr", _SFX, 2)
+    o = _dev(outputArr, "outputArr", (torch.float64,), 2)
+    w = _dev(precompWeights, "precompWeights", _SFX, 2)
+    sm = _dev(sigmaMap, "sigmaMap", (torch.int32,), 1)
+    sv = _dev(sigmaVals, "sigmaVals", (torch.float64,), 1)
+    g = _dev(gradArr, "gradArr", (torch.float64,), 3)
+    _same(x, w, "inputArr", "precompWeights")
+    # gpu_rf_gen/rbf_ops/ard_ops.cu:110-126 == cpu_rf_gen/rbf_ops/ard_ops.cpp:66-82
+    if x.shape[0] == 0 or o.shape[0] != x.shape[0]:
+        raise RuntimeError("no datapoints")
+    if g.shape[0] != o.shape[0] or g.shape[1] != o.shape[1]:
+        raise RuntimeError("Wrong array sizes.")
+    if w.shape[1] != x.shape[1] or o.shape[1] != 2 * w.shape[0] or sm.shape[0] != w.shape[1] \
+            or sv.shape[0] != sm.shape[0]:
+        raise RuntimeError("Wrong array sizes.")
+    check(getattr(lib, "xgpr_b200_ard_grad" + _SFX[x.dtype])(
+        x.data_ptr(), x.shape[0], x.shape[1], o.data_ptr(), w.data_ptr(), w.shape[0], sm.data_ptr(),
+        sv.data_ptr(), g.data_ptr(), g.shape[2], int(bool(fitIntercept)), _stream()))
+    return 0
+
+
+def _conv_common(inputArr, outputArr, radem, chiArr, seqlengths, odtype):
+    x = _dev(inputArr, "inputArr", _SFX, 3)
+    o = _dev(outputArr, "outputArr", (odtype,), 2)
+    r = _radem3(radem)
+    c = _dev(chiArr, "chiArr", _SFX, 1)
+    _same(x, c, "inputArr", "chiArr")
+    s = _host_i32(seqlengths, "seqlengths")
+    if x.shape[0] == 0 or o.shape[0] != x.shape[0]:
+        raise RuntimeError("no datapoints")
+    if s.shape[0] != x.shape[0]:
+        raise RuntimeError("wrong array sizes")
+    return x, o, r, c, s
+
+
+def cudaConv1dMaxpool(inputArr, outputArr, radem, chiArr, seqlengths, convWidth):
+    x, o, r, c, s = _conv_common(inputArr, outputArr, radem, chiArr, seqlengths, torch.float32)
+    check(getattr(lib, "xgpr_b200_conv1d_maxpool" + _SFX[x.dtype])(
+        x.data_ptr(), x.shape[0], x.shape[1], x.shape[2], o.data_ptr(), o.shape[1], r.data_ptr(), r.shape[2],
+        c.data_ptr(), c.shape[0], s.ctypes.data, int(convWidth), _stream()))
+    return 0
+
+
+def cudaConv1dFGen(inputArr, outputArr, radem, chiArr, seqlengths, convWidth, scalingType):
+    x, o, r, c, s = _conv_common(inputArr, outputArr, radem, chiArr, seqlengths, torch.float64)
+    check(getattr(lib, "xgpr_b200_conv1d_fgen" + _SFX[x.dtype])(
+        x.data_ptr(), x.shape[0], x.shape[1], x.shape[2], o.data_ptr(), o.shape[1], r.data_ptr(), r.shape[2],
+        c.data_ptr(), c.shape[0], s.ctypes.data, int(convWidth), int(scalingType), _stream()))
+    return 0
+
+
+def cudaConvGrad(inputArr, outputArr, radem, chiArr, seqlengths, gradArr, sigma, convWidth, scalingType):
+    x, o, r, c, s = _conv_common(inputArr, outputArr, radem, chiArr, seqlengths, torch.float64)
+    g = _dev(gradArr, "gradArr", (torch.float64,), 3)
+    if g.shape[0] != o.shape[0] or g.shape[1] != o.shape[1] or g.shape[2] != 1:
+        raise RuntimeError("wrong array sizes")
+    check(getattr(lib, "xgpr_b200_conv1d_grad" + _SFX[x.dtype])(
+        x.data_ptr(), x.shape[0], x.shape[1], x.shape[2], o.data_ptr(), o.shape[1], r.data_ptr(), r.shape[2],
+        c.data_ptr(), c.shape[0], s.ctypes.data, g.data_ptr(), float(sigma), int(convWidth), int(scalingType),
+        _stream()))
+    return 0
+
+
+# ---- downstream consumers (no counterpart in the reference extension: they replace `@` expressions)
+def zty_accum(z, y, zty):
+    z = _dev(z, "z", (torch.float64,), 2)
+    y = _dev(y, "y", (torch.float64,), 1)
+    zty = _dev(zty, "zty", (torch.float64,), 1)
+    if y.shape[0] != z.shape[0] or zty.shape[0] != z.shape[1]:
+        raise RuntimeError("wrong array sizes")
+    check(lib.xgpr_b200_zty_accum_f64(z.data_ptr(), z.shape[0], z.shape[1], y.data_ptr(), zty.data_ptr(), _stream()))
+
+
+def ztz_accum(z, ztz):
+    z = _dev(z, "z", (torch.float64,), 2)
+    ztz = _dev(ztz, "ztz", (torch.float64,), 2)
+    if ztz.shape[0] != z.shape[1] or ztz.shape[1] != z.shape[1]:
+        raise RuntimeError("wrong array sizes")
+    check(lib.xgpr_b200_ztz_accum_f64(z.data_ptr(), z.shape[0], z.shape[1], ztz.data_ptr(), _stream()))
+
+
+def cg_matvec_accum(z, v, w, scratch=None):
+    z = _dev(z, "z", (torch.float64,), 2)
+    v = _dev(v, "v", (torch.float64,), 2)
+    w = _dev(w, "w", (torch.float64,), 2)
+    if v.shape[0] != z.shape[1] or w.shape != v.shape:
+        raise RuntimeError("wrong array sizes")
+    if scratch is None:
+        scratch = torch.empty((z.shape[0], v.shape[1]), dtype=torch.float64, device=z.device)
+    scratch = _dev(scratch, "scratch", (torch.float64,), 2)
+    if scratch.shape[0] < z.shape[0] or scratch.shape[1] != v.shape[1]:
+        raise RuntimeError("wrong array sizes")
+    check(lib.xgpr_b200_cg_matvec_accum_f64(z.data_ptr(), z.shape[0], z.shape[1], v.data_ptr(), v.shape[1],
+                                            w.data_ptr(), scratch.data_ptr(), _stream()))
+
+
+launch_count = _native.launch_count

@@ -1,0 +1,108 @@
+"""Fixed-vector SORF kernels: RBF, Matern, Cauchy.
+
+Mirrors src/xGPR/kernels/basic_kernels/sorf_kernel_baseclass.py:39-84 (parameter draws),
+:88-101 (device move), :105-125 (transform), :136-162 (gradient); rbf.py:21-41; matern.py:26-59;
+cauchy.py:21-47.  The host draws are bit-identical to the reference's given the same seed
+(checked against tests/golden/l2_*.npz).
+"""
+from math import ceil
+
+import numpy as np
+import torch
+from scipy.stats import chi
+
+from .. import ext
+from .base import KernelBaseclass
+
+RADEM_VALUES = np.asarray([-1, 1], dtype=np.int8)
+
+
+def draw_sorf_params(padded_dims, num_freqs, random_seed, double_precision, rng=None):
+    """radem (3,1,R) int8 from Generator.choice, chi (F) from scipy chi.rvs(df=padded width) -- the
+    exact recipe of sorf_kernel_baseclass.py:71-84 / conv_kernel_baseclass.py:85-99."""
+    if rng is None:
+        rng = np.random.default_rng(random_seed)
+    nblocks = ceil(num_freqs / padded_dims) if padded_dims < num_freqs else 1
+    radem = rng.choice(RADEM_VALUES, size=(3, 1, nblocks * padded_dims), replace=True)
+    chi_arr = chi.rvs(df=padded_dims, size=num_freqs, random_state=random_seed)
+    if not double_precision:
+        chi_arr = chi_arr.astype(np.float32)
+    return radem, chi_arr
+
+
+class SORFKernelBaseclass(KernelBaseclass):
+    def __init__(self, num_rffs, xdim, sine_cosine_kernel=True, random_seed=123, double_precision=False,
+                 kernel_spec_parms={}):
+        super().__init__(num_rffs, xdim, sine_cosine_kernel=sine_cosine_kernel,
+                         double_precision=double_precision, kernel_spec_parms=kernel_spec_parms)
+        if len(xdim) != 2:
+            raise ValueError("The dimensionality of the input is inappropriate for the kernel you have selected.")
+        padded_dims = 2 ** ceil(np.log2(max(xdim[-1], 2)))
+        self.radem_diag, self.chi_arr = draw_sorf_params(padded_dims, self.num_freqs, random_seed, double_precision)
+
+    def kernel_specific_set_device(self, new_device):
+        self._move(("radem_diag", "chi_arr"), new_device)
+
+    def kernel_specific_set_hyperparams(self):
+        return
+
+    def kernel_specific_transform(self, input_x, sequence_length=None):
+        input_x *= self.hyperparams[1]                       # sigma applied in the FHT dtype, before SORF
+        output_x = torch.empty((input_x.shape[0], self.num_rffs), dtype=torch.float64, device=input_x.device)
+        ext.cudaRBFFeatureGen(input_x, output_x, self.radem_diag, self.chi_arr, self.fit_intercept)
+        return output_x
+
+    def kernel_specific_gradient(self, input_x, sequence_length=None):
+        output_x = torch.empty((input_x.shape[0], self.num_rffs), dtype=torch.float64, device=input_x.device)
+        dz_dsigma = torch.empty((input_x.shape[0], self.num_rffs, 1), dtype=torch.float64, device=input_x.device)
+        ext.cudaRBFGrad(input_x, output_x, dz_dsigma, self.radem_diag, self.chi_arr,
+                        float(self.hyperparams[1]), self.fit_intercept)
+        return output_x, dz_dsigma
+
+
+class RBF(SORFKernelBaseclass):
+    """hyperparams: [lambda, sigma] (rbf.py:38-39)."""
+
+    def __init__(self, xdim, num_rffs, random_seed=123, device="cpu", double_precision=False, kernel_spec_parms={}):
+        super().__init__(num_rffs, xdim, sine_cosine_kernel=True, random_seed=random_seed,
+                         double_precision=double_precision, kernel_spec_parms=kernel_spec_parms)
+        self.hyperparams = np.ones((2))
+        self.bounds = np.asarray([[1e-3, 4], [1e-6, 1e2]])
+        self.device = device
+
+
+def matern_rescale_(chi_arr, matern_nu, num_freqs, random_seed):
+    """chi /= sqrt(chisquare(2 nu)/(2 nu)) IN PLACE on the already-cast array (matern.py:50-54)."""
+    rng = np.random.default_rng(random_seed)
+    chi_arr /= np.sqrt(rng.chisquare(2 * matern_nu, size=num_freqs) / (matern_nu * 2))
+
+
+def cauchy_rescale_(chi_arr, num_freqs, random_seed):
+    """chi *= sqrt(Exp(1)) IN PLACE (cauchy.py:39-41)."""
+    rng = np.random.default_rng(random_seed)
+    chi_arr *= np.sqrt(rng.exponential(size=num_freqs))
+
+
+class Matern(SORFKernelBaseclass):
+    def __init__(self, xdim, num_rffs, random_seed=123, device="cpu", double_precision=False, kernel_spec_parms={}):
+        super().__init__(num_rffs, xdim, sine_cosine_kernel=True, random_seed=random_seed,
+                         double_precision=double_precision, kernel_spec_parms=kernel_spec_parms)
+        if "matern_nu" not in kernel_spec_parms:
+            raise ValueError("Tried to initialize a Matern kernel without supplying nu.")
+        self.matern_nu = kernel_spec_parms["matern_nu"]
+        if self.matern_nu < 1 / 2 or self.matern_nu > 5 / 2:
+            raise ValueError("nu must be >= 1/2 and <= 5/2.")
+        matern_rescale_(self.chi_arr, self.matern_nu, self.num_freqs, random_seed)
+        self.hyperparams = np.ones((2))
+        self.bounds = np.asarray([[1e-3, 1e1], [1e-6, 1e2]])
+        self.device = device
+
+
+class Cauchy(SORFKernelBaseclass):
+    def __init__(self, xdim, num_rffs, random_seed=123, device="cpu", double_precision=False, kernel_spec_parms={}):
+        super().__init__(num_rffs, xdim, sine_cosine_kernel=True, random_seed=random_seed,
+                         double_precision=double_precision, kernel_spec_parms=kernel_spec_parms)
+        cauchy_rescale_(self.chi_arr, self.num_freqs, random_seed)
+        self.hyperparams = np.ones((2))
+        self.bounds = np.asarray([[1e-3, 1e1], [1e-6, 1e2]])
+        self.device = device
