@@ -40,7 +40,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--rows", type=int, default=32768, help="rows per step per GPU")
+    ap.add_argument("--rows", type=int, default=262144, help="rows per step per GPU")
     ap.add_argument("--cpu-rows", type=int, default=16384, help="rows per CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -66,13 +66,13 @@ class ClockSampler(threading.Thread):
         super().__init__(daemon=True)
         self.index = index
         self.samples, self.reasons, self.max_mhz = [], set(), None
-        self._stop = threading.Event()
+        self._halt = threading.Event()
 
     def run(self):
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        while not self._stop.is_set():
+        while not self._halt.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits",
                                       "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
@@ -84,10 +84,10 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(nm)
             except Exception:
                 pass
-            self._stop.wait(0.1)
+            self._halt.wait(0.1)
 
     def stop(self):
-        self._stop.set()
+        self._halt.set()
         self.join(timeout=6)
         med = float(np.median(self.samples)) if self.samples else None
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
@@ -240,8 +240,6 @@ def run_b200(args):
     launches = ext.launch_count() - l0
     kern_ms = [a.elapsed_time(b) for a, b in evs]
     dev_ms = evs[0][0].elapsed_time(evs[-1][1])
-    clocks = sampler.stop() if sampler else None
-
     # ---------------- end to end through the plugin API (host input, H2D, D2H of a result row)
     def e2e_step():
         z = kern.transform_x(x_pinned)             # H2D + sigma scale + fused kernel + intercept column
@@ -260,6 +258,7 @@ def run_b200(args):
     torch.cuda.synchronize()
     barrier()
     e2e_ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if sampler else None      # sampled across both timed regions
 
     t = torch.tensor([dev_ms, e2e_ms, float(np.mean(kern_ms))], dtype=torch.float64, device=dev)
     if world > 1:
@@ -276,7 +275,7 @@ def run_b200(args):
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
             try:
-                traffic = json.load(open(tp)).get("rbf_warp_kernel_bytes_per_launch")
+                traffic = json.load(open(tp)).get("rbf_warp_kernel_bytes_per_row") * rows
             except Exception:
                 traffic = None
         line = {

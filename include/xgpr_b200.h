@@ -48,6 +48,15 @@ int xgpr_b200_fht2d_f64(double* x, int64_t n, int64_t p, void* stream);
 int xgpr_b200_srht_f32(float*  x, int64_t n, int64_t p, const int8_t* radem, int64_t radem_len, void* stream);
 int xgpr_b200_srht_f64(double* x, int64_t n, int64_t p, const int8_t* radem, int64_t radem_len, void* stream);
 
+/* ---- input staging: x[i, j] <- T( double(x[i, j]) * (col_weights ? col_weights[j] : 1) * sigma ), in place.
+ * This is the NumPy expression the reference's kernel classes evaluate on the host before calling the
+ * extension: `input_x *= self.hyperparams[1]` (float32 array times a float64 scalar: the product is
+ * formed in double and rounded ONCE, src/xGPR/kernels/basic_kernels/sorf_kernel_baseclass.py:117,
+ * convolution_kernels/conv_kernel_baseclass.py:136) and MiniARD's `x * full_ard_weights[None, :]`
+ * (ARD_kernels/mini_ard.py:191-196).  x (n, d) device; col_weights (d) f64 device or NULL. */
+int xgpr_b200_scale_input_f32(float*  x, int64_t n, int64_t d, const double* col_weights, double sigma, void* stream);
+int xgpr_b200_scale_input_f64(double* x, int64_t n, int64_t d, const double* col_weights, double sigma, void* stream);
+
 /* ---- cudaRBFFeatureGen  (xgpr_cuda_rfgen_cpp_ext.cpp:32-39; gpu_rf_gen/rbf_ops/rbf_ops.cu:261-326)
  * x (n, d); out (n, num_rffs) f64, OVERWRITTEN with interleaved [cos, sin] pairs;
  * radem (3, 1, radem_len) int8; chi (num_freqs); num_rffs == 2 * num_freqs. */

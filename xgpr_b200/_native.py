@@ -21,6 +21,7 @@ _i64, _int, _dbl, _ptr = ctypes.c_int64, ctypes.c_int, ctypes.c_double, ctypes.c
 # name -> argtypes (all return int unless noted); mirrors include/xgpr_b200.h one to one
 SIGNATURES = {
     "xgpr_b200_fht2d": [_ptr, _i64, _i64, _ptr],
+    "xgpr_b200_scale_input": [_ptr, _i64, _i64, _ptr, _dbl, _ptr],
     "xgpr_b200_srht": [_ptr, _i64, _i64, _ptr, _i64, _ptr],
     "xgpr_b200_rbf_feature_gen": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _int, _ptr],
     "xgpr_b200_rbf_grad": [_ptr, _i64, _i64, _ptr, _ptr, _i64, _ptr, _i64, _ptr, _i64, _dbl, _int, _ptr],

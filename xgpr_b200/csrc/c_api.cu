@@ -27,6 +27,8 @@ int check_launch(const char* what) {
 // implemented in the kernel translation units
 template <typename T, bool SRHT>
 int fht_dispatch(T* x, int64_t n, int64_t P, const int8_t* radem, int64_t radem_len, cudaStream_t st);
+template <typename T>
+int scale_input(T* x, int64_t n, int64_t d, const double* w, double sigma, cudaStream_t st);
 template <typename T, bool GRAD>
 int rbf_dispatch(const T* x, int64_t n, int64_t d, double* out, double* grad, int64_t num_rffs,
                  const int8_t* radem, int64_t R, const T* chi, int64_t F, double sigma, int fit_intercept,
@@ -59,6 +61,9 @@ int xgpr_b200_fht2d_f32(float* x, int64_t n, int64_t p, void* s) { return fht_di
 int xgpr_b200_fht2d_f64(double* x, int64_t n, int64_t p, void* s) { return fht_dispatch<double, false>(x, n, p, nullptr, 0, ST(s)); }
 int xgpr_b200_srht_f32(float* x, int64_t n, int64_t p, const int8_t* radem, int64_t rl, void* s) { return fht_dispatch<float, true>(x, n, p, radem, rl, ST(s)); }
 int xgpr_b200_srht_f64(double* x, int64_t n, int64_t p, const int8_t* radem, int64_t rl, void* s) { return fht_dispatch<double, true>(x, n, p, radem, rl, ST(s)); }
+
+int xgpr_b200_scale_input_f32(float* x, int64_t n, int64_t d, const double* w, double sigma, void* s) { return scale_input<float>(x, n, d, w, sigma, ST(s)); }
+int xgpr_b200_scale_input_f64(double* x, int64_t n, int64_t d, const double* w, double sigma, void* s) { return scale_input<double>(x, n, d, w, sigma, ST(s)); }
 
 int xgpr_b200_rbf_feature_gen_f32(const float* x, int64_t n, int64_t d, double* out, int64_t num_rffs, const int8_t* radem,
                                   int64_t rl, const float* chi, int64_t nf, int fi, void* s) {

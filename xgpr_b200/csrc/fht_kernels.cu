@@ -196,6 +196,33 @@ int fht_dispatch(T* x, int64_t n, int64_t P, const int8_t* radem, int64_t radem_
     return check_launch("fht_cross_kernel");
 }
 
+// ------------------------------------------------------------------ input staging (see xgpr_b200.h)
+template <typename T>
+__global__ void __launch_bounds__(256)
+scale_input_kernel(T* __restrict__ x, int64_t total, int64_t d, const double* __restrict__ w, double sigma) {
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (int64_t)gridDim.x * blockDim.x) {
+        double v = (double)x[t];
+        if (w) v = __dmul_rn(v, w[t % d]);
+        else   v = __dmul_rn(v, sigma);
+        x[t] = (T)v;
+    }
+}
+
+template <typename T>
+int scale_input(T* x, int64_t n, int64_t d, const double* w, double sigma, cudaStream_t st) {
+    XB_REQUIRE(n > 0 && d > 0, "no datapoints");
+    XB_REQUIRE(x, "null pointer");
+    const int64_t total = n * d;
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    scale_input_kernel<T><<<(unsigned)blocks, 256, 0, st>>>(x, total, d, w, sigma);
+    count_launch();
+    return check_launch("scale_input_kernel");
+}
+template int scale_input<float>(float*, int64_t, int64_t, const double*, double, cudaStream_t);
+template int scale_input<double>(double*, int64_t, int64_t, const double*, double, cudaStream_t);
+
 template int fht_dispatch<float, false>(float*, int64_t, int64_t, const int8_t*, int64_t, cudaStream_t);
 template int fht_dispatch<float, true>(float*, int64_t, int64_t, const int8_t*, int64_t, cudaStream_t);
 template int fht_dispatch<double, false>(double*, int64_t, int64_t, const int8_t*, int64_t, cudaStream_t);

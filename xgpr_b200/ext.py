@@ -67,6 +67,24 @@ def cudaSRHT(inputArr, radem):
     return 0
 
 
+def scale_input_(x, sigma=1.0, col_weights=None):
+    """In place x <- T(double(x) * sigma) (or * col_weights[j]): the reference's host-side
+    `input_x *= hyperparams[1]` / MiniARD `x * full_ard_weights` with NumPy's rounding (one rounding of
+    the double product), see include/xgpr_b200.h."""
+    if x.dtype not in _SFX or not x.is_cuda or not x.is_contiguous():
+        raise TypeError("x: expected a C-contiguous CUDA float32/float64 tensor")
+    wptr = 0
+    if col_weights is not None:
+        w = _dev(col_weights, "col_weights", (torch.float64,), 1)
+        if w.shape[0] != x.shape[-1]:
+            raise RuntimeError("wrong array sizes")
+        wptr = w.data_ptr()
+    d = x.shape[-1]
+    check(getattr(lib, "xgpr_b200_scale_input" + _SFX[x.dtype])(x.data_ptr(), x.numel() // d, d, wptr,
+                                                                float(sigma), _stream()))
+    return x
+
+
 def cudaRBFFeatureGen(inputArr, outputArr, radem, chiArr, fitIntercept):
     x = _dev(inputArr, "inputArr", _SFX, 2)
     o = _dev(outputArr, "outputArr", (torch.float64,), 2)

@@ -74,11 +74,9 @@ class MiniARD(KernelBaseclass):
 
     def kernel_specific_transform(self, input_x, sequence_length=None):
         # float64 weights x T input -> float64, then back to T (mini_ard.py:191-196)
-        xtrans = input_x * self.full_ard_weights[None, :]
-        if not self.double_precision:
-            xtrans = xtrans.to(torch.float32)
+        xtrans = ext.scale_input_(input_x, col_weights=self.full_ard_weights)
         output_x = torch.empty((input_x.shape[0], self.num_rffs), dtype=torch.float64, device=input_x.device)
-        ext.cudaRBFFeatureGen(xtrans.contiguous(), output_x, self.radem_diag, self.chi_arr, self.fit_intercept)
+        ext.cudaRBFFeatureGen(xtrans, output_x, self.radem_diag, self.chi_arr, self.fit_intercept)
         return output_x
 
     def precompute_weights(self):

@@ -53,7 +53,7 @@ class ConvKernelBaseclass(KernelBaseclass):
 
     def kernel_specific_transform(self, input_x, sequence_length):
         self._check(input_x, sequence_length)
-        input_x *= self.hyperparams[1]
+        ext.scale_input_(input_x, float(self.hyperparams[1]))   # NumPy rounding of `input_x *= sigma`
         xtrans = torch.zeros((input_x.shape[0], self.num_rffs), dtype=torch.float64, device=input_x.device)
         ext.cudaConv1dFGen(input_x, xtrans, self.radem_diag, self.chi_arr, sequence_length,
                            self.conv_width, self.scaling_type)

@@ -47,7 +47,8 @@ class SORFKernelBaseclass(KernelBaseclass):
         return
 
     def kernel_specific_transform(self, input_x, sequence_length=None):
-        input_x *= self.hyperparams[1]                       # sigma applied in the FHT dtype, before SORF
+        # `input_x *= sigma`: NumPy forms float32 * float64-scalar in double and rounds once
+        ext.scale_input_(input_x, float(self.hyperparams[1]))
         output_x = torch.empty((input_x.shape[0], self.num_rffs), dtype=torch.float64, device=input_x.device)
         ext.cudaRBFFeatureGen(input_x, output_x, self.radem_diag, self.chi_arr, self.fit_intercept)
         return output_x

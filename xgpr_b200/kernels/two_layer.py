@@ -70,7 +70,7 @@ class Conv1dTwoLayer(KernelBaseclass):
     def kernel_specific_transform(self, input_x, sequence_length):
         feat = self._first_layer(input_x, sequence_length)
         xtrans = torch.empty((feat.shape[0], self.num_rffs), dtype=torch.float64, device=feat.device)
-        feat *= self.hyperparams[1]
+        ext.scale_input_(feat, float(self.hyperparams[1]))      # NumPy rounding of `featurized_x *= sigma`
         ext.cudaRBFFeatureGen(feat, xtrans, self.radem_diag2, self.chi_arr2, self.fit_intercept)
         return xtrans
 
