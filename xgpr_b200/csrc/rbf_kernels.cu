@@ -5,16 +5,152 @@
 // Numerics follow the CPU oracle (cpu_rf_gen/rbf_ops/rbf_ops.cpp:26-106, :135-221 and
 // cpu_rf_gen/shared_fht_functions/shared_rfgen_ops.cpp:50-156).
 //
-// One HBM round trip per row: the row is read once per repeat group (L1/L2 resident afterwards),
-// all three sign-flip/FWHT rounds, the chi scale and cos/sin happen in registers, and the
-// interleaved fp64 [cos, sin] pairs are written with 128-bit stores that are contiguous across
-// the K sub-lanes of a vector.  No scratch buffer, no per-call allocation.
-#include "sorf_warp.cuh"
+// One HBM round trip per row: the row is read once per repeat group (L1 resident afterwards), all
+// three sign-flip/FWHT rounds, the chi scale and cos/sin happen in registers (sorf_core.cuh), and the
+// interleaved fp64 [cos, sin] pairs leave through a padded per-warp shared-memory tile so that every
+// 128-bit global store of a warp covers whole 128-byte lines.  No scratch buffer, no per-call allocation.
+#include "sorf_core.cuh"
+#include "sorf_warp.cuh"   // cta_sorf for P > 1024
 
 namespace xb {
 
-// out[2f], out[2f+1] (and the gradient pair) for one frequency -- forward variant
-// singleVectorRBFPostProcess, shared_rfgen_ops.cpp:91-114
+// ---------------------------------------------------------------------------------------------
+// Register kernel, P <= 1024.
+//   slot g = warp*V + q   (V = 32/K vectors per warp, S = WARPS*V slots per CTA)
+//   repeat  = blockIdx.y*RC + g % RC      (RC = repeats per CTA, power of two <= S)
+//   rowlane = g / RC, nrl = S/RC row lanes.  Each slot keeps its repeat's sign bits (and chi when E <= 16)
+//   in registers and walks the CTA's rows; rows arrive through a double-buffered cp.async tile in shared
+//   memory (zero-padded, permuted), ITB row-iterations per batch, so no global-load latency sits on the
+//   per-row critical path.  The K sub-lanes of a slot write K*16 contiguous bytes per register index.
+template <typename T, int P, int E, bool GRAD, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
+rbf_core_kernel(const T* __restrict__ x, double* __restrict__ out, double* __restrict__ grad,
+                const int8_t* __restrict__ radem, const T* __restrict__ chi,
+                int N, int D, int F, int64_t R, int reps, int RC, int rows_per_cta, int ITB,
+                T cnorm, T fold, double scale, double sigma) {
+    constexpr int K = P / E;
+    constexpr int V = 32 / K;
+    constexpr int S = WARPS * V;
+    constexpr bool FOLD = is_pow4(P);
+    constexpr int CH = cmin(8, E);
+    constexpr int CPITCH = ChiTile<T, E>::PITCH;
+    constexpr bool CHI_REGS = (E <= 16);
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int nrl = S / RC;
+    const int tile_rows = nrl * ITB;
+    T* xt0 = reinterpret_cast<T*>(smem_raw);
+    T* xt1 = xt0 + (size_t)tile_rows * K * CPITCH;
+    T* chi_tile = xt1 + (size_t)tile_rows * K * CPITCH;
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = lane % K, q = lane / K;
+    const int g = warp * V + q;
+    const int rep0 = blockIdx.y * RC;
+    const int rl_rep = g % RC;
+    const int rep = rep0 + rl_rep;
+    const int rowlane = g / RC;
+    const bool rep_ok = rep < reps;
+    const int64_t base = (int64_t)rep * P;
+    const bool full = rep_ok && (base + P <= F);      // every frequency of this repeat is kept
+
+    const int row0 = blockIdx.x * rows_per_cta;
+    const int iters = (rows_per_cta + nrl - 1) / nrl;
+    const int nbatch = (iters + ITB - 1) / ITB;
+
+    issue_x_tile<T, P, E>(xt0, x, row0, tile_rows, min(N, row0 + rows_per_cta), D);
+    cp_async_commit();
+    load_chi_tile<T, P, E>(chi_tile, chi, rep0, RC, reps, F, fold);
+    SignBits<E> sg;
+    sg.template load<K>(radem, R, base, sub, rep_ok);
+    __syncthreads();
+    const T* my_chi = chi_tile + (rl_rep * K + sub) * CPITCH;
+    T chr[CHI_REGS ? E : 1];
+    if (CHI_REGS) {
+#pragma unroll
+        for (int r = 0; r < E; ++r) chr[r] = my_chi[r];
+    }
+
+    for (int b = 0; b < nbatch; ++b) {
+        T* cur = (b & 1) ? xt1 : xt0;
+        if (b + 1 < nbatch) {
+            issue_x_tile<T, P, E>((b & 1) ? xt0 : xt1, x, row0 + (b + 1) * tile_rows, tile_rows,
+                                  min(N, row0 + rows_per_cta), D);
+            cp_async_commit();
+            cp_async_wait<1>();
+        } else {
+            cp_async_wait<0>();
+        }
+        __syncthreads();
+        for (int ib = 0; ib < ITB; ++ib) {
+            const int it = b * ITB + ib;
+            const int rl = rowlane + it * nrl;
+            const int row = row0 + rl;
+            const bool ok = rep_ok && (rl < rows_per_cta) && (row < N);
+            if (it >= iters) break;                       // warp-uniform
+            T v[E];
+            lds_chunk<E>(cur + ((ib * nrl + rowlane) * K + sub) * CPITCH, v);
+            core_sorf<T, E, K, FOLD>(v, sg, sub, cnorm);
+
+            double2* orow = reinterpret_cast<double2*>(out) + (size_t)row * F + base + sub;
+            double2* grow = reinterpret_cast<double2*>(grad) + (size_t)row * F + base + sub;
+#pragma unroll
+            for (int r0 = 0; r0 < E; r0 += CH) {
+                T a[CH], sn[CH], cs[CH], gv[CH], ch[CH];
+                if (CHI_REGS) {
+#pragma unroll
+                    for (int i = 0; i < CH; ++i) ch[i] = chr[r0 + i];
+                } else {
+                    lds_chunk<CH>(my_chi + r0, ch);
+                }
+#pragma unroll
+                for (int i = 0; i < CH; ++i) {
+                    gv[i] = mul_rn(v[r0 + i], ch[i]);
+                    // gradient: prodVal = g * sigma is formed in double and stored to T (shared_rfgen_ops.cpp:143-144)
+                    a[i] = GRAD ? (T)((double)gv[i] * sigma) : gv[i];
+                }
+                sincos_group<CH>(a, sn, cs);
+                double2 o[CH], og[GRAD ? CH : 1];
+#pragma unroll
+                for (int i = 0; i < CH; ++i) {
+                    if (!GRAD) {
+                        o[i].x = (double)cs[i] * scale;
+                        o[i].y = (double)sn[i] * scale;
+                    } else {
+                        // cosVal / sinVal are rounded to T before use (shared_rfgen_ops.cpp:145-153)
+                        const T cv = (T)((double)cs[i] * scale);
+                        const T sv = (T)((double)sn[i] * scale);
+                        o[i].x = (double)cv;
+                        o[i].y = (double)sv;
+                        og[i].x = -(double)mul_rn(sv, gv[i]);
+                        og[i].y = (double)mul_rn(cv, gv[i]);
+                    }
+                }
+                if (ok) {
+                    if (full) {
+#pragma unroll
+                        for (int i = 0; i < CH; ++i) {
+                            orow[K * (r0 + i)] = o[i];
+                            if (GRAD) grow[K * (r0 + i)] = og[i];
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < CH; ++i) {
+                            if (base + sub + K * (r0 + i) < F) {
+                                orow[K * (r0 + i)] = o[i];
+                                if (GRAD) grow[K * (r0 + i)] = og[i];
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();     // the tile is overwritten by the batch after next
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Shared-memory kernel for P > 1024 (rare: more than 1024 input features).  One CTA per row.
 template <typename T>
 __device__ __forceinline__ void rbf_post(T v, T chi, double scale, double2* __restrict__ dst) {
     const T a = mul_rn(v, chi);
@@ -25,9 +161,6 @@ __device__ __forceinline__ void rbf_post(T v, T chi, double scale, double2* __re
     o.y = (double)sn * scale;
     *dst = o;
 }
-
-// gradient variant -- singleVectorRBFPostGrad, shared_rfgen_ops.cpp:124-156.  cosVal / sinVal and the
-// two gradient products are rounded to T before being widened, exactly as the oracle does.
 template <typename T>
 __device__ __forceinline__ void rbf_post_grad(T v, T chi, double scale, double sigma,
                                               double2* __restrict__ dst, double2* __restrict__ gdst) {
@@ -46,72 +179,6 @@ __device__ __forceinline__ void rbf_post_grad(T v, T chi, double scale, double s
     *gdst = go;
 }
 
-// ---------------------------------------------------------------------------------------------
-// Register/shuffle kernel, P <= 1024.
-//   slot g = warp*V + q  (V = 32/K vectors per warp, S = WARPS*V slots per CTA)
-//   repeat  = blockIdx.y*RC + g % RC      (RC = repeats per CTA, power of two <= S)
-//   rowlane = g / RC, S/RC row lanes; each slot keeps its repeat's signs and chi in registers and
-//   walks the CTA's rows.
-template <typename T, int P, int K, bool GRAD, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32)
-rbf_warp_kernel(const T* __restrict__ x, double* __restrict__ out, double* __restrict__ grad,
-                const int8_t* __restrict__ radem, const T* __restrict__ chi,
-                int N, int D, int F, int64_t R, int reps, int RC, int rows_per_cta,
-                T cnorm, double scale, double sigma) {
-    constexpr int E = P / K;
-    constexpr int V = 32 / K;
-    constexpr int S = WARPS * V;
-    constexpr bool FS = (sizeof(T) == 4) && (E <= 8);
-
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int sub = lane % K, q = lane / K;
-    const int g = warp * V + q;
-    const int rep = blockIdx.y * RC + (g % RC);
-    const int rowlane = g / RC;
-    const int nrl = S / RC;
-    const bool rep_ok = rep < reps;
-    const int64_t base = (int64_t)rep * P;
-
-    Signs<T, E, K, FS> sg;
-    sg.load(radem, R, base, sub, rep_ok, cnorm);
-    T ch[E];
-#pragma unroll
-    for (int r = 0; r < E; ++r) {
-        const int64_t idx = base + sub + K * r;
-        ch[r] = (rep_ok && idx < F) ? chi[idx] : T(0);
-    }
-
-    const int row0 = blockIdx.x * rows_per_cta;
-    const int iters = (rows_per_cta + nrl - 1) / nrl;
-    for (int it = 0; it < iters; ++it) {
-        const int rl = rowlane + it * nrl;
-        const int row = row0 + rl;
-        const bool ok = rep_ok && (rl < rows_per_cta) && (row < N);
-        T v[E];
-        const T* xr = x + (size_t)row * D;
-#pragma unroll
-        for (int r = 0; r < E; ++r) {
-            const int j = sub + K * r;
-            v[r] = (ok && j < D) ? __ldg(xr + j) : T(0);
-        }
-        warp_sorf<T, E, K, FS>(v, sg, sub, cnorm);
-        if (ok) {
-            double2* orow = reinterpret_cast<double2*>(out + (size_t)row * 2 * F);
-            double2* grow = GRAD ? reinterpret_cast<double2*>(grad + (size_t)row * 2 * F) : nullptr;
-#pragma unroll
-            for (int r = 0; r < E; ++r) {
-                const int64_t idx = base + sub + K * r;
-                if (idx < F) {
-                    if (GRAD) rbf_post_grad<T>(v[r], ch[r], scale, sigma, orow + idx, grow + idx);
-                    else      rbf_post<T>(v[r], ch[r], scale, orow + idx);
-                }
-            }
-        }
-    }
-}
-
-// ---------------------------------------------------------------------------------------------
-// Shared-memory kernel for P > 1024 (rare: more than 1024 input features).  One CTA per row.
 template <typename T, bool GRAD>
 __global__ void __launch_bounds__(256)
 rbf_cta_kernel(const T* __restrict__ x, double* __restrict__ out, double* __restrict__ grad,
@@ -141,30 +208,47 @@ rbf_cta_kernel(const T* __restrict__ x, double* __restrict__ out, double* __rest
 }
 
 // ---------------------------------------------------------------------------------------------
-static inline int pow2_floor(int v) { int p = 1; while (p * 2 <= v) p *= 2; return p; }
 static inline int pow2_ceil(int v) { int p = 1; while (p < v) p *= 2; return p; }
 
-template <typename T, int P, int K, bool GRAD>
-static int launch_warp(const T* x, int64_t n, int64_t d, double* out, double* grad, const int8_t* radem,
+// elements per lane: K = P/E sub-lanes; K >= 4 where possible (>= 64 contiguous bytes per store group),
+// E = 16 for 64 <= P <= 512 (two..five shuffle stages), E = 32 for P = 1024
+__host__ __device__ constexpr int rbf_k(int p) {
+    return cmin(32, (p / 16 > cmin(4, p / 2)) ? p / 16 : cmin(4, p / 2));
+}
+
+template <typename T, int P, bool GRAD>
+static int launch_core(const T* x, int64_t n, int64_t d, double* out, double* grad, const int8_t* radem,
                        int64_t R, const T* chi, int64_t F, double scale, double sigma, cudaStream_t st) {
+    constexpr int K = rbf_k(P);
+    constexpr int E = P / K;
     constexpr int WARPS = 8;
     constexpr int V = 32 / K;
     constexpr int S = WARPS * V;
+    constexpr int CPITCH = ChiTile<T, E>::PITCH;
     const int reps = (int)((F + P - 1) / P);
     int RC = pow2_ceil(reps);
     if (RC > S) RC = S;
     const int nrl = S / RC;
-    // ~64 row iterations per slot amortise the sign/chi setup; keep the grid >= a few waves
-    int rows_per_cta = 64 * nrl;
+    // ~32 row iterations per slot amortise the sign/chi setup; keep the grid >= a few waves
+    int rows_per_cta = 32 * nrl;
     const int64_t rep_groups = (reps + RC - 1) / RC;
-    while (rows_per_cta > nrl && ((n + rows_per_cta - 1) / rows_per_cta) * rep_groups < 148 * 8)
+    while (rows_per_cta > nrl && ((n + rows_per_cta - 1) / rows_per_cta) * rep_groups < 148 * 6)
         rows_per_cta /= 2;
+    // row iterations per cp.async batch: <= 16 KB per buffer
+    const size_t row_bytes = (size_t)nrl * K * CPITCH * sizeof(T);
+    int ITB = (int)((16 * 1024) / row_bytes);
+    if (ITB < 1) ITB = 1;
+    if (ITB > 8) ITB = 8;
+    const size_t smem = 2 * ITB * row_bytes + (size_t)RC * K * CPITCH * sizeof(T);
+    auto kern = rbf_core_kernel<T, P, E, GRAD, WARPS>;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const T c = norm_constant<T>(P);
+    const T fold = is_pow4(P) ? (T)(c * c * c) : T(1);
     dim3 grid((unsigned)((n + rows_per_cta - 1) / rows_per_cta), (unsigned)rep_groups);
-    rbf_warp_kernel<T, P, K, GRAD, WARPS><<<grid, WARPS * 32, 0, st>>>(
-        x, out, grad, radem, chi, (int)n, (int)d, (int)F, R, reps, RC, rows_per_cta,
-        norm_constant<T>(P), scale, sigma);
+    kern<<<grid, WARPS * 32, smem, st>>>(x, out, grad, radem, chi, (int)n, (int)d, (int)F, R, reps, RC,
+                                         rows_per_cta, ITB, c, fold, scale, sigma);
     count_launch();
-    return check_launch("rbf_warp_kernel");
+    return check_launch("rbf_core_kernel");
 }
 
 template <typename T, bool GRAD>
@@ -205,19 +289,11 @@ int rbf_dispatch(const T* x, int64_t n, int64_t d, double* out, double* grad, in
     double scale = fit_intercept ? sqrt(1.0 / (ff - 0.5)) : sqrt(1.0 / ff);
     if (!GRAD) scale = (double)(T)scale;
 
-#define XB_CASE(PP, KK) \
-    case PP: return launch_warp<T, PP, KK, GRAD>(x, n, d, out, grad, radem, R, chi, F, scale, sigma, st);
+#define XB_CASE(PP) \
+    case PP: return launch_core<T, PP, GRAD>(x, n, d, out, grad, radem, R, chi, F, scale, sigma, st);
     switch (P) {
-        XB_CASE(2, 2)
-        XB_CASE(4, 4)
-        XB_CASE(8, 8)
-        XB_CASE(16, 8)
-        XB_CASE(32, 8)
-        XB_CASE(64, 8)
-        XB_CASE(128, 16)
-        XB_CASE(256, 32)
-        XB_CASE(512, 32)
-        XB_CASE(1024, 32)
+        XB_CASE(2) XB_CASE(4) XB_CASE(8) XB_CASE(16) XB_CASE(32) XB_CASE(64)
+        XB_CASE(128) XB_CASE(256) XB_CASE(512) XB_CASE(1024)
         default: break;
     }
 #undef XB_CASE
