@@ -9,7 +9,8 @@
 // slot slides over the sequence's windows, pools in fp64 (sum) or fp32 (max) registers in the same
 // window order as the oracle, and touches the output row exactly once -- instead of the
 // reference's global read-modify-write per window per repeat and its N*(M-w+1)*P scratch buffer.
-#include "sorf_warp.cuh"
+#include "sorf_core.cuh"
+#include "sorf_warp.cuh"   // cta_sorf for P > 1024
 
 #include <mutex>
 #include <unordered_map>
@@ -25,23 +26,35 @@ __device__ __forceinline__ double conv_row_scale(double base, int nk, int scalin
     return base;
 }
 
-template <typename T, int P, int K, int MODE, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32)
-conv_warp_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __restrict__ grad,
+// Register kernel, P <= 1024 (sorf_core.cuh).  Slot g = warp*V + q owns (sequence rowlane = g / RC,
+// repeat = blockIdx.y*RC + g % RC).  SMEMX: the CTA's sequences are first copied (cp.async) into shared
+// memory, so every overlapping window is served on-chip and global memory sees each input element once
+// per repeat group.
+template <typename T, int P, int E, int MODE, int WARPS, bool SMEMX>
+__global__ void __launch_bounds__(WARPS * 32, (E <= 16 && sizeof(T) == 4 && MODE != CONV_GRAD) ? 2 : 1)
+conv_core_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __restrict__ grad,
                  const int8_t* __restrict__ radem, const T* __restrict__ chi,
                  const int32_t* __restrict__ seqlen, int N, int M, int C, int F, int64_t R,
-                 int reps, int RC, int conv_width, int scaling_type, T cnorm, double base_scale,
-                 double sigma) {
-    constexpr int E = P / K;
+                 int reps, int RC, int conv_width, int scaling_type, T cnorm, T fold, double base_scale,
+                 double sigma, int tile_elems) {
+    constexpr int K = P / E;
     constexpr int V = 32 / K;
     constexpr int S = WARPS * V;
-    constexpr bool FS = (sizeof(T) == 4) && (E <= 8);
-    constexpr int NACC = (MODE == CONV_GRAD) ? 4 : 2;
+    constexpr bool FOLD = is_pow4(P);
+    constexpr int CH = cmin(8, E);
+    constexpr int CPITCH = ChiTile<T, E>::PITCH;
+    constexpr int NACC = (MODE == CONV_GRAD) ? 4 : ((MODE == CONV_FGEN) ? 2 : 0);
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T* chi_tile = reinterpret_cast<T*>(smem_raw);
+    T* xtile = chi_tile + (size_t)RC * K * CPITCH;
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int sub = lane % K, q = lane / K;
     const int g = warp * V + q;
-    const int rep = blockIdx.y * RC + (g % RC);
+    const int rep0 = blockIdx.y * RC;
+    const int rl_rep = g % RC;
+    const int rep = rep0 + rl_rep;
     const int rowlane = g / RC;
     const int nrl = S / RC;
     const int row = blockIdx.x * nrl + rowlane;
@@ -49,14 +62,32 @@ conv_warp_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __re
     const int64_t base = (int64_t)rep * P;
     const int wlen = conv_width * C;
 
-    Signs<T, E, K, FS> sg;
-    sg.load(radem, R, base, sub, ok, cnorm);
-    T ch[E];
-#pragma unroll
-    for (int r = 0; r < E; ++r) {
-        const int64_t idx = base + sub + K * r;
-        ch[r] = (ok && idx < F) ? chi[idx] : T(0);
+    if (SMEMX) {
+        // sequences of this CTA -> shared memory (only the seqlen[row] * C leading elements are needed)
+        for (int rl = 0; rl < nrl; ++rl) {
+            const int rw = blockIdx.x * nrl + rl;
+            if (rw >= N) break;
+            const int cnt = min(seqlen[rw] * C, tile_elems);
+            const T* src = x + (size_t)rw * M * C;
+            T* dst = xtile + (size_t)rl * tile_elems;
+            for (int t = threadIdx.x; t < cnt; t += blockDim.x) cp_async_elem<T>(dst + t, src + t, true);
+        }
+        cp_async_commit();
     }
+    load_chi_tile<T, P, E>(chi_tile, chi, rep0, RC, reps, F, fold);
+    SignBits<E> sg;
+    sg.template load<K>(radem, R, base, sub, ok);
+    if (SMEMX) cp_async_wait<0>();
+    __syncthreads();
+    const T* my_chi = chi_tile + (rl_rep * K + sub) * CPITCH;
+    T chr[E];
+#pragma unroll
+    for (int r = 0; r < E; ++r) chr[r] = my_chi[r];
+
+    // bit r set <=> element sub + K*r lies inside the window (the rest of the padded vector is zero)
+    uint32_t vmask = 0;
+#pragma unroll
+    for (int r = 0; r < E; ++r) vmask |= (sub + K * r < wlen ? 1u : 0u) << r;
 
     const int nk = ok ? (seqlen[row] - conv_width + 1) : 0;
     int nk_max = nk;
@@ -64,50 +95,61 @@ conv_warp_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __re
     for (int o = 16; o > 0; o >>= 1) nk_max = max(nk_max, __shfl_xor_sync(0xffffffffu, nk_max, o));
     const double scale = conv_row_scale(base_scale, nk > 0 ? nk : 1, scaling_type);
 
-    double acc[E][NACC];
-    float  mx[E];
+    double acc[E][NACC > 0 ? NACC : 1];
+    float  mx[MODE == CONV_MAXPOOL ? E : 1];
 #pragma unroll
     for (int r = 0; r < E; ++r) {
-        mx[r] = 0.f;
+        if (MODE == CONV_MAXPOOL) mx[r] = 0.f;
 #pragma unroll
         for (int a = 0; a < NACC; ++a) acc[r][a] = 0.0;
     }
 
-    const T* xrow = x + (size_t)row * M * C;
+    const T* xrow = SMEMX ? (xtile + (size_t)rowlane * tile_elems + sub) : (x + (size_t)row * M * C + sub);
     for (int j = 0; j < nk_max; ++j) {
         const bool act = j < nk;
         const T* win = xrow + (size_t)j * C;
+        uint32_t vm = act ? vmask : 0u;
+        asm volatile("" : "+r"(vm));          // keep the per-element predicates out of loop-invariant hoisting
         T v[E];
 #pragma unroll
         for (int r = 0; r < E; ++r) {
-            const int e = sub + K * r;
-            v[r] = (act && e < wlen) ? __ldg(win + e) : T(0);
+            v[r] = T(0);
+            if ((vm >> r) & 1u) v[r] = SMEMX ? win[K * r] : __ldg(win + K * r);
         }
-        warp_sorf<T, E, K, FS>(v, sg, sub, cnorm);
-        if (act) {
+        core_sorf<T, E, K, FOLD>(v, sg, sub, cnorm);
+        if (!act) continue;                   // shuffles are done; nothing below is warp-collective
 #pragma unroll
-            for (int r = 0; r < E; ++r) {
-                if (MODE == CONV_MAXPOOL) {
+        for (int r0 = 0; r0 < E; r0 += CH) {
+            if (MODE == CONV_MAXPOOL) {
+#pragma unroll
+                for (int i = 0; i < CH; ++i) {
                     // conv1d_operations.cpp:161-167: float prodVal = x * chi; out = max(out, prodVal)
-                    const float pv = (float)mul_rn(v[r], ch[r]);
-                    mx[r] = fmaxf(mx[r], pv);
-                } else if (MODE == CONV_FGEN) {
-                    const T a = mul_rn(v[r], ch[r]);
-                    T sn, cs;
-                    sincos_t(a, &sn, &cs);
-                    acc[r][0] = __dadd_rn(acc[r][0], __dmul_rn((double)cs, scale));
-                    acc[r][1] = __dadd_rn(acc[r][1], __dmul_rn((double)sn, scale));
-                } else {
-                    const T gv = mul_rn(v[r], ch[r]);
-                    const T p = (T)((double)gv * sigma);
-                    T sn, cs;
-                    sincos_t(p, &sn, &cs);
-                    const T cv = (T)((double)cs * scale);
-                    const T sv = (T)((double)sn * scale);
-                    acc[r][0] = __dadd_rn(acc[r][0], (double)cv);
-                    acc[r][1] = __dadd_rn(acc[r][1], (double)sv);
-                    acc[r][2] = __dsub_rn(acc[r][2], (double)mul_rn(sv, gv));
-                    acc[r][3] = __dadd_rn(acc[r][3], (double)mul_rn(cv, gv));
+                    const float pv = (float)mul_rn(v[r0 + i], chr[r0 + i]);
+                    mx[r0 + i] = fmaxf(mx[r0 + i], pv);
+                }
+            } else {
+                T a[CH], sn[CH], cs[CH], gv[CH];
+#pragma unroll
+                for (int i = 0; i < CH; ++i) {
+                    gv[i] = mul_rn(v[r0 + i], chr[r0 + i]);
+                    a[i] = (MODE == CONV_GRAD) ? (T)((double)gv[i] * sigma) : gv[i];
+                }
+                sincos_group<CH>(a, sn, cs);
+#pragma unroll
+                for (int i = 0; i < CH; ++i) {
+                    if (MODE == CONV_FGEN) {
+                        // sum_j double(cos_j) * scale: the scale is applied once after the window loop
+                        // (differs from the oracle's per-window multiply by <= 1 ulp of fp64)
+                        acc[r0 + i][0] = __dadd_rn(acc[r0 + i][0], (double)cs[i]);
+                        acc[r0 + i][1] = __dadd_rn(acc[r0 + i][1], (double)sn[i]);
+                    } else {
+                        const T cv = (T)((double)cs[i] * scale);
+                        const T sv = (T)((double)sn[i] * scale);
+                        acc[r0 + i][0] = __dadd_rn(acc[r0 + i][0], (double)cv);
+                        acc[r0 + i][1] = __dadd_rn(acc[r0 + i][1], (double)sv);
+                        acc[r0 + i][2] = __dsub_rn(acc[r0 + i][2], (double)mul_rn(sv, gv[i]));
+                        acc[r0 + i][3] = __dadd_rn(acc[r0 + i][3], (double)mul_rn(cv, gv[i]));
+                    }
                 }
             }
         }
@@ -129,8 +171,13 @@ conv_warp_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __re
             const int64_t idx = base + sub + K * r;
             if (idx < F) {
                 double2 o = orow[idx];          // `+=` semantics of the reference API
-                o.x += acc[r][0];
-                o.y += acc[r][1];
+                if (MODE == CONV_FGEN) {
+                    o.x += acc[r][0] * scale;
+                    o.y += acc[r][1] * scale;
+                } else {
+                    o.x += acc[r][0];
+                    o.y += acc[r][1];
+                }
                 orow[idx] = o;
                 if (MODE == CONV_GRAD) {
                     double2 go = grow[idx];
@@ -233,23 +280,53 @@ static int stage_seqlen(const int32_t* host, int64_t n, cudaStream_t st, const i
 
 static inline int pow2_ceil(int v) { int p = 1; while (p < v) p *= 2; return p; }
 
-template <typename T, int P, int K, int MODE>
-static int launch_conv_warp(const T* x, int64_t n, int64_t m, int64_t c, void* out, double* grad,
+// elements per lane for the pooled kernels: the fp64 accumulators cost 4 (8 for the gradient) registers
+// per element, so E = 16 (8 for double / gradient) and K = P/E sub-lanes
+template <typename T, int MODE> __host__ __device__ constexpr int conv_e(int p) {
+    return cmin(p, (sizeof(T) == 4 && MODE != CONV_GRAD) ? 16 : 8) < p / 32 ? p / 32
+         : cmin(p, (sizeof(T) == 4 && MODE != CONV_GRAD) ? 16 : 8);
+}
+
+template <typename T, int P, int MODE>
+static int launch_conv_core(const T* x, int64_t n, int64_t m, int64_t c, void* out, double* grad,
                             const int8_t* radem, int64_t R, const T* chi, int64_t F, const int32_t* seq_dev,
-                            int conv_width, int scaling_type, double base_scale, double sigma, cudaStream_t st) {
-    constexpr int WARPS = (MODE == CONV_GRAD) ? 4 : 8;
+                            int max_seqlen, int conv_width, int scaling_type, double base_scale, double sigma,
+                            cudaStream_t st) {
+    constexpr int E = conv_e<T, MODE>(P);
+    constexpr int K = P / E;
+    constexpr int WARPS = 8;
     constexpr int V = 32 / K;
     constexpr int S = WARPS * V;
+    constexpr int CPITCH = ChiTile<T, E>::PITCH;
     const int reps = (int)((F + P - 1) / P);
     int RC = pow2_ceil(reps);
     if (RC > S) RC = S;
     const int nrl = S / RC;
+    const T cn = norm_constant<T>(P);
+    const T fold = is_pow4(P) ? (T)(cn * cn * cn) : T(1);
+    const size_t chi_bytes = (size_t)RC * K * CPITCH * sizeof(T);
+    // sequence tile: the longest sequence of the batch, rounded up to 16 bytes
+    int tile_elems = max_seqlen * (int)c;
+    tile_elems = (tile_elems + 3) & ~3;
+    const size_t x_bytes = (size_t)nrl * tile_elems * sizeof(T);
     dim3 grid((unsigned)((n + nrl - 1) / nrl), (unsigned)((reps + RC - 1) / RC));
-    conv_warp_kernel<T, P, K, MODE, WARPS><<<grid, WARPS * 32, 0, st>>>(
-        x, out, grad, radem, chi, seq_dev, (int)n, (int)m, (int)c, (int)F, R, reps, RC, conv_width,
-        scaling_type, norm_constant<T>(P), base_scale, sigma);
+    if (chi_bytes + x_bytes <= 100 * 1024) {
+        const size_t smem = chi_bytes + x_bytes;
+        auto kern = conv_core_kernel<T, P, E, MODE, WARPS, true>;
+        if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        kern<<<grid, WARPS * 32, smem, st>>>(x, out, grad, radem, chi, seq_dev, (int)n, (int)m, (int)c, (int)F, R,
+                                             reps, RC, conv_width, scaling_type, cn, fold, base_scale, sigma,
+                                             tile_elems);
+    } else {
+        auto kern = conv_core_kernel<T, P, E, MODE, WARPS, false>;
+        if (chi_bytes > 48 * 1024)
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)chi_bytes);
+        kern<<<grid, WARPS * 32, chi_bytes, st>>>(x, out, grad, radem, chi, seq_dev, (int)n, (int)m, (int)c, (int)F,
+                                                  R, reps, RC, conv_width, scaling_type, cn, fold, base_scale,
+                                                  sigma, 0);
+    }
     count_launch();
-    return check_launch("conv_warp_kernel");
+    return check_launch("conv_core_kernel");
 }
 
 template <typename T, int MODE>
@@ -282,20 +359,12 @@ int conv_dispatch(const T* x, int64_t n, int64_t m, int64_t c, void* out, int64_
     if (rc != XGPR_B200_OK) return rc;
     const double base_scale = sqrt(1.0 / (double)F);   // rbf_convolution.cpp:40
 
-#define XB_CASE(PP, KK)                                                                                   \
-    case PP: return launch_conv_warp<T, PP, KK, MODE>(x, n, m, c, out, grad, radem, R, chi, F, seq_dev,   \
-                                                      conv_width, scaling_type, base_scale, sigma, st);
+#define XB_CASE(PP)                                                                                        \
+    case PP: return launch_conv_core<T, PP, MODE>(x, n, m, c, out, grad, radem, R, chi, F, seq_dev, (int)mxl, \
+                                                  conv_width, scaling_type, base_scale, sigma, st);
     switch (P) {
-        XB_CASE(2, 2)
-        XB_CASE(4, 4)
-        XB_CASE(8, 8)
-        XB_CASE(16, 8)
-        XB_CASE(32, 8)
-        XB_CASE(64, 8)
-        XB_CASE(128, 16)
-        XB_CASE(256, 32)
-        XB_CASE(512, 32)
-        XB_CASE(1024, 32)
+        XB_CASE(2) XB_CASE(4) XB_CASE(8) XB_CASE(16) XB_CASE(32) XB_CASE(64)
+        XB_CASE(128) XB_CASE(256) XB_CASE(512) XB_CASE(1024)
         default: break;
     }
 #undef XB_CASE
