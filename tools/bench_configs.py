@@ -31,6 +31,9 @@ def timeit(fn, reps=5, warm=2):
     return best
 
 
+ONLY = os.environ.get("XB_CASE")          # substring filter on the case name (for ncu runs)
+
+
 def report(name, rows, ms, bytes_per_row=None, flops=None, extra=None):
     d = {"case": name, "rows": rows, "ms": round(ms, 4), "rows_per_s": rows / (ms * 1e-3)}
     if bytes_per_row:
@@ -43,6 +46,8 @@ def report(name, rows, ms, bytes_per_row=None, flops=None, extra=None):
 
 
 def rbf_case(name, n, d, m, grad=False):
+    if ONLY and ONLY not in name:
+        return
     k = RBF((n, d), m, device="cuda")
     x = torch.randn((n, d), device=dev, dtype=torch.float32) * (0.5 / np.sqrt(d))
     out = torch.empty((n, m), dtype=torch.float64, device=dev)
@@ -56,6 +61,8 @@ def rbf_case(name, n, d, m, grad=False):
 
 
 def conv_case(name, cls, n, mlen, c, w, m, seq_lo, seq_hi, onehot=False, grad=False):
+    if ONLY and ONLY not in name:
+        return
     parms = {"conv_width": w} if cls is Conv1dRBF else {}
     k = cls((n, mlen, c), m, device="cuda", kernel_spec_parms=parms)
     rng = np.random.default_rng(123)
