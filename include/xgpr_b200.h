@@ -123,6 +123,9 @@ int xgpr_b200_conv1d_grad_f64(const double* x, int64_t n, int64_t m, int64_t c, 
 int xgpr_b200_zty_accum_f64(const double* z, int64_t n, int64_t m, const double* y, double* zty, void* stream);
 /* ztz (m, m) += Z^T Z (full symmetric matrix written) */
 int xgpr_b200_ztz_accum_f64(const double* z, int64_t n, int64_t m, double* ztz, void* stream);
+/* acc (r, m) += A^T Z ;  A (n, r) row-major: the Nystrom sketch accumulation
+ * `acc_results += compressor.transform_x(xdata).T @ xdata` (src/xGPR/preconditioners/rand_nys_constructors.py:119) */
+int xgpr_b200_atb_accum_f64(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc, void* stream);
 /* w (m, r) += Z^T (Z v) ;  v (m, r) row-major; scratch (n, r) f64 device workspace */
 int xgpr_b200_cg_matvec_accum_f64(const double* z, int64_t n, int64_t m, const double* v, int64_t r,
                                   double* w, double* scratch, void* stream);

@@ -1,0 +1,92 @@
+"""GPU parity of the downstream path: xgpr_b200/fitting.py with the CUDA
+kernels and the C-ABI consumers of Z against fixtures produced by the REFERENCE's own toolkits on its CPU path
+(tests/golden/make_golden_fits.py).
+
+Tolerances: float64 FHT -> 1e-6 on fitted weights, variance matrix and predictions (north_star).  float32 FHT: the
+features agree to ~5e-7 of scale, and the solve amplifies that by the conditioning of Z^T Z + lambda^2 I, so the
+end-to-end float32 bound is looser and is stated where it is asserted; the float32 algebra on IDENTICAL features
+is checked at 1e-6 separately (test_consumers_vs_numpy)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN, load_golden
+
+pytestmark = pytest.mark.gpu
+
+CASES = {"rbf_f64": ("RBF", 256, {}, True, 32, 64), "rbf_f32": ("RBF", 256, {}, False, 32, 64),
+         "conv_f64": ("Conv1dRBF", 192, {"conv_width": 3}, True, 24, 32)}
+
+
+def _setup(name, resident=False):
+    from xgpr_b200 import fitting
+    from xgpr_b200.kernels import KERNEL_NAME_TO_CLASS
+    g = load_golden(os.path.join(GOLDEN, f"l3_fit_{name}.npz"))
+    kname, m, parms, dp, rank_p, vrffs = CASES[name]
+    kern = KERNEL_NAME_TO_CLASS[kname](g["x"].shape, m, random_seed=123, device="cuda", double_precision=dp,
+                                       kernel_spec_parms=parms)
+    kern.set_hyperparams(np.log(g["hyperparams"]), logspace=True)
+    x = torch.from_numpy(g["x"]).cuda() if resident else g["x"]
+    ds = fitting.build_shard_dataset(x, g["y"], g.get("seqlen"), chunk_size=97)
+    return fitting, g, kern, ds, rank_p, vrffs
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_fit_matches_reference(name):
+    fitting, g, kern, ds, rank_p, vrffs = _setup(name)
+    f64 = CASES[name][3]
+    tol = dict(rtol=1e-6, atol=1e-9) if f64 else dict(rtol=2e-3, atol=2e-4)   # float32: see module docstring
+    np.testing.assert_allclose(ds.get_ymean(), float(g["trainy_mean"]), rtol=1e-12)
+    np.testing.assert_allclose(ds.get_ystd(), float(g["trainy_std"]), rtol=1e-12)
+    w, _, _ = fitting.calc_weights_exact(ds, kern)
+    np.testing.assert_allclose(w.cpu().numpy(), g["w_exact"], **tol)
+    for method in ("srht", "srht_2"):
+        pre = fitting.RandNysPreconditioner(kern, ds, rank_p, False, 123, method)
+        np.testing.assert_allclose(pre.achieved_ratio, float(g[f"ratio_{method}"]), rtol=1e-6 if f64 else 1e-3)
+        np.testing.assert_allclose(pre.get_zty().cpu().numpy(), g[f"zty_{method}"], rtol=1e-6 if f64 else 1e-3,
+                                   atol=1e-9 if f64 else 1e-3)
+        wcg, nit, _ = fitting.cg_fit_lib_internal(kern, ds, 1e-12, 500, pre, False)
+        np.testing.assert_allclose(wcg.cpu().numpy(), g[f"w_cg_{method}"], **tol)
+        assert abs(nit - int(g[f"niter_{method}"])) <= 2
+    wcg0, nit0, _ = fitting.cg_fit_lib_internal(kern, ds, 1e-12, 2000, None, False)
+    np.testing.assert_allclose(wcg0.cpu().numpy(), g["w_cg_none"], **tol)
+    var = fitting.calc_variance_exact(kern, ds, vrffs)
+    np.testing.assert_allclose(var.cpu().numpy(), g["var"], rtol=1e-6 if f64 else 1e-2, atol=1e-10 if f64 else 1e-5)
+    pred, pvar = fitting.predict(kern, wcg0, g["xtest"], g.get("stest"), 23, ds.get_ymean(), ds.get_ystd(), var, vrffs)
+    np.testing.assert_allclose(pred, g["pred_cg"], rtol=1e-6 if f64 else 1e-4, atol=1e-9 if f64 else 1e-4)
+    np.testing.assert_allclose(pvar, g["pred_var"], rtol=1e-6 if f64 else 1e-3, atol=1e-10)
+    pe = fitting.predict(kern, w, g["xtest"], g.get("stest"), 50, ds.get_ymean(), ds.get_ystd())
+    np.testing.assert_allclose(pe, g["pred_exact"], rtol=1e-6 if f64 else 1e-4, atol=1e-9 if f64 else 1e-4)
+
+
+def test_resident_shard_gives_identical_weights():
+    fitting, g, kern, ds, _, _ = _setup("rbf_f32")
+    w0, _, _ = fitting.calc_weights_exact(ds, kern)
+    _, _, kern2, ds2, _, _ = _setup("rbf_f32", resident=True)
+    w1, _, _ = fitting.calc_weights_exact(ds2, kern2)
+    assert torch.equal(w0, w1)
+
+
+@pytest.mark.parametrize("shape", [(300, 64, 1), (1000, 200, 7), (257, 130, 26), (64, 2048, 3)])
+def test_consumers_vs_numpy(shape):
+    """zty / ztz / atb / cg_matvec on the same Z as NumPy float64: 1e-6 is the north_star bound, 1e-12 is what holds."""
+    from xgpr_b200 import ext
+    n, m, r = shape
+    rng = np.random.default_rng(5)
+    z, y, v, a = rng.standard_normal((n, m)), rng.standard_normal(n), rng.standard_normal((m, r)), rng.standard_normal((n, 2 * r + 1))
+    Z, Y, V, A = (torch.from_numpy(t).cuda() for t in (z, y, v, a))
+    zty = torch.ones(m, dtype=torch.float64, device="cuda")
+    ztz = torch.ones((m, m), dtype=torch.float64, device="cuda")
+    acc = torch.ones((2 * r + 1, m), dtype=torch.float64, device="cuda")
+    w = torch.ones((m, r), dtype=torch.float64, device="cuda")
+    ext.zty_accum(Z, Y, zty)
+    ext.ztz_accum(Z, ztz)
+    ext.atb_accum(A, Z, acc)
+    ext.cg_matvec_accum(Z, V, w)
+    t = dict(rtol=1e-12, atol=1e-11)
+    np.testing.assert_allclose(zty.cpu().numpy(), 1 + z.T @ y, **t)
+    np.testing.assert_allclose(ztz.cpu().numpy(), 1 + z.T @ z, **t)
+    np.testing.assert_allclose(acc.cpu().numpy(), 1 + a.T @ z, **t)
+    np.testing.assert_allclose(w.cpu().numpy(), 1 + z.T @ (z @ v), **t)

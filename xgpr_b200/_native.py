@@ -34,6 +34,7 @@ SIGNATURES = {
 F64_ONLY = {
     "xgpr_b200_zty_accum_f64": [_ptr, _i64, _i64, _ptr, _ptr, _ptr],
     "xgpr_b200_ztz_accum_f64": [_ptr, _i64, _i64, _ptr, _ptr],
+    "xgpr_b200_atb_accum_f64": [_ptr, _ptr, _i64, _i64, _i64, _ptr, _ptr],
     "xgpr_b200_cg_matvec_accum_f64": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _ptr, _ptr],
 }
 

@@ -43,6 +43,7 @@ int ard_dispatch(const T* x, int64_t n, int64_t d, double* out, const T* w, int6
                  int fit_intercept, cudaStream_t st);
 int zty_accum(const double* z, int64_t n, int64_t m, const double* y, double* zty, cudaStream_t st);
 int ztz_accum(const double* z, int64_t n, int64_t m, double* ztz, cudaStream_t st);
+int atb_accum(const double* a, const double* b, int64_t n, int64_t r, int64_t m, double* c, cudaStream_t st);
 int cg_matvec_accum(const double* z, int64_t n, int64_t m, const double* v, int64_t r, double* w,
                     double* scratch, cudaStream_t st);
 
@@ -122,6 +123,9 @@ int xgpr_b200_zty_accum_f64(const double* z, int64_t n, int64_t m, const double*
     return zty_accum(z, n, m, y, zty, ST(s));
 }
 int xgpr_b200_ztz_accum_f64(const double* z, int64_t n, int64_t m, double* ztz, void* s) { return ztz_accum(z, n, m, ztz, ST(s)); }
+int xgpr_b200_atb_accum_f64(const double* a, const double* b, int64_t n, int64_t r, int64_t m, double* c, void* s) {
+    return atb_accum(a, b, n, r, m, c, ST(s));
+}
 int xgpr_b200_cg_matvec_accum_f64(const double* z, int64_t n, int64_t m, const double* v, int64_t r, double* w, double* scratch,
                                   void* s) {
     return cg_matvec_accum(z, n, m, v, r, w, scratch, ST(s));

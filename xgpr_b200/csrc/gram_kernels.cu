@@ -146,7 +146,76 @@ ztz_kernel(const double* __restrict__ z, int64_t n, int64_t m, double* __restric
         }
 }
 
+// ------------------------------------------------------------------ c (r, m) += A^T B ;  A (n, r), B (n, m)
+// The Nystrom sketch accumulation  acc += SRHT(Z)[:, perm[:rank]]^T Z
+// (src/xGPR/preconditioners/rand_nys_constructors.py:119).  Same tiling as ztz_kernel, no symmetry.
+__global__ void __launch_bounds__(256)
+atb_kernel(const double* __restrict__ a, const double* __restrict__ b, int64_t n, int64_t r, int64_t m,
+           double* __restrict__ c, int tiles_j, int64_t rows_per_split) {
+    const int ti = blockIdx.x / tiles_j, tj = blockIdx.x % tiles_j;
+    const int64_t i0 = (int64_t)ti * GT, j0 = (int64_t)tj * GT;
+    const int64_t n0 = (int64_t)blockIdx.y * rows_per_split;
+    const int64_t n1 = (n0 + rows_per_split < n) ? n0 + rows_per_split : n;
+    __shared__ double as[GK][GT];
+    __shared__ double bs[GK][GT];
+    const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;
+    double acc[4][4];
+#pragma unroll
+    for (int x = 0; x < 4; ++x)
+#pragma unroll
+        for (int y = 0; y < 4; ++y) acc[x][y] = 0.0;
+    for (int64_t k0 = n0; k0 < n1; k0 += GK) {
+        __syncthreads();
+        for (int t = threadIdx.x; t < GK * GT; t += 256) {
+            const int kk = t / GT, cc = t % GT;
+            const int64_t row = k0 + kk;
+            as[kk][cc] = (row < n1 && i0 + cc < r) ? a[row * r + i0 + cc] : 0.0;
+            bs[kk][cc] = (row < n1 && j0 + cc < m) ? b[row * m + j0 + cc] : 0.0;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < GK; ++kk) {
+            double av[4], bv[4];
+#pragma unroll
+            for (int x = 0; x < 4; ++x) av[x] = as[kk][ty + 16 * x];
+#pragma unroll
+            for (int y = 0; y < 4; ++y) bv[y] = bs[kk][tx + 16 * y];
+#pragma unroll
+            for (int x = 0; x < 4; ++x)
+#pragma unroll
+                for (int y = 0; y < 4; ++y) acc[x][y] = fma(av[x], bv[y], acc[x][y]);
+        }
+    }
+    const bool split = gridDim.y > 1;
+#pragma unroll
+    for (int x = 0; x < 4; ++x)
+#pragma unroll
+        for (int y = 0; y < 4; ++y) {
+            const int64_t i = i0 + ty + 16 * x, j = j0 + tx + 16 * y;
+            if (i < r && j < m) {
+                if (split) atomicAdd(c + i * m + j, acc[x][y]);
+                else       c[i * m + j] += acc[x][y];
+            }
+        }
+}
+
 // ------------------------------------------------------------------ host
+int atb_accum(const double* a, const double* b, int64_t n, int64_t r, int64_t m, double* c, cudaStream_t st) {
+    XB_REQUIRE(n > 0 && r > 0 && m > 0, "no datapoints");
+    XB_REQUIRE(a && b && c, "null pointer");
+    const int ti = (int)((r + GT - 1) / GT), tj = (int)((m + GT - 1) / GT);
+    const int64_t ntile = (int64_t)ti * tj;
+    int64_t splits = 1;
+    if (ntile < 148 * 2) splits = (148 * 2 + ntile - 1) / ntile;
+    int64_t rows_per = (n + splits - 1) / splits;
+    rows_per = ((rows_per + GK - 1) / GK) * GK;
+    splits = (n + rows_per - 1) / rows_per;
+    dim3 grid((unsigned)ntile, (unsigned)splits);
+    atb_kernel<<<grid, 256, 0, st>>>(a, b, n, r, m, c, tj, rows_per);
+    count_launch();
+    return check_launch("atb_kernel");
+}
+
 int zty_accum(const double* z, int64_t n, int64_t m, const double* y, double* zty, cudaStream_t st) {
     XB_REQUIRE(n > 0 && m > 0, "no datapoints");
     XB_REQUIRE(z && y && zty, "null pointer");

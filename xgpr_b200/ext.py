@@ -198,6 +198,17 @@ def ztz_accum(z, ztz):
     check(lib.xgpr_b200_ztz_accum_f64(z.data_ptr(), z.shape[0], z.shape[1], ztz.data_ptr(), _stream()))
 
 
+def atb_accum(a, z, acc):
+    """acc (r, m) += a^T z ; a (n, r) may be a strided view (it is made contiguous), z (n, m)."""
+    a = _dev(a.contiguous(), "a", (torch.float64,), 2)
+    z = _dev(z, "z", (torch.float64,), 2)
+    acc = _dev(acc, "acc", (torch.float64,), 2)
+    if a.shape[0] != z.shape[0] or acc.shape[0] != a.shape[1] or acc.shape[1] != z.shape[1]:
+        raise RuntimeError("wrong array sizes")
+    check(lib.xgpr_b200_atb_accum_f64(a.data_ptr(), z.data_ptr(), z.shape[0], a.shape[1], z.shape[1],
+                                      acc.data_ptr(), _stream()))
+
+
 def cg_matvec_accum(z, v, w, scratch=None):
     z = _dev(z, "z", (torch.float64,), 2)
     v = _dev(v, "v", (torch.float64,), 2)

@@ -1,0 +1,435 @@
+"""The L4 call sites of the hot path: chunk loop -> kernel.transform_x -> accumulate.
+
+Mirrors, on torch tensors and the C-ABI consumers of Z (xgpr_b200_{zty,ztz,cg_matvec}_accum_f64):
+
+  calc_zty / calc_design_mat / direct_weight_calc / calc_var_design_mat
+        src/xGPR/scoring_toolkit/exact_nmll_calcs.py:13-38, :42-78, :82-112, :116-139
+  calc_weights_exact / calc_variance_exact
+        src/xGPR/fitting_toolkit/exact_fitting_toolkit.py:16-36, :40-68   (incl. lambda^2 added twice)
+  ConjugateGrad / cg_fit_lib_internal
+        src/xGPR/fitting_toolkit/cg_tools.py:26-156, cg_fitting_toolkit.py:18-70
+  RandNysPreconditioner (methods "srht", "srht_2", ...)
+        src/xGPR/preconditioners/rand_nys_constructors.py:18-123, :128-296,
+        src/xGPR/preconditioners/rand_nys_preconditioners.py:18-72
+  predict   src/xGPR/xgp_regression.py:105-134
+
+Rows shard across GPUs: every rank holds a contiguous row block in its own
+``ShardDataset``; parameters are replicated; ``RowShardComm.all_reduce_`` (NCCL, fp64 sum) runs at the
+reduction points only -- Z^T y / y^T y, Z^T Z, the Nystrom accumulator, and the CG matvec partial sum
+once per iteration.  Dense factorizations (Cholesky, SVD, QR) are replicated library calls, as in the
+reference.
+
+``ops`` is the provider of the three consumers; the default is the CUDA library (``xgpr_b200.ext``) and
+fails loudly on non-CUDA tensors.  Tests inject an oracle-backed provider to run the host logic under
+``gloo`` on CPU.
+"""
+import warnings
+
+import numpy as np
+import torch
+
+from . import ext as _cuda_ops
+
+
+# ----------------------------------------------------------------------------------------- plumbing
+class RowShardComm:
+    """Thin wrapper over torch.distributed for the row-sharded reductions (no-op when world size is 1)."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        self.dist = dist if (dist.is_available() and dist.is_initialized()) else None
+        self.group = group
+        self.world = self.dist.get_world_size(group) if self.dist else 1
+        self.rank = self.dist.get_rank(group) if self.dist else 0
+        self.n_allreduce = 0
+
+    def all_reduce_(self, *tensors):
+        """In-place sum over ranks.  Several small tensors are flattened into ONE call (latency-bound)."""
+        if self.world == 1:
+            return
+        self.n_allreduce += 1
+        if len(tensors) == 1:
+            self.dist.all_reduce(tensors[0], group=self.group)
+            return
+        flat = torch.cat([t.reshape(-1) for t in tensors])
+        self.dist.all_reduce(flat, group=self.group)
+        off = 0
+        for t in tensors:
+            t.copy_(flat[off:off + t.numel()].view_as(t))
+            off += t.numel()
+
+    def sum_scalar(self, value, device):
+        t = torch.tensor([float(value)], dtype=torch.float64, device=device)
+        self.all_reduce_(t)
+        return float(t[0])
+
+
+class ShardDataset:
+    """This rank's row block, with the reference's dataset-iterator interface
+    (src/xGPR/data_handling/online_data_handling.py:54-94, data_handling_baseclass.py:40-75).
+
+    x / y / sequence_lengths may be NumPy arrays, pinned host tensors or CUDA tensors (a resident shard
+    avoids the per-pass H2D copies).  ``trainy_mean`` / ``trainy_std`` and ``global_ndatapoints`` are
+    GLOBAL statistics (use ``build_shard_dataset``)."""
+
+    def __init__(self, xdata, ydata=None, sequence_lengths=None, chunk_size=2000, trainy_mean=0.0,
+                 trainy_std=1.0, global_ndatapoints=None):
+        self._xdata, self._ydata, self._sequence_lengths = xdata, ydata, sequence_lengths
+        self._chunk_size = int(chunk_size)
+        self._trainy_mean, self._trainy_std = float(trainy_mean), float(trainy_std)
+        self._n_local = int(xdata.shape[0])
+        self._n_global = int(global_ndatapoints) if global_ndatapoints is not None else self._n_local
+
+    def get_chunk_size(self):
+        return self._chunk_size
+
+    def get_ndatapoints(self):
+        return self._n_global
+
+    def get_local_ndatapoints(self):
+        return self._n_local
+
+    def get_xdim(self):
+        return tuple(self._xdata.shape)
+
+    def get_ymean(self):
+        return self._trainy_mean
+
+    def get_ystd(self):
+        return self._trainy_std
+
+    def _ychunk(self, lo, hi):
+        y = self._ydata[lo:hi]
+        if isinstance(y, torch.Tensor):
+            return (y.to(torch.float64) - self._trainy_mean) / self._trainy_std
+        y = y.astype(np.float64)
+        y -= self._trainy_mean
+        y /= self._trainy_std
+        return y
+
+    def get_chunked_data(self):
+        for lo in range(0, self._n_local, self._chunk_size):
+            hi = min(lo + self._chunk_size, self._n_local)
+            sl = None if self._sequence_lengths is None else self._sequence_lengths[lo:hi]
+            yield self._xdata[lo:hi, ...], self._ychunk(lo, hi), sl
+
+    def get_chunked_x_data(self):
+        for lo in range(0, self._n_local, self._chunk_size):
+            hi = min(lo + self._chunk_size, self._n_local)
+            sl = None if self._sequence_lengths is None else self._sequence_lengths[lo:hi]
+            yield self._xdata[lo:hi, ...], sl
+
+
+def build_shard_dataset(xdata, ydata, sequence_lengths=None, chunk_size=2000, comm=None):
+    """y is standardised with the GLOBAL mean / std (dataset_builder.py:14-70 computes them over the whole
+    training set): one all-reduce of (n, sum y, sum y^2)."""
+    comm = comm or RowShardComm()
+    yv = ydata.detach().double().cpu().numpy() if isinstance(ydata, torch.Tensor) else np.asarray(ydata, np.float64)
+    dev = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu")
+    n = comm.sum_scalar(yv.shape[0], dev)
+    mean = comm.sum_scalar(yv.sum(), dev) / n
+    var = comm.sum_scalar(((yv - mean) ** 2).sum(), dev) / n       # np.std: population std
+    return ShardDataset(xdata, ydata, sequence_lengths, chunk_size, mean, float(np.sqrt(var)), int(round(n)))
+
+
+# ----------------------------------------------------------------------------------------- accumulation passes
+def _new(shape, like_device):
+    return torch.zeros(shape, dtype=torch.float64, device=like_device)
+
+
+def _device_of(kernel):
+    return torch.device("cuda", torch.cuda.current_device()) if kernel.device == "cuda" else torch.device("cpu")
+
+
+def calc_zty(dataset, kernel, comm=None, ops=_cuda_ops):
+    """z^T y and y^T y over the whole (sharded) dataset.  exact_nmll_calcs.py:13-38."""
+    comm = comm or RowShardComm()
+    dev = _device_of(kernel)
+    z_trans_y, y_trans_y = _new((kernel.get_num_rffs(),), dev), _new((1,), dev)
+    for xin, yin, ldata in dataset.get_chunked_data():
+        z, y = kernel.transform_x_y(xin, yin, ldata)
+        ops.zty_accum(z, y, z_trans_y)
+        y_trans_y += y @ y
+    comm.all_reduce_(z_trans_y, y_trans_y)
+    return z_trans_y, float(y_trans_y[0])
+
+
+def calc_design_mat(dataset, kernel, comm=None, ops=_cuda_ops):
+    """z^T z, z^T y, y^T y.  exact_nmll_calcs.py:42-78; one all-reduce of the M x M Gram per pass."""
+    comm = comm or RowShardComm()
+    dev = _device_of(kernel)
+    m = kernel.get_num_rffs()
+    z_trans_z, z_trans_y, y_trans_y = _new((m, m), dev), _new((m,), dev), _new((1,), dev)
+    for xin, yin, ldata in dataset.get_chunked_data():
+        z, y = kernel.transform_x_y(xin, yin, ldata)
+        ops.zty_accum(z, y, z_trans_y)
+        ops.ztz_accum(z, z_trans_z)
+        y_trans_y += y @ y
+    comm.all_reduce_(z_trans_z)
+    comm.all_reduce_(z_trans_y, y_trans_y)
+    return z_trans_z, z_trans_y, float(y_trans_y[0])
+
+
+def direct_weight_calc(chol_z_trans_z, z_trans_y, kernel):
+    """Cholesky + two triangular solves; adds lambda^2 to the diagonal.  exact_nmll_calcs.py:82-112."""
+    lambda_p = kernel.get_hyperparams(logspace=False)[0]
+    chol_z_trans_z.diagonal().add_(lambda_p ** 2)
+    chol = torch.linalg.cholesky(chol_z_trans_z)
+    w = torch.linalg.solve_triangular(chol, z_trans_y[:, None], upper=False)
+    w = torch.linalg.solve_triangular(chol.T, w, upper=True)
+    return chol, w[:, 0]
+
+
+def calc_weights_exact(dataset, kernel, comm=None, ops=_cuda_ops):
+    """exact_fitting_toolkit.py:16-36.  lambda^2 is added here AND inside direct_weight_calc, exactly as
+    the reference does: the exact fit solves (Z^T Z + 2 lambda^2 I) w = Z^T y."""
+    z_trans_z, z_trans_y, _ = calc_design_mat(dataset, kernel, comm, ops)
+    lambda_p = kernel.get_hyperparams(logspace=False)[0]
+    z_trans_z.diagonal().add_(lambda_p ** 2)
+    _, weights = direct_weight_calc(z_trans_z, z_trans_y, kernel)
+    return weights, 1, []
+
+
+def calc_var_design_mat(dataset, kernel, variance_rffs, comm=None, ops=_cuda_ops):
+    """exact_nmll_calcs.py:116-139: Gram of the first variance_rffs columns."""
+    comm = comm or RowShardComm()
+    z_trans_z = _new((variance_rffs, variance_rffs), _device_of(kernel))
+    for xdata, ldata in dataset.get_chunked_x_data():
+        z = kernel.transform_x(xdata, ldata)
+        ops.ztz_accum(z[:, :variance_rffs].contiguous(), z_trans_z)
+    comm.all_reduce_(z_trans_z)
+    return z_trans_z
+
+
+def calc_variance_exact(kernel, dataset, variance_rffs, comm=None, ops=_cuda_ops):
+    """exact_fitting_toolkit.py:40-68."""
+    z_trans_z = calc_var_design_mat(dataset, kernel, variance_rffs, comm, ops)
+    z_trans_z.diagonal().add_(kernel.get_lambda() ** 2)
+    return torch.linalg.pinv(z_trans_z)
+
+
+# ----------------------------------------------------------------------------------------- conjugate gradients
+class ConjugateGrad:
+    """Batched-RHS preconditioned CG on (Z^T Z + lambda^2 I).  cg_tools.py:15-156 (GPU_ConjugateGrad)."""
+
+    def __init__(self, comm=None, ops=_cuda_ops):
+        self.comm = comm or RowShardComm()
+        self.ops = ops
+        self._scratch = None
+
+    def _matvec(self, dataset, kernel, vec, matvec):
+        """matvec <- sum_chunks Z^T (Z vec) + lambda^2 vec.  cg_tools.py:26-53.  The per-rank partial sum is
+        all-reduced ONCE per call (one NCCL call per CG iteration); lambda^2 vec is added after it."""
+        matvec.zero_()
+        vec = vec.contiguous()
+        for x, lengths in dataset.get_chunked_x_data():
+            z = kernel.transform_x(x, lengths)
+            if self._scratch is None or self._scratch.shape[0] < z.shape[0] or self._scratch.shape[1] != vec.shape[1] \
+                    or self._scratch.device != z.device:
+                self._scratch = torch.empty((z.shape[0], vec.shape[1]), dtype=torch.float64, device=z.device)
+            self.ops.cg_matvec_accum(z, vec, matvec, self._scratch)
+        self.comm.all_reduce_(matvec)
+        matvec.add_(vec, alpha=kernel.get_lambda() ** 2)
+
+    def fit(self, dataset, kernel, preconditioner, resid, maxiter=200, tol=1e-4, verbose=True,
+            nmll_settings=False):
+        converged = False
+        target = resid[:, 0, :].clone()
+        init_norms = torch.linalg.norm(target, dim=0)
+        dev, nr, nrhs = resid.device, resid.shape[0], resid.shape[2]
+        z_k = torch.zeros((nr, 2, nrhs), dtype=torch.float64, device=dev)
+        p_k = torch.zeros((nr, 2, nrhs), dtype=torch.float64, device=dev)
+        alphas, betas, losses = [], [], []
+        x_k = torch.zeros((nr, nrhs), dtype=torch.float64, device=dev)
+        w = torch.zeros((nr, nrhs), dtype=torch.float64, device=dev)
+
+        z_k[:, 0, :] = resid[:, 0, :] if preconditioner is None else preconditioner.batch_matvec(resid[:, 0, :])
+        p_k[:, 0, :] = z_k[:, 0, :]
+        next_col, current_col = 1, 0
+        niter = 0
+        for niter in range(maxiter):
+            self._matvec(dataset, kernel, p_k[:, current_col, :], w)
+            alpha = (resid[:, current_col, :] * z_k[:, current_col, :]).sum(dim=0) / \
+                    (p_k[:, current_col, :] * w).sum(dim=0)
+            x_k += alpha[None, :] * p_k[:, current_col, :]
+            resid[:, next_col, :] = resid[:, current_col, :] - alpha[None, :] * w
+            # convergence is judged on the PREVIOUS residual, as in the reference (cg_tools.py:116,139)
+            err = torch.linalg.norm(resid[:, current_col, :], dim=0) / init_norms
+            if preconditioner is None:
+                z_k[:, next_col, :] = resid[:, next_col, :]
+            else:
+                z_k[:, next_col, :] = preconditioner.batch_matvec(resid[:, next_col, :])
+            beta = (resid[:, next_col, :] * z_k[:, next_col, :]).sum(dim=0) / \
+                   (resid[:, current_col, :] * z_k[:, current_col, :]).sum(dim=0)
+            p_k[:, next_col, :] = z_k[:, next_col, :] + beta[None, :] * p_k[:, current_col, :]
+            if nmll_settings:
+                alphas.append(alpha.clone())
+                betas.append(beta.clone())
+            else:
+                losses.append(float(err[0]))
+            next_col, current_col = abs(next_col - 1), abs(current_col - 1)
+            if niter % 5 == 0 and verbose:
+                print(f"{niter} iterations complete.")
+            if float(err.max()) < tol:
+                converged = True
+                break
+
+        if nmll_settings:
+            alphas, betas = torch.stack(alphas), torch.stack(betas)
+            return x_k, alphas[:, 1:].cpu().numpy(), betas[:, 1:].cpu().numpy()
+        if x_k.shape[1] > 1:
+            return x_k, converged, niter + 1, losses
+        return x_k[:, 0], converged, niter + 1, losses
+
+
+def cg_fit_lib_internal(kernel, dataset, cg_tol=1e-4, max_iter=500, preconditioner=None, verbose=True,
+                        comm=None, ops=_cuda_ops):
+    """cg_fitting_toolkit.py:18-70: rhs = Z^T y / N, zero start, result * N."""
+    comm = comm or RowShardComm()
+    cg_operator = ConjugateGrad(comm, ops)
+    if preconditioner is None:
+        z_trans_y, _ = calc_zty(dataset, kernel, comm, ops)
+    else:
+        z_trans_y = preconditioner.get_zty()
+    resid = torch.zeros((kernel.get_num_rffs(), 2, 1), dtype=torch.float64, device=z_trans_y.device)
+    resid[:, 0, :] = z_trans_y[:, None] / dataset.get_ndatapoints()
+    weights, converged, n_iter, losses = cg_operator.fit(dataset, kernel, preconditioner, resid, max_iter, cg_tol,
+                                                         verbose, nmll_settings=False)
+    weights *= dataset.get_ndatapoints()
+    if not converged:
+        warnings.warn("Conjugate gradients failed to converge! Try refitting the model with updated settings.")
+    if verbose:
+        print(f"CG iterations: {n_iter}")
+    return weights, n_iter, losses
+
+
+# ----------------------------------------------------------------------------------------- randomised Nystrom
+def _single_pass_srht_zty(dataset, kernel, compressor, acc_results, z_trans_y, ops):
+    """rand_nys_constructors.py:96-123: acc (rank, M) += SRHT(Z)[:, perm[:rank]]^T Z ; z^T y ; y^T y."""
+    y_trans_y = _new((1,), acc_results.device)
+    for xin, yin, ldata in dataset.get_chunked_data():
+        z, y = kernel.transform_x_y(xin, yin, ldata)
+        ops.zty_accum(z, y, z_trans_y)
+        y_trans_y += y @ y
+        ops.atb_accum(compressor.transform_x(z), z, acc_results)
+    return y_trans_y
+
+
+def _single_pass_gauss(dataset, kernel, q_mat, acc_results, ops, scratch_holder):
+    """rand_nys_constructors.py:18-36: acc (M, rank) += Z^T (Z Q) -- the CG matvec with `rank` right-hand sides."""
+    q_mat = q_mat.contiguous()
+    for xdata, ldata in dataset.get_chunked_x_data():
+        z = kernel.transform_x(xdata, ldata)
+        s = scratch_holder.get("s")
+        if s is None or s.shape[0] < z.shape[0] or s.shape[1] != q_mat.shape[1]:
+            s = scratch_holder["s"] = torch.empty((z.shape[0], q_mat.shape[1]), dtype=torch.float64, device=z.device)
+        ops.cg_matvec_accum(z, q_mat, acc_results, s)
+
+
+def initialize_srht(dataset, rank, kernel, random_state, comm, ops, compressor_cls):
+    """rand_nys_constructors.py:221-296 (single pass)."""
+    dev = _device_of(kernel)
+    m = kernel.get_num_rffs()
+    acc_results, z_trans_y = _new((rank, m), dev), _new((m,), dev)
+    compressor = compressor_cls(rank, m, random_seed=random_state, device=kernel.device)
+    y_trans_y = _single_pass_srht_zty(dataset, kernel, compressor, acc_results, z_trans_y, ops)
+    comm.all_reduce_(acc_results)
+    comm.all_reduce_(z_trans_y, y_trans_y)
+
+    c_mat = compressor.transform_x(acc_results)
+    _, c_s1, c_v1 = torch.linalg.svd(c_mat, full_matrices=False)
+    mask = c_s1 < 1e-14
+    c_s1 = 1.0 / torch.sqrt(c_s1.clamp(min=1e-14))
+    c_s1[mask] = 0
+    acc_results = acc_results.T @ c_v1.T @ (c_s1[:, None] * c_v1)
+    u_mat, s_mat, _ = torch.linalg.svd(acc_results, full_matrices=False)
+    return u_mat, s_mat ** 2, z_trans_y, float(y_trans_y[0])
+
+
+def initialize_srht_multipass(dataset, rank, kernel, random_state, comm, ops, compressor_cls, n_passes=2):
+    """rand_nys_constructors.py:128-218 (SRHT pass, then QR + Z^T (Z Q) passes, shifted Cholesky, SVD)."""
+    dev = _device_of(kernel)
+    m = kernel.get_num_rffs()
+    acc_results, z_trans_y = _new((rank, m), dev), _new((m,), dev)
+    compressor = compressor_cls(rank, m, random_seed=random_state, device=kernel.device)
+    y_trans_y = _single_pass_srht_zty(dataset, kernel, compressor, acc_results, z_trans_y, ops)
+    comm.all_reduce_(acc_results)
+    comm.all_reduce_(z_trans_y, y_trans_y)
+    acc_results = acc_results.T.contiguous()
+    q_mat, holder = None, {}
+    for _ in range(n_passes - 1):
+        q_mat, _ = torch.linalg.qr(acc_results)
+        acc_results.zero_()
+        _single_pass_gauss(dataset, kernel, q_mat, acc_results, ops, holder)
+        comm.all_reduce_(acc_results)
+    norm = float(torch.sqrt((acc_results ** 2).sum()))
+    shift = float(np.spacing(norm))
+    acc_results += shift * q_mat
+    q_mat = torch.linalg.cholesky(q_mat.T @ acc_results)
+    acc_results = torch.linalg.solve_triangular(q_mat, acc_results.T, upper=False).T
+    u_mat, s_mat, _ = torch.linalg.svd(acc_results, full_matrices=False)
+    s_mat = (s_mat ** 2 - shift).clamp(min=0)
+    return u_mat, s_mat, z_trans_y, float(y_trans_y[0])
+
+
+class RandNysPreconditioner:
+    """rand_nys_preconditioners.py:14-72."""
+
+    def __init__(self, kernel, dataset, max_rank, verbose=False, random_state=123, method="srht", comm=None,
+                 ops=_cuda_ops, compressor_cls=None):
+        if method not in ["srht_2", "srht_3", "srht"]:
+            raise RuntimeError("Unknown method supplied for tuning preconditioner construction.")
+        comm = comm or RowShardComm()
+        if compressor_cls is None:
+            from .kernels import SRHTCompressor as compressor_cls
+        if method.startswith("srht_"):
+            self.u_mat, self.eig, self.z_trans_y, self.y_trans_y = initialize_srht_multipass(
+                dataset, max_rank, kernel, random_state, comm, ops, compressor_cls, int(method.split("_")[1]))
+        else:
+            self.u_mat, self.eig, self.z_trans_y, self.y_trans_y = initialize_srht(
+                dataset, max_rank, kernel, random_state, comm, ops, compressor_cls)
+        lambda_ = kernel.get_lambda()
+        min_eig = float(self.eig.min())
+        self.eig = self.eig + lambda_ ** 2
+        self.inv_eig = self.eig.clone()
+        mask = self.inv_eig > 1e-14
+        self.inv_eig[mask] = 1 / self.inv_eig[mask]
+        self.inv_eig[~mask] = 0.0
+        self.achieved_ratio = min_eig / lambda_ ** 2
+        self.prefactor = float(min_eig + lambda_ ** 2)
+        self.device = kernel.device
+
+    def batch_matvec(self, xvec):
+        xprod = self.u_mat.T @ xvec
+        xprod1 = self.u_mat @ (self.inv_eig[:, None] * self.prefactor * xprod)
+        xprod2 = xvec - (self.u_mat @ xprod)
+        return xprod2 + xprod1
+
+    def get_zty(self):
+        return self.z_trans_y
+
+    def get_rank(self):
+        return self.inv_eig.shape[0]
+
+
+# ----------------------------------------------------------------------------------------- predict
+def predict(kernel, weights, input_x, sequence_lengths=None, chunk_size=2000, trainy_mean=0.0, trainy_std=1.0,
+            var=None, variance_rffs=None):
+    """xgp_regression.py:105-134: (Z * w).sum(1), de-standardised; optional exact variance (:120-126)."""
+    preds, pvar = [], []
+    lambda_ = kernel.get_lambda()
+    for i in range(0, input_x.shape[0], chunk_size):
+        cutoff = min(i + chunk_size, input_x.shape[0])
+        sl = None if sequence_lengths is None else sequence_lengths[i:cutoff]
+        z = kernel.transform_x(input_x[i:cutoff, ...], sl)
+        preds.append((z * weights[None, :]).sum(dim=1))
+        if var is not None:
+            zv = z[:, :variance_rffs]
+            pv = (var @ zv.T).T
+            pvar.append(lambda_ ** 2 + lambda_ ** 2 * (zv * pv).sum(dim=1))
+    preds = torch.cat(preds).cpu().numpy() * trainy_std + trainy_mean
+    if var is None:
+        return preds
+    pvar = torch.cat(pvar).cpu().numpy()
+    pvar[pvar < 0] = 0
+    return preds, pvar * trainy_std ** 2
