@@ -61,12 +61,13 @@ def test_fit_matches_reference(name):
     np.testing.assert_allclose(pe, g["pred_exact"], rtol=1e-6 if f64 else 1e-4, atol=1e-9 if f64 else 1e-4)
 
 
-def test_resident_shard_gives_identical_weights():
+def test_resident_shard_gives_same_weights():
     fitting, g, kern, ds, _, _ = _setup("rbf_f32")
     w0, _, _ = fitting.calc_weights_exact(ds, kern)
     _, _, kern2, ds2, _, _ = _setup("rbf_f32", resident=True)
     w1, _, _ = fitting.calc_weights_exact(ds2, kern2)
-    assert torch.equal(w0, w1)
+    # same features bit for bit; the split-K consumers add partial sums with atomics, so order may differ
+    np.testing.assert_allclose(w0.cpu().numpy(), w1.cpu().numpy(), rtol=1e-9, atol=1e-12)
 
 
 @pytest.mark.parametrize("shape", [(300, 64, 1), (1000, 200, 7), (257, 130, 26), (64, 2048, 3)])
