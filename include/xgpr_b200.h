@@ -76,6 +76,23 @@ int xgpr_b200_rbf_grad_f64(const double* x, int64_t n, int64_t d, double* out, d
                            const int8_t* radem, int64_t radem_len, const double* chi, int64_t num_freqs,
                            double sigma, int fit_intercept, void* stream);
 
+/* ---- fused featurise -> matvec for the fixed-vector SORF kernels (no Z in HBM).  One right-hand side of the
+ *      reference's CG matvec `Z = kernel.transform_x(x); matvec += Z.T @ (Z @ vec)`
+ *      (src/xGPR/fitting_toolkit/cg_tools.py:42-44) and of `z_trans_y += Z.T @ y`
+ *      (src/xGPR/scoring_toolkit/exact_nmll_calcs.py:35-36), where Z is exactly what cudaRBFFeatureGen would
+ *      write for the same (already sigma-scaled) x, with Z[:, 0] = 1 when fit_intercept
+ *      (src/xGPR/kernels/kernel_baseclass.py:296-297).  d <= 1024.
+ *   zv : t (n) f64 += Z v ;   v (2*num_freqs) f64
+ *   ztv: w (2*num_freqs) f64 += Z^T t ;  t (n) f64 */
+int xgpr_b200_rbf_zv_f32(const float*  x, int64_t n, int64_t d, const int8_t* radem, int64_t radem_len, const float*  chi,
+                         int64_t num_freqs, int fit_intercept, const double* v, double* t, void* stream);
+int xgpr_b200_rbf_zv_f64(const double* x, int64_t n, int64_t d, const int8_t* radem, int64_t radem_len, const double* chi,
+                         int64_t num_freqs, int fit_intercept, const double* v, double* t, void* stream);
+int xgpr_b200_rbf_ztv_f32(const float*  x, int64_t n, int64_t d, const int8_t* radem, int64_t radem_len, const float*  chi,
+                          int64_t num_freqs, int fit_intercept, const double* t, double* w, void* stream);
+int xgpr_b200_rbf_ztv_f64(const double* x, int64_t n, int64_t d, const int8_t* radem, int64_t radem_len, const double* chi,
+                          int64_t num_freqs, int fit_intercept, const double* t, double* w, void* stream);
+
 /* ---- cudaMiniARDGrad  (xgpr_cuda_rfgen_cpp_ext.cpp:50-59; gpu_rf_gen/rbf_ops/ard_ops.cu:87-148)
  * x (n, d); out (n, 2*num_freqs) f64; w (num_freqs, d) precomputed weights; sigma_map (d) i32;
  * sigma_vals (d) f64; grad (n, 2*num_freqs, num_lengthscales) f64.  All device pointers. */

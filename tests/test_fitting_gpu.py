@@ -91,3 +91,30 @@ def test_consumers_vs_numpy(shape):
     np.testing.assert_allclose(ztz.cpu().numpy(), 1 + z.T @ z, **t)
     np.testing.assert_allclose(acc.cpu().numpy(), 1 + a.T @ z, **t)
     np.testing.assert_allclose(w.cpu().numpy(), 1 + z.T @ (z @ v), **t)
+
+
+@pytest.mark.parametrize("dp", [False, True])
+@pytest.mark.parametrize("case", [(700, 64, 2048, True), (333, 20, 100, True), (129, 7, 6, False), (260, 512, 2048, True),
+                                  (50, 130, 1000, False), (1000, 64, 16384, True), (40, 1000, 300, True)])
+def test_fused_matvec_equals_materialised(case, dp):
+    """rbf_zv / rbf_ztv (features regenerated on chip) against transform_x(x) @ v and transform_x(x).T @ t."""
+    from xgpr_b200.kernels import RBF, Matern
+    n, d, m, icpt = case
+    rng = np.random.default_rng(11)
+    cls = Matern if d == 20 else RBF
+    parms = {"intercept": icpt}
+    if cls is Matern:
+        parms["matern_nu"] = 1.5
+    k = cls((n, d), m, device="cuda", double_precision=dp, kernel_spec_parms=parms)
+    k.set_hyperparams(np.log(np.asarray([0.3, 1.0 / np.sqrt(d)])), logspace=True)
+    x = rng.standard_normal((n, d))
+    z = k.transform_x(x)
+    v = torch.from_numpy(rng.standard_normal(m)).cuda()
+    tin = torch.from_numpy(rng.standard_normal(n)).cuda()
+    xs = k.stage_scaled(x)
+    t = torch.full((n,), 0.5, dtype=torch.float64, device="cuda")
+    w = torch.full((m,), -0.25, dtype=torch.float64, device="cuda")
+    k.fused_zv(xs, v, t)
+    k.fused_ztv(xs, tin, w)
+    np.testing.assert_allclose(t.cpu().numpy(), 0.5 + (z @ v).cpu().numpy(), rtol=1e-11, atol=1e-12)
+    np.testing.assert_allclose(w.cpu().numpy(), -0.25 + (z.T @ tin).cpu().numpy(), rtol=1e-11, atol=1e-12)

@@ -24,6 +24,8 @@ SIGNATURES = {
     "xgpr_b200_scale_input": [_ptr, _i64, _i64, _ptr, _dbl, _ptr],
     "xgpr_b200_srht": [_ptr, _i64, _i64, _ptr, _i64, _ptr],
     "xgpr_b200_rbf_feature_gen": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _int, _ptr],
+    "xgpr_b200_rbf_zv": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _int, _ptr, _ptr, _ptr],
+    "xgpr_b200_rbf_ztv": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _int, _ptr, _ptr, _ptr],
     "xgpr_b200_rbf_grad": [_ptr, _i64, _i64, _ptr, _ptr, _i64, _ptr, _i64, _ptr, _i64, _dbl, _int, _ptr],
     "xgpr_b200_ard_grad": [_ptr, _i64, _i64, _ptr, _ptr, _i64, _ptr, _ptr, _ptr, _i64, _int, _ptr],
     "xgpr_b200_conv1d_maxpool": [_ptr, _i64, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr, _int, _ptr],

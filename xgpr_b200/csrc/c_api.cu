@@ -34,6 +34,9 @@ int rbf_dispatch(const T* x, int64_t n, int64_t d, double* out, double* grad, in
                  const int8_t* radem, int64_t R, const T* chi, int64_t F, double sigma, int fit_intercept,
                  cudaStream_t st);
 template <typename T, int MODE>
+int rbf_matvec_dispatch(const T* x, int64_t n, int64_t d, const int8_t* radem, int64_t R, const T* chi, int64_t F,
+                        int fit_intercept, const double* v, double* t, double* w, cudaStream_t st);
+template <typename T, int MODE>
 int conv_dispatch(const T* x, int64_t n, int64_t m, int64_t c, void* out, int64_t num_rffs, double* grad,
                   const int8_t* radem, int64_t R, const T* chi, int64_t F, const int32_t* seq_host,
                   double sigma, int conv_width, int scaling_type, cudaStream_t st);
@@ -81,6 +84,23 @@ int xgpr_b200_rbf_grad_f32(const float* x, int64_t n, int64_t d, double* out, do
 int xgpr_b200_rbf_grad_f64(const double* x, int64_t n, int64_t d, double* out, double* grad, int64_t num_rffs, const int8_t* radem,
                            int64_t rl, const double* chi, int64_t nf, double sigma, int fi, void* s) {
     return rbf_dispatch<double, true>(x, n, d, out, grad, num_rffs, radem, rl, chi, nf, sigma, fi, ST(s));
+}
+
+int xgpr_b200_rbf_zv_f32(const float* x, int64_t n, int64_t d, const int8_t* radem, int64_t rl, const float* chi, int64_t nf, int fi,
+                         const double* v, double* t, void* s) {
+    return rbf_matvec_dispatch<float, 0>(x, n, d, radem, rl, chi, nf, fi, v, t, nullptr, ST(s));
+}
+int xgpr_b200_rbf_zv_f64(const double* x, int64_t n, int64_t d, const int8_t* radem, int64_t rl, const double* chi, int64_t nf, int fi,
+                         const double* v, double* t, void* s) {
+    return rbf_matvec_dispatch<double, 0>(x, n, d, radem, rl, chi, nf, fi, v, t, nullptr, ST(s));
+}
+int xgpr_b200_rbf_ztv_f32(const float* x, int64_t n, int64_t d, const int8_t* radem, int64_t rl, const float* chi, int64_t nf, int fi,
+                          const double* t, double* w, void* s) {
+    return rbf_matvec_dispatch<float, 1>(x, n, d, radem, rl, chi, nf, fi, nullptr, const_cast<double*>(t), w, ST(s));
+}
+int xgpr_b200_rbf_ztv_f64(const double* x, int64_t n, int64_t d, const int8_t* radem, int64_t rl, const double* chi, int64_t nf, int fi,
+                          const double* t, double* w, void* s) {
+    return rbf_matvec_dispatch<double, 1>(x, n, d, radem, rl, chi, nf, fi, nullptr, const_cast<double*>(t), w, ST(s));
 }
 
 int xgpr_b200_ard_grad_f32(const float* x, int64_t n, int64_t d, double* out, const float* w, int64_t nf, const int32_t* smap,

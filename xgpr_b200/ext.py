@@ -99,6 +99,36 @@ def cudaRBFFeatureGen(inputArr, outputArr, radem, chiArr, fitIntercept):
     return 0
 
 
+def rbf_zv(inputArr, radem, chiArr, fitIntercept, v, t):
+    """t (n) += Z v with Z = cudaRBFFeatureGen(inputArr, ...) (column 0 = 1 when fitIntercept), Z never stored."""
+    x = _dev(inputArr, "inputArr", _SFX, 2)
+    r = _radem3(radem)
+    c = _dev(chiArr, "chiArr", _SFX, 1)
+    _same(x, c, "inputArr", "chiArr")
+    v = _dev(v, "v", (torch.float64,), 1)
+    t = _dev(t, "t", (torch.float64,), 1)
+    if v.shape[0] != 2 * c.shape[0] or t.shape[0] != x.shape[0]:
+        raise RuntimeError("wrong array sizes")
+    check(getattr(lib, "xgpr_b200_rbf_zv" + _SFX[x.dtype])(
+        x.data_ptr(), x.shape[0], x.shape[1], r.data_ptr(), r.shape[2], c.data_ptr(), c.shape[0],
+        int(bool(fitIntercept)), v.data_ptr(), t.data_ptr(), _stream()))
+
+
+def rbf_ztv(inputArr, radem, chiArr, fitIntercept, t, w):
+    """w (2F) += Z^T t, Z as in rbf_zv."""
+    x = _dev(inputArr, "inputArr", _SFX, 2)
+    r = _radem3(radem)
+    c = _dev(chiArr, "chiArr", _SFX, 1)
+    _same(x, c, "inputArr", "chiArr")
+    t = _dev(t, "t", (torch.float64,), 1)
+    w = _dev(w, "w", (torch.float64,), 1)
+    if w.shape[0] != 2 * c.shape[0] or t.shape[0] != x.shape[0]:
+        raise RuntimeError("wrong array sizes")
+    check(getattr(lib, "xgpr_b200_rbf_ztv" + _SFX[x.dtype])(
+        x.data_ptr(), x.shape[0], x.shape[1], r.data_ptr(), r.shape[2], c.data_ptr(), c.shape[0],
+        int(bool(fitIntercept)), t.data_ptr(), w.data_ptr(), _stream()))
+
+
 def cudaRBFGrad(inputArr, outputArr, gradArr, radem, chiArr, sigma, fitIntercept):
     x = _dev(inputArr, "inputArr", _SFX, 2)
     o = _dev(outputArr, "outputArr", (torch.float64,), 2)

@@ -141,11 +141,24 @@ def _device_of(kernel):
     return torch.device("cuda", torch.cuda.current_device()) if kernel.device == "cuda" else torch.device("cpu")
 
 
+def _fused_ok(kernel, ops):
+    """Fused featurise->matvec is offered by the fixed-vector SORF kernels on the CUDA path (<= 1024 inputs)."""
+    return ops is _cuda_ops and getattr(kernel, "supports_fused_matvec", False) and kernel.get_xdim()[-1] <= 1024
+
+
 def calc_zty(dataset, kernel, comm=None, ops=_cuda_ops):
     """z^T y and y^T y over the whole (sharded) dataset.  exact_nmll_calcs.py:13-38."""
     comm = comm or RowShardComm()
     dev = _device_of(kernel)
     z_trans_y, y_trans_y = _new((kernel.get_num_rffs(),), dev), _new((1,), dev)
+    if _fused_ok(kernel, ops):
+        from .kernels.base import to_device
+        for xin, yin, _ in dataset.get_chunked_data():
+            y = to_device(yin, torch.float64).contiguous()
+            kernel.fused_ztv(kernel.stage_scaled(xin), y, z_trans_y)
+            y_trans_y += y @ y
+        comm.all_reduce_(z_trans_y, y_trans_y)
+        return z_trans_y, float(y_trans_y[0])
     for xin, yin, ldata in dataset.get_chunked_data():
         z, y = kernel.transform_x_y(xin, yin, ldata)
         ops.zty_accum(z, y, z_trans_y)
@@ -222,6 +235,17 @@ class ConjugateGrad:
         all-reduced ONCE per call (one NCCL call per CG iteration); lambda^2 vec is added after it."""
         matvec.zero_()
         vec = vec.contiguous()
+        if _fused_ok(kernel, self.ops) and vec.shape[1] == 1:
+            # one right-hand side: two fused feature passes per chunk, Z never written to HBM
+            v1, w1 = vec[:, 0].contiguous(), matvec[:, 0]
+            for x, lengths in dataset.get_chunked_x_data():
+                xs = kernel.stage_scaled(x)
+                t = torch.zeros(xs.shape[0], dtype=torch.float64, device=xs.device)
+                kernel.fused_zv(xs, v1, t)
+                kernel.fused_ztv(xs, t, w1)
+            self.comm.all_reduce_(matvec)
+            matvec.add_(vec, alpha=kernel.get_lambda() ** 2)
+            return
         for x, lengths in dataset.get_chunked_x_data():
             z = kernel.transform_x(x, lengths)
             if self._scratch is None or self._scratch.shape[0] < z.shape[0] or self._scratch.shape[1] != vec.shape[1] \

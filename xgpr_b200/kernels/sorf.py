@@ -53,6 +53,23 @@ class SORFKernelBaseclass(KernelBaseclass):
         ext.cudaRBFFeatureGen(input_x, output_x, self.radem_diag, self.chi_arr, self.fit_intercept)
         return output_x
 
+    # ---- fused featurise -> matvec (xgpr_b200 extension of the plugin interface; Z is never materialised).
+    # Used by xgpr_b200.fitting for one right-hand side; equals transform_x(x) @ v / transform_x(x).T @ t.
+    supports_fused_matvec = True
+
+    def stage_scaled(self, input_x):
+        """The staged, sigma-scaled device copy that both fused passes of one chunk share."""
+        xin = self._stage_input(input_x)
+        if xin.shape[1] > 1024:
+            return None
+        return ext.scale_input_(xin, float(self.hyperparams[1]))
+
+    def fused_zv(self, xs, v, t):
+        ext.rbf_zv(xs, self.radem_diag, self.chi_arr, self.fit_intercept, v, t)
+
+    def fused_ztv(self, xs, t, w):
+        ext.rbf_ztv(xs, self.radem_diag, self.chi_arr, self.fit_intercept, t, w)
+
     def kernel_specific_gradient(self, input_x, sequence_length=None):
         output_x = torch.empty((input_x.shape[0], self.num_rffs), dtype=torch.float64, device=input_x.device)
         dz_dsigma = torch.empty((input_x.shape[0], self.num_rffs, 1), dtype=torch.float64, device=input_x.device)
