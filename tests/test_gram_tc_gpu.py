@@ -1,0 +1,96 @@
+"""GPU: the tensor-core Gram (xgpr_b200_ztz_accum_tc_f64: tcgen05 kind::i8 over exact int8 digit planes, int32 TMEM
+accumulators) against float64 NumPy for `xfeatures.T @ xfeatures` (reference: scoring_toolkit/exact_nmll_calcs.py:68-72).
+
+Bars, stated per test: inputs that are exactly representable in the digit planes -> BIT-EXACT; feature-shaped inputs ->
+|error| <= n * 2^(-7 s + 2) * colmax_i * colmax_j for s planes (6 planes: ~1e-12 of the column scale, i.e. the level of
+DGEMM's own rounding); fitted weights through the tensor-core Gram -> the north_star's 1e-6 against the reference
+fixture (tests/test_fitting_gpu.py runs with gram="tc" by default)."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _ext():
+    from xgpr_b200 import ext
+    return ext
+
+
+@pytest.mark.parametrize("shape", [(128, 256), (1, 8), (300, 200), (1000, 700), (4096, 1024), (777, 2049)])
+@pytest.mark.parametrize("slices", [3, 6, 7])
+def test_dyadic_inputs_bit_exact(shape, slices):
+    """Two-digit dyadic inputs: every product and partial sum is exact in int32 and in float64, so the tensor-core Gram
+    must equal the float64 Gram bit for bit, including accumulation over calls and the mirrored lower triangle."""
+    n, m = shape
+    rng = np.random.default_rng(n * 7 + m)
+    z = rng.integers(-8000, 8001, size=(n, m)).astype(np.float64) / 16384.0
+    ref = z.T @ z
+    ext = _ext()
+    zt = torch.from_numpy(z).to(DEV)
+    g = torch.zeros((m, m), dtype=torch.float64, device=DEV)
+    ext.ztz_accum_tc(zt, g, num_slices=slices)
+    assert np.array_equal(g.cpu().numpy(), ref)
+    ext.ztz_accum_tc(zt, g, num_slices=slices, mirror=False)      # accumulates; lower triangle untouched
+    got = g.cpu().numpy()
+    assert np.array_equal(np.triu(got), np.triu(2 * ref))
+    assert np.array_equal(np.tril(got, -1), np.tril(ref, -1))
+    ext.symmetrize_upper(g)
+    assert np.array_equal(g.cpu().numpy(), 2 * ref)
+
+
+@pytest.mark.parametrize("shape", [(2000, 2048), (5000, 1000), (333, 4100)])
+@pytest.mark.parametrize("slices", [4, 5, 6, 7])
+def test_feature_inputs_error_bound(shape, slices):
+    """Random-feature shaped Z (float32 cosines * scale, intercept column of ones)."""
+    n, m = shape
+    rng = np.random.default_rng(1)
+    z = np.cos(rng.standard_normal((n, m)) * 3).astype(np.float32).astype(np.float64) * np.sqrt(2.0 / m)
+    z[:, 0] = 1.0
+    ref = z.T @ z
+    ext = _ext()
+    g = torch.zeros((m, m), dtype=torch.float64, device=DEV)
+    ext.ztz_accum_tc(torch.from_numpy(z).to(DEV), g, num_slices=slices)
+    cmax = np.abs(z).max(axis=0)
+    bound = n * 2.0 ** (-7 * slices + 2) * cmax[:, None] * cmax[None, :] + 1e-15 * n * cmax[:, None] * cmax[None, :]
+    err = np.abs(g.cpu().numpy() - ref)
+    assert (err <= bound).all(), float((err / bound).max())
+    assert np.array_equal(g.cpu().numpy(), g.cpu().numpy().T)
+
+
+def test_row_passes_and_zero_columns():
+    """n above the int32 exactness cap (65536 rows per pass) takes several passes; an all-zero column is harmless."""
+    n, m = 70000, 300
+    rng = np.random.default_rng(2)
+    z = rng.integers(-100, 101, size=(n, m)).astype(np.float64) / 128.0
+    z[:, 5] = 0.0
+    ext = _ext()
+    g = torch.zeros((m, m), dtype=torch.float64, device=DEV)
+    ext.ztz_accum_tc(torch.from_numpy(z).to(DEV), g, num_slices=4)
+    assert np.array_equal(g.cpu().numpy(), z.T @ z)
+
+
+def test_matches_dfma_gram_on_large_tile_grid():
+    """Multi-wave schedule (more tiles than SMs, shared remainder tiles with atomic adds) vs the DFMA Gram kernel."""
+    n, m = 1024, 7000          # 28 x 28 tile grid -> 406 upper tiles on 148 SMs
+    torch.manual_seed(3)
+    z = torch.cos(torch.randn((n, m), device=DEV, dtype=torch.float64)) * (2.0 / m) ** 0.5
+    ext = _ext()
+    g0 = torch.zeros((m, m), dtype=torch.float64, device=DEV)
+    g1 = torch.zeros((m, m), dtype=torch.float64, device=DEV)
+    ext.ztz_accum(z, g0)
+    ext.ztz_accum_tc(z, g1, num_slices=7)
+    scale = float(g0.diagonal().max())
+    assert float((g0 - g1).abs().max()) <= 1e-13 * scale * 8
+
+
+def test_argument_errors():
+    ext = _ext()
+    z = torch.zeros((4, 8), dtype=torch.float64, device=DEV)
+    with pytest.raises(RuntimeError):
+        ext.ztz_accum_tc(z, torch.zeros((8, 7), dtype=torch.float64, device=DEV))
+    with pytest.raises(RuntimeError):
+        ext.ztz_accum_tc(z, torch.zeros((8, 8), dtype=torch.float64, device=DEV), num_slices=9)
+    with pytest.raises(TypeError):
+        ext.ztz_accum_tc(z.float(), torch.zeros((8, 8), dtype=torch.float64, device=DEV))

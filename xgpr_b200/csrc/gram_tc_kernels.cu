@@ -1,0 +1,515 @@
+// gram_tc_kernels.cu -- Z^T Z on the 5th-generation tensor cores (tcgen05.mma kind::i8, int32 accumulators in TMEM).
+//
+// Replaces the DGEMM behind `z_trans_z += xfeatures.T @ xfeatures`
+// (/root/reference/src/xGPR/scoring_toolkit/exact_nmll_calcs.py:68-72, also :35-38, :136-138 and
+// fitting_toolkit/exact_fitting_toolkit.py:16-36) for the fp64 feature matrix Z (n, m).
+//
+// Precision scheme ("split-int8", an Ozaki-style error-free slicing):
+//   1. per column j:  e_j = smallest integer with max_n |Z[n,j]| <= 2^(e_j - 1)
+//   2. x = Z[n,j] * 2^-e_j  (|x| <= 1/2, exact);  X = rint(x * 128^s);  X = sum_{k=1..s} d_k * 128^(s-k)
+//      with balanced digits d_k in [-64, 64]  ->  s int8 "slices" S_k, |x - sum_k d_k 128^-k| <= 2^(-7s-1)
+//   3. G[i,j] += 2^(e_i+e_j) * sum_{t=2..s+1} 128^-t * P_t[i,j],   P_t = sum_{k+l=t} S_k^T S_l
+//      Every P_t is an int8 x int8 -> int32 tensor-core GEMM (K = (t-1) * n, all pairs of one weight share one
+//      TMEM accumulator) and is EXACT: |d d'| <= 4096 and (t-1) * n <= 7 * 65536 keeps |P_t| < 2^31.
+//      Only the final scaling and the += into G round (fp64).
+//   Dropped pairs (k + l > s + 1) and the rounding of X bound the element error of the Gram update by
+//   ~ n * (s + 2) * 2^(-7s-2) * 2^(e_i+e_j):  s = 4: 1e-8, s = 5: 1e-10, s = 6 (default): 8e-13, s = 7: 7e-15
+//   relative to (column max)^2 per row -- s = 6 is at the level of the reference DGEMM's own rounding.
+//
+// Kernels: colmax -> slice (fp64 -> s int8 planes, transposed to K-major (m, n_pad)) -> persistent
+// warp-specialised tcgen05 GEMM (TMA producer warp / single-thread MMA issuer / 4 epilogue warps, 4-stage
+// 48 KB smem ring, double-buffered 128x256 int32 accumulators in TMEM, upper-triangle tiles only) -> mirror.
+#include "common.cuh"
+#include <cuda.h>
+
+namespace xb {
+
+constexpr int TC_BM = 128;          // UMMA M
+constexpr int TC_BN = 256;          // UMMA N
+constexpr int TC_TILE = 256;        // CTA output tile (rows and cols): two UMMA M = 128 accumulators
+constexpr int TC_BK = 128;          // K bytes per stage = one 128B swizzle atom row
+constexpr int TC_STAGES = 3;
+constexpr int TC_STAGE_BYTES = 2 * TC_TILE * TC_BK;  // A (256 x 128 B) + B (256 x 128 B) = 64 KB
+constexpr int TC_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int TC_EPI_WARPS = 8;
+constexpr int TC_THREADS = 64 + 32 * TC_EPI_WARPS;   // warp 0: TMA, warp 1: MMA, warps 2-9: epilogue
+constexpr int64_t TC_MAX_ROWS = 65536;   // int32 exactness bound for s <= 7
+
+// ------------------------------------------------------------------ column max |Z|  (bits of a non-negative double order as u64)
+__global__ void __launch_bounds__(256)
+tc_colmax_kernel(const double* __restrict__ z, int64_t n, int64_t m, unsigned long long* __restrict__ cmax,
+                 int64_t rows_per_block) {
+    const int64_t col = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (col >= m) return;
+    const int64_t n0 = (int64_t)blockIdx.y * rows_per_block;
+    const int64_t n1 = (n0 + rows_per_block < n) ? n0 + rows_per_block : n;
+    double mx = 0.0;
+    const double* p = z + n0 * m + col;
+#pragma unroll 8
+    for (int64_t r = n0; r < n1; ++r, p += m) mx = fmax(mx, fabs(*p));
+    atomicMax(cmax + col, (unsigned long long)__double_as_longlong(mx));
+}
+
+// exponent e with mx <= 2^(e-1); colscale = 2^e
+__global__ void tc_exponent_kernel(const unsigned long long* __restrict__ cmax, int64_t m, double* __restrict__ colscale) {
+    const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (col >= m) return;
+    const double mx = __longlong_as_double((long long)cmax[col]);
+    int q = 0;
+    if (mx > 0.0 && mx < 1e300) frexp(mx, &q);    // mx = f * 2^q, f in [0.5, 1)  =>  mx <= 2^q
+    colscale[col] = ldexp(1.0, q + 1);
+}
+
+// ------------------------------------------------------------------ fp64 -> s int8 digit planes, transposed
+// Tile: 128 rows (n) x 32 columns (m).  planes[k][col][row], row contiguous (K-major), row stride n_pad.
+template <int S>
+__global__ void __launch_bounds__(256)
+tc_slice_kernel(const double* __restrict__ z, int64_t n, int64_t m, int64_t n_pad,
+                const double* __restrict__ colscale, int8_t* __restrict__ planes) {
+    constexpr int LD = 132;   // bytes per (plane, col) row in smem: 33 words -> conflict-free transposed byte stores
+    __shared__ __align__(16) int8_t dig[S][32][LD];
+    const int64_t m0 = (int64_t)blockIdx.x * 32, n0 = (int64_t)blockIdx.y * 128;
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    const int64_t col = m0 + lane;
+    // multiply by 2^(7S) / colscale: both powers of two, product exact
+    const double mul = (col < m) ? ldexp(1.0 / colscale[col], 7 * S) : 0.0;
+#pragma unroll 4
+    for (int r = 0; r < 16; ++r) {
+        const int row = r * 8 + wrp;
+        const int64_t gr = n0 + row;
+        double v = 0.0;
+        if (gr < n && col < m) v = z[gr * m + col];
+        long long X = __double2ll_rn(v * mul);
+#pragma unroll
+        for (int k = S - 1; k >= 1; --k) {
+            const long long d = ((X + 64) & 127) - 64;      // balanced digit in [-64, 63]
+            dig[k][lane][row] = (int8_t)d;
+            X = (X - d) >> 7;
+        }
+        X = X > 64 ? 64 : (X < -64 ? -64 : X);              // |X| <= 64 by construction; clamp guards Inf/NaN input
+        dig[0][lane][row] = (int8_t)X;
+    }
+    __syncthreads();
+    const int64_t plane_stride = m * n_pad;
+#pragma unroll
+    for (int k = 0; k < S; ++k) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int idx = i * 256 + threadIdx.x;          // 32 cols x 32 words
+            const int c = idx >> 5, w = idx & 31;
+            if (m0 + c < m) {
+                const uint32_t val = *reinterpret_cast<const uint32_t*>(&dig[k][c][w * 4]);
+                *reinterpret_cast<uint32_t*>(planes + k * plane_stride + (m0 + c) * n_pad + n0 + w * 4) = val;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ PTX wrappers (sm_100a)
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok;
+}
+// Bounded spin: a protocol bug traps (launch error) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if (++spins > (1u << 28)) __trap();
+    }
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after()  { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc], int8 x int8 -> int32, M = 128, N = 256, K = 32
+__device__ __forceinline__ void tc_mma_i8(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+// K-major operand tile, 128-byte rows, SWIZZLE_128B: 8-row groups 1024 B apart (SBO), LBO unused, descriptor version 1.
+__device__ __forceinline__ uint64_t tc_smem_desc(uint32_t addr) {
+    return (uint64_t)((addr & 0x3FFFFu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::i8 instruction descriptor: D = S32 (bits 4-5 = 2), A = B = signed int8 (bits 7-9, 10-12 = 1), both K-major,
+// N >> 3 at bits 17-22, M >> 4 at bits 24-28.
+constexpr uint32_t TC_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// linear upper-tile index -> (ti, tj), ti <= tj < tiles
+__device__ __forceinline__ void tc_tile_coords(int lin, int tiles, int& ti, int& tj) {
+    ti = 0;
+    while (lin >= tiles - ti) { lin -= tiles - ti; ++ti; }
+    tj = ti + lin;
+}
+
+// ------------------------------------------------------------------ the GEMM
+// planes: tensor map over int8 [S][m][n_pad] (dims innermost-first {n_pad, m, S}), box {128, 128, 1}, SWIZZLE_128B.
+// Work is cut into segments (256 x 256 upper-triangle tile, K-block range).  CTA b of G first takes whole tiles
+// b, b + G, ... (full waves), then the remaining R < G tiles are shared: their R * n_kblocks K blocks are cut into G equal
+// contiguous ranges (<= 2 segments per CTA), so there is no wave quantisation and every CTA walks the same
+// (weight group g descending, plane k ascending, K ascending) sequence at the same time -- that phase coherence is what
+// keeps the shared plane tiles L2-resident (a de-phased schedule measured 25 % slower).
+// Per segment and weight group g = k + l (0-based) the g + 1 plane pairs (k, g - k) are summed into two 128 x 256
+// int32 TMEM accumulators (tile rows 0-127 / 128-255, all 512 TMEM columns); the epilogue scales by
+// 2^(e_i + e_j - 7 (g + 2)) and adds into G: plain += for whole-tile segments (deterministic), red.add.f64 for the shared ones.
+// Per 128-byte K block: 64 KB of operands for 2 x 4 MMAs (1024 tensor-pipe cycles) = 64 B/clk/SM of smem fill, which
+// is what bounds this kernel (the int8 pipe outruns L2), hence the large tile.
+struct TcSched {
+    int num_slices, n_kblocks, tiles, num_tiles, full_waves, split_remainder;
+};
+struct TcSeg { int tile, kb0, kb1; };
+
+// segment i (0 <= i < full_waves + 2) of CTA b; kb1 <= kb0 means empty
+__device__ __forceinline__ TcSeg tc_segment(const TcSched& sc, int i, int b, int G) {
+    TcSeg sg;
+    if (i < sc.full_waves) { sg.tile = b + i * G; sg.kb0 = 0; sg.kb1 = sc.n_kblocks; return sg; }
+    const int first = sc.full_waves * G, R = sc.num_tiles - first;
+    if (!sc.split_remainder) {       // remainder as whole tiles on the first R CTAs
+        sg.tile = first + b; sg.kb0 = 0;
+        sg.kb1 = (i == sc.full_waves && b < R) ? sc.n_kblocks : 0;
+        return sg;
+    }
+    const long long RB = (long long)R * sc.n_kblocks;
+    const long long lo = RB * b / G, hi = RB * (b + 1) / G;
+    const int t0 = (int)(lo / sc.n_kblocks);
+    const long long t0_end = (long long)(t0 + 1) * sc.n_kblocks;
+    if (i == sc.full_waves) {
+        sg.tile = first + t0;
+        sg.kb0 = (int)(lo - (long long)t0 * sc.n_kblocks);
+        sg.kb1 = (int)((hi < t0_end ? hi : t0_end) - (long long)t0 * sc.n_kblocks);
+    } else {
+        sg.tile = first + t0 + 1;
+        sg.kb0 = 0;
+        sg.kb1 = (hi > t0_end) ? (int)(hi - t0_end) : 0;
+    }
+    if (sg.tile >= sc.num_tiles) sg.kb1 = sg.kb0 = 0;
+    return sg;
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+tc_gram_kernel(const __grid_constant__ CUtensorMap planes_map, const TcSched sc, int64_t m,
+               const double* __restrict__ colscale, double* __restrict__ g_out) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_base = smem_base + TC_STAGES * TC_STAGE_BYTES;
+    // barrier slots (8 B each): full[stages], empty[stages], tmem_full, tmem_empty, then the TMEM base address
+    auto full_bar   = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar  = [&](int s) { return bar_base + 8u * (TC_STAGES + s); };
+    const uint32_t tfull_bar = bar_base + 8u * (2 * TC_STAGES);
+    const uint32_t tempty_bar = bar_base + 8u * (2 * TC_STAGES + 1);
+    const uint32_t tmem_slot = bar_base + 8u * (2 * TC_STAGES + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < TC_STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        mbar_init(tfull_bar, 1);
+        mbar_init(tempty_bar, TC_EPI_WARPS);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&planes_map) : "memory");
+    }
+    if (warp == 1) {   // TMEM: all 512 columns = two 128 x 256 int32 accumulators
+        const uint32_t ncols = 512;
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(ncols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+    if (warp == 0) {
+        // ---------------------------------------------------------------- TMA producer
+        if (lane == 0) {
+            uint32_t ks = 0;
+            for (int si = 0; si < sc.full_waves + 2; ++si) {
+                const TcSeg sg = tc_segment(sc, si, blockIdx.x, gridDim.x);
+                if (sg.kb1 <= sg.kb0) continue;
+                int ti, tj;
+                tc_tile_coords(sg.tile, sc.tiles, ti, tj);
+                for (int g = sc.num_slices - 1; g >= 0; --g) {
+                    for (int k = 0; k <= g; ++k) {
+                        const int l = g - k;
+                        for (int kb = sg.kb0; kb < sg.kb1; ++kb, ++ks) {
+                            const int st = ks % TC_STAGES;
+                            mbar_wait(empty_bar(st), ((ks / TC_STAGES) & 1) ^ 1);
+                            const uint32_t dst = smem_base + st * TC_STAGE_BYTES;
+                            mbar_expect_tx(full_bar(st), TC_STAGE_BYTES);
+                            tma_load_3d(dst,             &planes_map, full_bar(st), kb * TC_BK, ti * TC_TILE,       k);
+                            tma_load_3d(dst + 16384,     &planes_map, full_bar(st), kb * TC_BK, ti * TC_TILE + 128, k);
+                            tma_load_3d(dst + 2 * 16384, &planes_map, full_bar(st), kb * TC_BK, tj * TC_TILE,       l);
+                            tma_load_3d(dst + 3 * 16384, &planes_map, full_bar(st), kb * TC_BK, tj * TC_TILE + 128, l);
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ---------------------------------------------------------------- MMA issuer (one thread)
+        if (lane == 0) {
+            uint32_t ks = 0, it = 0;
+            for (int si = 0; si < sc.full_waves + 2; ++si) {
+                const TcSeg sg = tc_segment(sc, si, blockIdx.x, gridDim.x);
+                if (sg.kb1 <= sg.kb0) continue;
+                for (int g = sc.num_slices - 1; g >= 0; --g, ++it) {
+                    mbar_wait(tempty_bar, (it & 1) ^ 1);                 // epilogue has drained the accumulators
+                    tc_fence_after();
+                    const int nblk = (g + 1) * (sg.kb1 - sg.kb0);
+                    for (int b = 0; b < nblk; ++b, ++ks) {
+                        const int st = ks % TC_STAGES;
+                        mbar_wait(full_bar(st), (ks / TC_STAGES) & 1);
+                        tc_fence_after();
+                        const uint32_t a_addr = smem_base + st * TC_STAGE_BYTES;
+                        const uint64_t da0 = tc_smem_desc(a_addr), da1 = tc_smem_desc(a_addr + 16384),
+                                       db = tc_smem_desc(a_addr + 2 * 16384);
+#pragma unroll
+                        for (int kk = 0; kk < TC_BK / 32; ++kk) {      // 32-byte K steps inside the 128B swizzle row
+                            const uint32_t accum = (b > 0 || kk > 0) ? 1u : 0u;
+                            tc_mma_i8(tmem_base,        da0 + (uint64_t)(kk * 2), db + (uint64_t)(kk * 2), TC_IDESC, accum);
+                            tc_mma_i8(tmem_base + 256u, da1 + (uint64_t)(kk * 2), db + (uint64_t)(kk * 2), TC_IDESC, accum);
+                        }
+                        tc_commit(empty_bar(st));                       // smem slot free once these MMAs retire
+                    }
+                    tc_commit(tfull_bar);                               // accumulators complete
+                }
+            }
+        }
+    } else {
+        // ---------------------------------------------------------------- epilogue: TMEM -> fp64 -> G (upper triangle) +=
+        const int quad = warp & 3;                      // TMEM lane quadrant this warp may read
+        const int half = (warp - 2) >> 2;               // which accumulator (tile rows 0-127 / 128-255)
+        uint32_t it = 0;
+        for (int si = 0; si < sc.full_waves + 2; ++si) {
+            const TcSeg sg = tc_segment(sc, si, blockIdx.x, gridDim.x);
+            if (sg.kb1 <= sg.kb0) continue;
+            int ti, tj;
+            tc_tile_coords(sg.tile, sc.tiles, ti, tj);
+            const bool owned = (sg.kb0 == 0 && sg.kb1 == sc.n_kblocks);
+            const int64_t wrow0 = (int64_t)ti * TC_TILE + half * 128 + quad * 32;
+            const int64_t row = wrow0 + lane;
+            const int64_t col0 = (int64_t)tj * TC_TILE;
+            const double rs = (row < m) ? colscale[row] : 0.0;
+            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 256);
+            for (int g = sc.num_slices - 1; g >= 0; --g, ++it) {
+                mbar_wait(tfull_bar, it & 1);
+                tc_fence_after();
+                const double rsg = rs * exp2(-7.0 * (g + 2));     // exact power of two
+#pragma unroll 1
+                for (int c = 0; c < TC_TILE / 32; ++c) {
+                    const int64_t cb = col0 + c * 32;
+                    if (cb + 31 < wrow0 || cb >= m || wrow0 >= m) continue;      // warp-uniform: below the diagonal / outside
+                    uint32_t acc[32];
+                    tmem_ld32(taddr + c * 32, acc);
+                    tmem_ld_wait();
+                    if (row < m) {
+                        double* gp = g_out + row * m + cb;
+#pragma unroll
+                        for (int uu = 0; uu < 32; ++uu) {
+                            const int64_t col = cb + uu;
+                            if (col < m && col >= row) {
+                                const double v = (double)(int)acc[uu] * (rsg * __ldg(colscale + col));
+                                if (owned) gp[uu] += v;
+                                else atomicAdd(gp + uu, v);
+                            }
+                        }
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(tempty_bar);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        const uint32_t ncols = 512;
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(ncols) : "memory");
+    }
+}
+
+// ------------------------------------------------------------------ lower triangle <- upper triangle (32 x 32 tiles through smem)
+__global__ void __launch_bounds__(256)
+tc_mirror_kernel(double* __restrict__ g, int64_t m) {
+    if (blockIdx.y > blockIdx.x) return;           // (by, bx) with by <= bx: upper tile (rows by, cols bx)
+    __shared__ double t[32][33];
+    const int64_t r0 = (int64_t)blockIdx.y * 32, c0 = (int64_t)blockIdx.x * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int i = ty; i < 32; i += 8)
+        if (r0 + i < m && c0 + tx < m) t[i][tx] = g[(r0 + i) * m + c0 + tx];
+    __syncthreads();
+    for (int i = ty; i < 32; i += 8) {
+        const int64_t rr = c0 + i, cc = r0 + tx;       // lower element (rr, cc) = upper element (cc, rr)
+        if (rr < m && cc < m && rr > cc) g[rr * m + cc] = t[tx][i];
+    }
+}
+
+// ------------------------------------------------------------------ host
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    }
+    return fn;
+}
+
+static inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+
+// workspace: [cmax u64 (m)] [colscale f64 (m)] [planes int8 (S, m, n_pad)], each region 1024-byte aligned
+static inline int64_t tc_rows_per_pass(int64_t n) { return n < TC_MAX_ROWS ? n : TC_MAX_ROWS; }
+
+int64_t ztz_tc_workspace_bytes(int64_t n, int64_t m, int num_slices) {
+    if (n <= 0 || m <= 0 || num_slices < 2 || num_slices > 7) return -1;
+    const int64_t n_pad = round_up(tc_rows_per_pass(n), TC_BK);
+    return round_up(m * 8, 1024) * 2 + round_up((int64_t)num_slices * m * n_pad, 1024);
+}
+
+template <int S>
+static void launch_slice(const double* z, int64_t n, int64_t m, int64_t n_pad, const double* cs, int8_t* planes,
+                         cudaStream_t st) {
+    dim3 grid((unsigned)((m + 31) / 32), (unsigned)(n_pad / 128));
+    tc_slice_kernel<S><<<grid, 256, 0, st>>>(z, n, m, n_pad, cs, planes);
+}
+
+int ztz_accum_tc(const double* z, int64_t n, int64_t m, double* ztz, int num_slices, int mirror, void* workspace,
+                 int64_t workspace_bytes, cudaStream_t st) {
+    XB_REQUIRE(n > 0 && m > 0, "no datapoints");
+    XB_REQUIRE(z && ztz && workspace, "null pointer");
+    XB_REQUIRE(num_slices >= 2 && num_slices <= 7, "num_slices must be in [2, 7]");
+    XB_REQUIRE(workspace_bytes >= ztz_tc_workspace_bytes(n, m, num_slices), "workspace too small");
+    XB_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+    EncodeTiledFn encode = encode_tiled_fn();
+    if (!encode) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return XGPR_B200_ECUDA; }
+
+    static int smem_set = 0;
+    if (!smem_set) {
+        if (cudaFuncSetAttribute(tc_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES) != cudaSuccess)
+            return check_launch("tc_gram_kernel smem attribute");
+        smem_set = 1;
+    }
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+
+    uint8_t* ws = (uint8_t*)workspace;
+    unsigned long long* cmax = (unsigned long long*)ws;
+    double* colscale = (double*)(ws + round_up(m * 8, 1024));
+    int8_t* planes = (int8_t*)(ws + 2 * round_up(m * 8, 1024));
+
+    const int tiles = (int)((m + TC_TILE - 1) / TC_TILE);
+    const int num_tiles = tiles * (tiles + 1) / 2;
+
+    for (int64_t r0 = 0; r0 < n; r0 += TC_MAX_ROWS) {
+        const int64_t rows = (n - r0 < TC_MAX_ROWS) ? (n - r0) : TC_MAX_ROWS;
+        const int64_t n_pad = round_up(rows, TC_BK);
+        const double* zc = z + r0 * m;
+        cudaMemsetAsync(cmax, 0, m * 8, st);
+        {
+            const int64_t colblocks = (m + 255) / 256;
+            int64_t splits = (sms * 8 + colblocks - 1) / colblocks;
+            int64_t rows_per = (rows + splits - 1) / splits;
+            if (rows_per < 16) rows_per = 16;
+            splits = (rows + rows_per - 1) / rows_per;
+            dim3 grid((unsigned)colblocks, (unsigned)splits);
+            tc_colmax_kernel<<<grid, 256, 0, st>>>(zc, rows, m, cmax, rows_per);
+            tc_exponent_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(cmax, m, colscale);
+        }
+        switch (num_slices) {
+            case 2: launch_slice<2>(zc, rows, m, n_pad, colscale, planes, st); break;
+            case 3: launch_slice<3>(zc, rows, m, n_pad, colscale, planes, st); break;
+            case 4: launch_slice<4>(zc, rows, m, n_pad, colscale, planes, st); break;
+            case 5: launch_slice<5>(zc, rows, m, n_pad, colscale, planes, st); break;
+            case 6: launch_slice<6>(zc, rows, m, n_pad, colscale, planes, st); break;
+            default: launch_slice<7>(zc, rows, m, n_pad, colscale, planes, st); break;
+        }
+        CUtensorMap map;
+        const cuuint64_t gdim[3] = {(cuuint64_t)n_pad, (cuuint64_t)m, (cuuint64_t)num_slices};
+        const cuuint64_t gstride[2] = {(cuuint64_t)n_pad, (cuuint64_t)(m * n_pad)};
+        const cuuint32_t box[3] = {TC_BK, 128, 1};
+        const cuuint32_t estr[3] = {1, 1, 1};
+        const CUresult cr = encode(&map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, planes, gdim, gstride, box, estr,
+                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (cr != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d)", (int)cr); return XGPR_B200_ECUDA; }
+        TcSched sc;
+        sc.num_slices = num_slices;
+        sc.n_kblocks = (int)(n_pad / TC_BK);
+        sc.tiles = tiles;
+        sc.num_tiles = num_tiles;
+        // grid: all SMs, unless the whole problem has fewer K blocks than that
+        long long grid = (long long)num_tiles * sc.n_kblocks;
+        if (grid > sms) grid = sms;
+        sc.full_waves = num_tiles / (int)grid;
+        // Sharing the last partial wave's tiles along K balances the SMs but de-phases their K sweeps (less L2 reuse of
+        // the shared row blocks): measured to pay off only when that wave would leave > 1/4 of the SMs idle.
+        const int rem = num_tiles - sc.full_waves * (int)grid;
+        sc.split_remainder = (rem > 0 && rem * 4 < (int)grid * 3) ? 1 : 0;
+        tc_gram_kernel<<<(unsigned)grid, TC_THREADS, TC_SMEM_BYTES, st>>>(map, sc, m, colscale, ztz);
+        count_launch(4);
+        const int rc = check_launch("tc_gram_kernel");
+        if (rc != XGPR_B200_OK) return rc;
+    }
+    if (mirror) {
+        const unsigned nb = (unsigned)((m + 31) / 32);
+        tc_mirror_kernel<<<dim3(nb, nb), 256, 0, st>>>(ztz, m);
+        count_launch();
+    }
+    return check_launch("ztz_accum_tc");
+}
+
+int symmetrize_upper(double* g, int64_t m, cudaStream_t st) {
+    XB_REQUIRE(g && m > 0, "null pointer");
+    const unsigned nb = (unsigned)((m + 31) / 32);
+    tc_mirror_kernel<<<dim3(nb, nb), 256, 0, st>>>(g, m);
+    count_launch();
+    return check_launch("tc_mirror_kernel");
+}
+
+}  // namespace xb

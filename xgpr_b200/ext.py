@@ -228,6 +228,35 @@ def ztz_accum(z, ztz):
     check(lib.xgpr_b200_ztz_accum_f64(z.data_ptr(), z.shape[0], z.shape[1], ztz.data_ptr(), _stream()))
 
 
+_TC_WORKSPACE = {}
+
+
+def ztz_accum_tc(z, ztz, num_slices=6, mirror=True):
+    """Upper triangle of ztz += z^T z on the tensor cores (tcgen05 kind::i8 over `num_slices` exact int8 digit planes,
+    int32 accumulation in TMEM; csrc/gram_tc_kernels.cu).  mirror=True also refreshes the lower triangle."""
+    z = _dev(z, "z", (torch.float64,), 2)
+    ztz = _dev(ztz, "ztz", (torch.float64,), 2)
+    if ztz.shape[0] != z.shape[1] or ztz.shape[1] != z.shape[1]:
+        raise RuntimeError("wrong array sizes")
+    need = lib.xgpr_b200_ztz_tc_workspace_bytes(z.shape[0], z.shape[1], int(num_slices))
+    if need < 0:
+        raise RuntimeError("num_slices must be in [2, 7]")
+    key = (z.device.index, torch.cuda.current_stream().cuda_stream)
+    ws = _TC_WORKSPACE.get(key)
+    if ws is None or ws.numel() < need:          # grow-only per (device, stream): no allocation in steady state
+        ws = torch.empty(need, dtype=torch.uint8, device=z.device)
+        _TC_WORKSPACE[key] = ws
+    check(lib.xgpr_b200_ztz_accum_tc_f64(z.data_ptr(), z.shape[0], z.shape[1], ztz.data_ptr(), int(num_slices),
+                                         1 if mirror else 0, ws.data_ptr(), ws.numel(), _stream()))
+
+
+def symmetrize_upper(g):
+    g = _dev(g, "g", (torch.float64,), 2)
+    if g.shape[0] != g.shape[1]:
+        raise RuntimeError("wrong array sizes")
+    check(lib.xgpr_b200_symmetrize_upper_f64(g.data_ptr(), g.shape[0], _stream()))
+
+
 def atb_accum(a, z, acc):
     """acc (r, m) += a^T z ; a (n, r) may be a strided view (it is made contiguous), z (n, m)."""
     a = _dev(a.contiguous(), "a", (torch.float64,), 2)

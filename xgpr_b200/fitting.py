@@ -167,17 +167,30 @@ def calc_zty(dataset, kernel, comm=None, ops=_cuda_ops):
     return z_trans_y, float(y_trans_y[0])
 
 
-def calc_design_mat(dataset, kernel, comm=None, ops=_cuda_ops):
+def _gram_accumulator(ops, gram, gram_slices):
+    """Returns (accumulate(z, ztz), finish(ztz)).  gram="tc": tensor-core split-int8 Gram (tcgen05, exact int32
+    accumulation of `gram_slices` digit planes, csrc/gram_tc_kernels.cu), upper triangle per chunk and one mirror at the
+    end; gram="f64": the DFMA kernel.  Providers without the tensor-core entry point (the CPU test provider) use f64."""
+    if gram == "tc" and hasattr(ops, "ztz_accum_tc"):
+        return (lambda z, ztz: ops.ztz_accum_tc(z, ztz, num_slices=gram_slices, mirror=False)), ops.symmetrize_upper
+    if gram not in ("tc", "f64"):
+        raise ValueError("gram must be 'tc' or 'f64'")
+    return ops.ztz_accum, (lambda ztz: None)
+
+
+def calc_design_mat(dataset, kernel, comm=None, ops=_cuda_ops, gram="tc", gram_slices=6):
     """z^T z, z^T y, y^T y.  exact_nmll_calcs.py:42-78; one all-reduce of the M x M Gram per pass."""
     comm = comm or RowShardComm()
     dev = _device_of(kernel)
     m = kernel.get_num_rffs()
     z_trans_z, z_trans_y, y_trans_y = _new((m, m), dev), _new((m,), dev), _new((1,), dev)
+    accumulate, finish = _gram_accumulator(ops, gram, gram_slices)
     for xin, yin, ldata in dataset.get_chunked_data():
         z, y = kernel.transform_x_y(xin, yin, ldata)
         ops.zty_accum(z, y, z_trans_y)
-        ops.ztz_accum(z, z_trans_z)
+        accumulate(z, z_trans_z)
         y_trans_y += y @ y
+    finish(z_trans_z)
     comm.all_reduce_(z_trans_z)
     comm.all_reduce_(z_trans_y, y_trans_y)
     return z_trans_z, z_trans_y, float(y_trans_y[0])
@@ -193,23 +206,25 @@ def direct_weight_calc(chol_z_trans_z, z_trans_y, kernel):
     return chol, w[:, 0]
 
 
-def calc_weights_exact(dataset, kernel, comm=None, ops=_cuda_ops):
+def calc_weights_exact(dataset, kernel, comm=None, ops=_cuda_ops, gram="tc", gram_slices=6):
     """exact_fitting_toolkit.py:16-36.  lambda^2 is added here AND inside direct_weight_calc, exactly as
     the reference does: the exact fit solves (Z^T Z + 2 lambda^2 I) w = Z^T y."""
-    z_trans_z, z_trans_y, _ = calc_design_mat(dataset, kernel, comm, ops)
+    z_trans_z, z_trans_y, _ = calc_design_mat(dataset, kernel, comm, ops, gram, gram_slices)
     lambda_p = kernel.get_hyperparams(logspace=False)[0]
     z_trans_z.diagonal().add_(lambda_p ** 2)
     _, weights = direct_weight_calc(z_trans_z, z_trans_y, kernel)
     return weights, 1, []
 
 
-def calc_var_design_mat(dataset, kernel, variance_rffs, comm=None, ops=_cuda_ops):
+def calc_var_design_mat(dataset, kernel, variance_rffs, comm=None, ops=_cuda_ops, gram="tc", gram_slices=6):
     """exact_nmll_calcs.py:116-139: Gram of the first variance_rffs columns."""
     comm = comm or RowShardComm()
     z_trans_z = _new((variance_rffs, variance_rffs), _device_of(kernel))
+    accumulate, finish = _gram_accumulator(ops, gram, gram_slices)
     for xdata, ldata in dataset.get_chunked_x_data():
         z = kernel.transform_x(xdata, ldata)
-        ops.ztz_accum(z[:, :variance_rffs].contiguous(), z_trans_z)
+        accumulate(z[:, :variance_rffs].contiguous(), z_trans_z)
+    finish(z_trans_z)
     comm.all_reduce_(z_trans_z)
     return z_trans_z
 
