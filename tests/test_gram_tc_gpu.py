@@ -94,3 +94,30 @@ def test_argument_errors():
         ext.ztz_accum_tc(z, torch.zeros((8, 8), dtype=torch.float64, device=DEV), num_slices=9)
     with pytest.raises(TypeError):
         ext.ztz_accum_tc(z.float(), torch.zeros((8, 8), dtype=torch.float64, device=DEV))
+
+
+@pytest.mark.parametrize("shape", [(300, 64, 200), (4096, 512, 1024), (1000, 300, 2049), (70000, 16, 40)])
+def test_atb_dyadic_bit_exact(shape):
+    """acc (r, m) += A^T Z on the tensor cores (rand_nys_constructors.py:119), exactly representable inputs."""
+    n, r, m = shape
+    rng = np.random.default_rng(n + r + m)
+    a = rng.integers(-8000, 8001, size=(n, r)).astype(np.float64) / 16384.0
+    z = rng.integers(-100, 101, size=(n, m)).astype(np.float64) / 128.0
+    ext = _ext()
+    acc = torch.zeros((r, m), dtype=torch.float64, device=DEV)
+    ext.atb_accum_tc(torch.from_numpy(a).to(DEV), torch.from_numpy(z).to(DEV), acc, num_slices=4)
+    assert np.array_equal(acc.cpu().numpy(), a.T @ z)
+    ext.atb_accum_tc(torch.from_numpy(a).to(DEV), torch.from_numpy(z).to(DEV), acc, num_slices=4)
+    assert np.array_equal(acc.cpu().numpy(), 2 * (a.T @ z))
+
+
+def test_atb_general_error_bound():
+    n, r, m = 3000, 512, 4096
+    rng = np.random.default_rng(5)
+    a = rng.standard_normal((n, r))
+    z = np.cos(rng.standard_normal((n, m)) * 3) * np.sqrt(2.0 / m)
+    ext = _ext()
+    acc = torch.zeros((r, m), dtype=torch.float64, device=DEV)
+    ext.atb_accum_tc(torch.from_numpy(a).to(DEV), torch.from_numpy(z).to(DEV), acc, num_slices=6)
+    bound = n * 2.0 ** (-40) * np.abs(a).max(axis=0)[:, None] * np.abs(z).max(axis=0)[None, :]
+    assert (np.abs(acc.cpu().numpy() - a.T @ z) <= bound).all()

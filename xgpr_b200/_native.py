@@ -38,6 +38,7 @@ F64_ONLY = {
     "xgpr_b200_ztz_accum_f64": [_ptr, _i64, _i64, _ptr, _ptr],
     "xgpr_b200_ztz_accum_tc_f64": [_ptr, _i64, _i64, _ptr, _int, _int, _ptr, _i64, _ptr],
     "xgpr_b200_symmetrize_upper_f64": [_ptr, _i64, _ptr],
+    "xgpr_b200_atb_accum_tc_f64": [_ptr, _ptr, _i64, _i64, _i64, _ptr, _int, _ptr, _i64, _ptr],
     "xgpr_b200_atb_accum_f64": [_ptr, _ptr, _i64, _i64, _i64, _ptr, _ptr],
     "xgpr_b200_cg_matvec_accum_f64": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _ptr, _ptr],
 }
@@ -58,6 +59,9 @@ for _name, _args in F64_ONLY.items():
 lib.xgpr_b200_ztz_tc_workspace_bytes.argtypes = [_i64, _i64, _int]
 lib.xgpr_b200_ztz_tc_workspace_bytes.restype = _i64
 EXPORTED.append("xgpr_b200_ztz_tc_workspace_bytes")
+lib.xgpr_b200_atb_tc_workspace_bytes.argtypes = [_i64, _i64, _i64, _int]
+lib.xgpr_b200_atb_tc_workspace_bytes.restype = _i64
+EXPORTED.append("xgpr_b200_atb_tc_workspace_bytes")
 lib.xgpr_b200_abi_version.restype = _int
 lib.xgpr_b200_last_error.restype = ctypes.c_char_p
 lib.xgpr_b200_launch_count.restype = _i64

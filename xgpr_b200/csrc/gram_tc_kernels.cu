@@ -172,12 +172,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-// linear upper-tile index -> (ti, tj), ti <= tj < tiles
-__device__ __forceinline__ void tc_tile_coords(int lin, int tiles, int& ti, int& tj) {
-    ti = 0;
-    while (lin >= tiles - ti) { lin -= tiles - ti; ++ti; }
-    tj = ti + lin;
-}
+
 
 // ------------------------------------------------------------------ the GEMM
 // planes: tensor map over int8 [S][m][n_pad] (dims innermost-first {n_pad, m, S}), box {128, 128, 1}, SWIZZLE_128B.
@@ -192,9 +187,21 @@ __device__ __forceinline__ void tc_tile_coords(int lin, int tiles, int& ti, int&
 // Per 128-byte K block: 64 KB of operands for 2 x 4 MMAs (1024 tensor-pipe cycles) = 64 B/clk/SM of smem fill, which
 // is what bounds this kernel (the int8 pipe outruns L2), hence the large tile.
 struct TcSched {
-    int num_slices, n_kblocks, tiles, num_tiles, full_waves, split_remainder;
+    int num_slices, n_kblocks, tiles, num_tiles, full_waves, split_remainder, symmetric;
 };
 struct TcSeg { int tile, kb0, kb1; };
+
+// linear tile index -> (ti, tj): symmetric = upper triangle (ti <= tj < tiles), else row-major over tiles_i x tiles
+__device__ __forceinline__ void tc_tile_coords(const TcSched& sc, int lin, int& ti, int& tj) {
+    if (sc.symmetric) {
+        ti = 0;
+        while (lin >= sc.tiles - ti) { lin -= sc.tiles - ti; ++ti; }
+        tj = ti + lin;
+    } else {
+        ti = lin / sc.tiles;
+        tj = lin - ti * sc.tiles;
+    }
+}
 
 // segment i (0 <= i < full_waves + 2) of CTA b; kb1 <= kb0 means empty
 __device__ __forceinline__ TcSeg tc_segment(const TcSched& sc, int i, int b, int G) {
@@ -224,8 +231,11 @@ __device__ __forceinline__ TcSeg tc_segment(const TcSched& sc, int i, int b, int
 }
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
-tc_gram_kernel(const __grid_constant__ CUtensorMap planes_map, const TcSched sc, int64_t m,
-               const double* __restrict__ colscale, double* __restrict__ g_out) {
+tc_gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const TcSched sc,
+               int64_t ma, int64_t mb, const double* __restrict__ scale_a, const double* __restrict__ scale_b,
+               double* __restrict__ g_out) {
+    // C (ma, mb) += A^T B with A = planes behind map_a (ma columns of the fp64 operand), B behind map_b.
+    // sc.symmetric: A == B, only tiles on or above the diagonal, only elements col >= row are written.
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t bar_base = smem_base + TC_STAGES * TC_STAGE_BYTES;
@@ -243,7 +253,8 @@ tc_gram_kernel(const __grid_constant__ CUtensorMap planes_map, const TcSched sc,
         mbar_init(tfull_bar, 1);
         mbar_init(tempty_bar, TC_EPI_WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("prefetch.tensormap [%0];" ::"l"(&planes_map) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
     }
     if (warp == 1) {   // TMEM: all 512 columns = two 128 x 256 int32 accumulators
         const uint32_t ncols = 512;
@@ -264,7 +275,7 @@ tc_gram_kernel(const __grid_constant__ CUtensorMap planes_map, const TcSched sc,
                 const TcSeg sg = tc_segment(sc, si, blockIdx.x, gridDim.x);
                 if (sg.kb1 <= sg.kb0) continue;
                 int ti, tj;
-                tc_tile_coords(sg.tile, sc.tiles, ti, tj);
+                tc_tile_coords(sc, sg.tile, ti, tj);
                 for (int g = sc.num_slices - 1; g >= 0; --g) {
                     for (int k = 0; k <= g; ++k) {
                         const int l = g - k;
@@ -273,10 +284,10 @@ tc_gram_kernel(const __grid_constant__ CUtensorMap planes_map, const TcSched sc,
                             mbar_wait(empty_bar(st), ((ks / TC_STAGES) & 1) ^ 1);
                             const uint32_t dst = smem_base + st * TC_STAGE_BYTES;
                             mbar_expect_tx(full_bar(st), TC_STAGE_BYTES);
-                            tma_load_3d(dst,             &planes_map, full_bar(st), kb * TC_BK, ti * TC_TILE,       k);
-                            tma_load_3d(dst + 16384,     &planes_map, full_bar(st), kb * TC_BK, ti * TC_TILE + 128, k);
-                            tma_load_3d(dst + 2 * 16384, &planes_map, full_bar(st), kb * TC_BK, tj * TC_TILE,       l);
-                            tma_load_3d(dst + 3 * 16384, &planes_map, full_bar(st), kb * TC_BK, tj * TC_TILE + 128, l);
+                            tma_load_3d(dst,             &map_a, full_bar(st), kb * TC_BK, ti * TC_TILE,       k);
+                            tma_load_3d(dst + 16384,     &map_a, full_bar(st), kb * TC_BK, ti * TC_TILE + 128, k);
+                            tma_load_3d(dst + 2 * 16384, &map_b, full_bar(st), kb * TC_BK, tj * TC_TILE,       l);
+                            tma_load_3d(dst + 3 * 16384, &map_b, full_bar(st), kb * TC_BK, tj * TC_TILE + 128, l);
                         }
                     }
                 }
@@ -321,12 +332,13 @@ tc_gram_kernel(const __grid_constant__ CUtensorMap planes_map, const TcSched sc,
             const TcSeg sg = tc_segment(sc, si, blockIdx.x, gridDim.x);
             if (sg.kb1 <= sg.kb0) continue;
             int ti, tj;
-            tc_tile_coords(sg.tile, sc.tiles, ti, tj);
+            tc_tile_coords(sc, sg.tile, ti, tj);
             const bool owned = (sg.kb0 == 0 && sg.kb1 == sc.n_kblocks);
             const int64_t wrow0 = (int64_t)ti * TC_TILE + half * 128 + quad * 32;
             const int64_t row = wrow0 + lane;
             const int64_t col0 = (int64_t)tj * TC_TILE;
-            const double rs = (row < m) ? colscale[row] : 0.0;
+            const double rs = (row < ma) ? scale_a[row] : 0.0;
+            const int64_t diag = sc.symmetric ? wrow0 : 0;          // first column this warp may write
             const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 256);
             for (int g = sc.num_slices - 1; g >= 0; --g, ++it) {
                 mbar_wait(tfull_bar, it & 1);
@@ -335,17 +347,18 @@ tc_gram_kernel(const __grid_constant__ CUtensorMap planes_map, const TcSched sc,
 #pragma unroll 1
                 for (int c = 0; c < TC_TILE / 32; ++c) {
                     const int64_t cb = col0 + c * 32;
-                    if (cb + 31 < wrow0 || cb >= m || wrow0 >= m) continue;      // warp-uniform: below the diagonal / outside
+                    if (cb + 31 < diag || cb >= mb || wrow0 >= ma) continue;      // warp-uniform: below the diagonal / outside
                     uint32_t acc[32];
                     tmem_ld32(taddr + c * 32, acc);
                     tmem_ld_wait();
-                    if (row < m) {
-                        double* gp = g_out + row * m + cb;
+                    if (row < ma) {
+                        double* gp = g_out + row * mb + cb;
+                        const int64_t cmin = sc.symmetric ? row : 0;
 #pragma unroll
                         for (int uu = 0; uu < 32; ++uu) {
                             const int64_t col = cb + uu;
-                            if (col < m && col >= row) {
-                                const double v = (double)(int)acc[uu] * (rsg * __ldg(colscale + col));
+                            if (col < mb && col >= cmin) {
+                                const double v = (double)(int)acc[uu] * (rsg * __ldg(scale_b + col));
                                 if (owned) gp[uu] += v;
                                 else atomicAdd(gp + uu, v);
                             }
@@ -402,13 +415,26 @@ static EncodeTiledFn encode_tiled_fn() {
 
 static inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
 
-// workspace: [cmax u64 (m)] [colscale f64 (m)] [planes int8 (S, m, n_pad)], each region 1024-byte aligned
+// One operand's share of the workspace: [cmax u64 (m)] [colscale f64 (m)] [planes int8 (S, m, n_pad)], 1024-byte aligned
 static inline int64_t tc_rows_per_pass(int64_t n) { return n < TC_MAX_ROWS ? n : TC_MAX_ROWS; }
+static inline int64_t tc_operand_bytes(int64_t n, int64_t m, int num_slices) {
+    const int64_t n_pad = round_up(tc_rows_per_pass(n), TC_BK);
+    return round_up(m * 8, 1024) * 2 + round_up((int64_t)num_slices * m * n_pad, 1024);
+}
+struct TcOperand {
+    unsigned long long* cmax;
+    double* colscale;
+    int8_t* planes;
+    CUtensorMap map;
+};
 
 int64_t ztz_tc_workspace_bytes(int64_t n, int64_t m, int num_slices) {
     if (n <= 0 || m <= 0 || num_slices < 2 || num_slices > 7) return -1;
-    const int64_t n_pad = round_up(tc_rows_per_pass(n), TC_BK);
-    return round_up(m * 8, 1024) * 2 + round_up((int64_t)num_slices * m * n_pad, 1024);
+    return tc_operand_bytes(n, m, num_slices);
+}
+int64_t atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int num_slices) {
+    if (n <= 0 || m <= 0 || r <= 0 || num_slices < 2 || num_slices > 7) return -1;
+    return tc_operand_bytes(n, r, num_slices) + tc_operand_bytes(n, m, num_slices);
 }
 
 template <int S>
@@ -418,6 +444,80 @@ static void launch_slice(const double* z, int64_t n, int64_t m, int64_t n_pad, c
     tc_slice_kernel<S><<<grid, 256, 0, st>>>(z, n, m, n_pad, cs, planes);
 }
 
+// column exponents + digit planes + tensor map of one fp64 operand chunk z (rows, m); 3 launches
+static int tc_prepare_operand(TcOperand& op, uint8_t* ws, const double* z, int64_t rows, int64_t m, int num_slices,
+                              int sms, cudaStream_t st) {
+    const int64_t n_pad = round_up(rows, TC_BK);
+    op.cmax = (unsigned long long*)ws;
+    op.colscale = (double*)(ws + round_up(m * 8, 1024));
+    op.planes = (int8_t*)(ws + 2 * round_up(m * 8, 1024));
+    cudaMemsetAsync(op.cmax, 0, m * 8, st);
+    const int64_t colblocks = (m + 255) / 256;
+    int64_t splits = (sms * 8 + colblocks - 1) / colblocks;
+    int64_t rows_per = (rows + splits - 1) / splits;
+    if (rows_per < 16) rows_per = 16;
+    splits = (rows + rows_per - 1) / rows_per;
+    tc_colmax_kernel<<<dim3((unsigned)colblocks, (unsigned)splits), 256, 0, st>>>(z, rows, m, op.cmax, rows_per);
+    tc_exponent_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(op.cmax, m, op.colscale);
+    switch (num_slices) {
+        case 2: launch_slice<2>(z, rows, m, n_pad, op.colscale, op.planes, st); break;
+        case 3: launch_slice<3>(z, rows, m, n_pad, op.colscale, op.planes, st); break;
+        case 4: launch_slice<4>(z, rows, m, n_pad, op.colscale, op.planes, st); break;
+        case 5: launch_slice<5>(z, rows, m, n_pad, op.colscale, op.planes, st); break;
+        case 6: launch_slice<6>(z, rows, m, n_pad, op.colscale, op.planes, st); break;
+        default: launch_slice<7>(z, rows, m, n_pad, op.colscale, op.planes, st); break;
+    }
+    count_launch(3);
+    EncodeTiledFn encode = encode_tiled_fn();
+    if (!encode) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return XGPR_B200_ECUDA; }
+    const cuuint64_t gdim[3] = {(cuuint64_t)n_pad, (cuuint64_t)m, (cuuint64_t)num_slices};
+    const cuuint64_t gstride[2] = {(cuuint64_t)n_pad, (cuuint64_t)(m * n_pad)};
+    const cuuint32_t box[3] = {TC_BK, 128, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult cr = encode(&op.map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, op.planes, gdim, gstride, box, estr,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d)", (int)cr); return XGPR_B200_ECUDA; }
+    return check_launch("tc_prepare_operand");
+}
+
+static int tc_setup(int& sms) {
+    static int smem_set = 0;
+    if (!smem_set) {
+        if (cudaFuncSetAttribute(tc_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES) != cudaSuccess)
+            return check_launch("tc_gram_kernel smem attribute");
+        smem_set = 1;
+    }
+    int dev = 0;
+    sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return XGPR_B200_OK;
+}
+
+// c (ma, mb) += A^T B for one pass of rows (both operands already sliced)
+static int tc_launch_gemm(const TcOperand& a, const TcOperand& b, int64_t rows, int64_t ma, int64_t mb, int symmetric,
+                          int num_slices, double* c, int sms, cudaStream_t st) {
+    TcSched sc;
+    sc.num_slices = num_slices;
+    sc.n_kblocks = (int)(round_up(rows, TC_BK) / TC_BK);
+    sc.symmetric = symmetric;
+    sc.tiles = (int)((mb + TC_TILE - 1) / TC_TILE);
+    const int tiles_i = (int)((ma + TC_TILE - 1) / TC_TILE);
+    sc.num_tiles = symmetric ? sc.tiles * (sc.tiles + 1) / 2 : tiles_i * sc.tiles;
+    // grid: all SMs, unless the whole problem has fewer K blocks than that
+    long long grid = (long long)sc.num_tiles * sc.n_kblocks;
+    if (grid > sms) grid = sms;
+    sc.full_waves = sc.num_tiles / (int)grid;
+    // Sharing the last partial wave's tiles along K balances the SMs but de-phases their K sweeps (less L2 reuse of
+    // the shared row blocks): measured to pay off only when that wave would leave > 1/4 of the SMs idle.
+    const int rem = sc.num_tiles - sc.full_waves * (int)grid;
+    sc.split_remainder = (rem > 0 && rem * 4 < (int)grid * 3) ? 1 : 0;
+    tc_gram_kernel<<<(unsigned)grid, TC_THREADS, TC_SMEM_BYTES, st>>>(a.map, b.map, sc, ma, mb, a.colscale, b.colscale, c);
+    count_launch();
+    return check_launch("tc_gram_kernel");
+}
+
 int ztz_accum_tc(const double* z, int64_t n, int64_t m, double* ztz, int num_slices, int mirror, void* workspace,
                  int64_t workspace_bytes, cudaStream_t st) {
     XB_REQUIRE(n > 0 && m > 0, "no datapoints");
@@ -425,75 +525,14 @@ int ztz_accum_tc(const double* z, int64_t n, int64_t m, double* ztz, int num_sli
     XB_REQUIRE(num_slices >= 2 && num_slices <= 7, "num_slices must be in [2, 7]");
     XB_REQUIRE(workspace_bytes >= ztz_tc_workspace_bytes(n, m, num_slices), "workspace too small");
     XB_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
-    EncodeTiledFn encode = encode_tiled_fn();
-    if (!encode) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return XGPR_B200_ECUDA; }
-
-    static int smem_set = 0;
-    if (!smem_set) {
-        if (cudaFuncSetAttribute(tc_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES) != cudaSuccess)
-            return check_launch("tc_gram_kernel smem attribute");
-        smem_set = 1;
-    }
-    int dev = 0, sms = 148;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-
-    uint8_t* ws = (uint8_t*)workspace;
-    unsigned long long* cmax = (unsigned long long*)ws;
-    double* colscale = (double*)(ws + round_up(m * 8, 1024));
-    int8_t* planes = (int8_t*)(ws + 2 * round_up(m * 8, 1024));
-
-    const int tiles = (int)((m + TC_TILE - 1) / TC_TILE);
-    const int num_tiles = tiles * (tiles + 1) / 2;
-
+    int sms, rc = tc_setup(sms);
+    if (rc != XGPR_B200_OK) return rc;
     for (int64_t r0 = 0; r0 < n; r0 += TC_MAX_ROWS) {
         const int64_t rows = (n - r0 < TC_MAX_ROWS) ? (n - r0) : TC_MAX_ROWS;
-        const int64_t n_pad = round_up(rows, TC_BK);
-        const double* zc = z + r0 * m;
-        cudaMemsetAsync(cmax, 0, m * 8, st);
-        {
-            const int64_t colblocks = (m + 255) / 256;
-            int64_t splits = (sms * 8 + colblocks - 1) / colblocks;
-            int64_t rows_per = (rows + splits - 1) / splits;
-            if (rows_per < 16) rows_per = 16;
-            splits = (rows + rows_per - 1) / rows_per;
-            dim3 grid((unsigned)colblocks, (unsigned)splits);
-            tc_colmax_kernel<<<grid, 256, 0, st>>>(zc, rows, m, cmax, rows_per);
-            tc_exponent_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(cmax, m, colscale);
-        }
-        switch (num_slices) {
-            case 2: launch_slice<2>(zc, rows, m, n_pad, colscale, planes, st); break;
-            case 3: launch_slice<3>(zc, rows, m, n_pad, colscale, planes, st); break;
-            case 4: launch_slice<4>(zc, rows, m, n_pad, colscale, planes, st); break;
-            case 5: launch_slice<5>(zc, rows, m, n_pad, colscale, planes, st); break;
-            case 6: launch_slice<6>(zc, rows, m, n_pad, colscale, planes, st); break;
-            default: launch_slice<7>(zc, rows, m, n_pad, colscale, planes, st); break;
-        }
-        CUtensorMap map;
-        const cuuint64_t gdim[3] = {(cuuint64_t)n_pad, (cuuint64_t)m, (cuuint64_t)num_slices};
-        const cuuint64_t gstride[2] = {(cuuint64_t)n_pad, (cuuint64_t)(m * n_pad)};
-        const cuuint32_t box[3] = {TC_BK, 128, 1};
-        const cuuint32_t estr[3] = {1, 1, 1};
-        const CUresult cr = encode(&map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, planes, gdim, gstride, box, estr,
-                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (cr != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d)", (int)cr); return XGPR_B200_ECUDA; }
-        TcSched sc;
-        sc.num_slices = num_slices;
-        sc.n_kblocks = (int)(n_pad / TC_BK);
-        sc.tiles = tiles;
-        sc.num_tiles = num_tiles;
-        // grid: all SMs, unless the whole problem has fewer K blocks than that
-        long long grid = (long long)num_tiles * sc.n_kblocks;
-        if (grid > sms) grid = sms;
-        sc.full_waves = num_tiles / (int)grid;
-        // Sharing the last partial wave's tiles along K balances the SMs but de-phases their K sweeps (less L2 reuse of
-        // the shared row blocks): measured to pay off only when that wave would leave > 1/4 of the SMs idle.
-        const int rem = num_tiles - sc.full_waves * (int)grid;
-        sc.split_remainder = (rem > 0 && rem * 4 < (int)grid * 3) ? 1 : 0;
-        tc_gram_kernel<<<(unsigned)grid, TC_THREADS, TC_SMEM_BYTES, st>>>(map, sc, m, colscale, ztz);
-        count_launch(4);
-        const int rc = check_launch("tc_gram_kernel");
+        TcOperand op;
+        rc = tc_prepare_operand(op, (uint8_t*)workspace, z + r0 * m, rows, m, num_slices, sms, st);
+        if (rc != XGPR_B200_OK) return rc;
+        rc = tc_launch_gemm(op, op, rows, m, m, 1, num_slices, ztz, sms, st);
         if (rc != XGPR_B200_OK) return rc;
     }
     if (mirror) {
@@ -502,6 +541,31 @@ int ztz_accum_tc(const double* z, int64_t n, int64_t m, double* ztz, int num_sli
         count_launch();
     }
     return check_launch("ztz_accum_tc");
+}
+
+// acc (r, m) += A^T Z ;  A (n, r), Z (n, m) fp64 row-major
+int atb_accum_tc(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc, int num_slices,
+                 void* workspace, int64_t workspace_bytes, cudaStream_t st) {
+    XB_REQUIRE(n > 0 && m > 0 && r > 0, "no datapoints");
+    XB_REQUIRE(a && z && acc && workspace, "null pointer");
+    XB_REQUIRE(num_slices >= 2 && num_slices <= 7, "num_slices must be in [2, 7]");
+    XB_REQUIRE(workspace_bytes >= atb_tc_workspace_bytes(n, r, m, num_slices), "workspace too small");
+    XB_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+    int sms, rc = tc_setup(sms);
+    if (rc != XGPR_B200_OK) return rc;
+    uint8_t* ws_a = (uint8_t*)workspace;
+    uint8_t* ws_b = ws_a + tc_operand_bytes(n, r, num_slices);
+    for (int64_t r0 = 0; r0 < n; r0 += TC_MAX_ROWS) {
+        const int64_t rows = (n - r0 < TC_MAX_ROWS) ? (n - r0) : TC_MAX_ROWS;
+        TcOperand oa, ob;
+        rc = tc_prepare_operand(oa, ws_a, a + r0 * r, rows, r, num_slices, sms, st);
+        if (rc != XGPR_B200_OK) return rc;
+        rc = tc_prepare_operand(ob, ws_b, z + r0 * m, rows, m, num_slices, sms, st);
+        if (rc != XGPR_B200_OK) return rc;
+        rc = tc_launch_gemm(oa, ob, rows, r, m, 0, num_slices, acc, sms, st);
+        if (rc != XGPR_B200_OK) return rc;
+    }
+    return XGPR_B200_OK;
 }
 
 int symmetrize_upper(double* g, int64_t m, cudaStream_t st) {

@@ -231,6 +231,32 @@ def ztz_accum(z, ztz):
 _TC_WORKSPACE = {}
 
 
+def _tc_workspace(device, need):
+    """Grow-only scratch per (device, stream): no allocation in steady state."""
+    key = (device.index, torch.cuda.current_stream().cuda_stream)
+    ws = _TC_WORKSPACE.get(key)
+    if ws is None or ws.numel() < need:
+        _TC_WORKSPACE[key] = None
+        ws = torch.empty(need, dtype=torch.uint8, device=device)
+        _TC_WORKSPACE[key] = ws
+    return ws
+
+
+def atb_accum_tc(a, z, acc, num_slices=6):
+    """acc (r, m) += a^T z on the tensor cores (same split-int8 scheme as ztz_accum_tc)."""
+    a = _dev(a.contiguous(), "a", (torch.float64,), 2)
+    z = _dev(z, "z", (torch.float64,), 2)
+    acc = _dev(acc, "acc", (torch.float64,), 2)
+    if a.shape[0] != z.shape[0] or acc.shape[0] != a.shape[1] or acc.shape[1] != z.shape[1]:
+        raise RuntimeError("wrong array sizes")
+    need = lib.xgpr_b200_atb_tc_workspace_bytes(z.shape[0], a.shape[1], z.shape[1], int(num_slices))
+    if need < 0:
+        raise RuntimeError("num_slices must be in [2, 7]")
+    ws = _tc_workspace(z.device, need)
+    check(lib.xgpr_b200_atb_accum_tc_f64(a.data_ptr(), z.data_ptr(), z.shape[0], a.shape[1], z.shape[1],
+                                         acc.data_ptr(), int(num_slices), ws.data_ptr(), ws.numel(), _stream()))
+
+
 def ztz_accum_tc(z, ztz, num_slices=6, mirror=True):
     """Upper triangle of ztz += z^T z on the tensor cores (tcgen05 kind::i8 over `num_slices` exact int8 digit planes,
     int32 accumulation in TMEM; csrc/gram_tc_kernels.cu).  mirror=True also refreshes the lower triangle."""
@@ -241,11 +267,7 @@ def ztz_accum_tc(z, ztz, num_slices=6, mirror=True):
     need = lib.xgpr_b200_ztz_tc_workspace_bytes(z.shape[0], z.shape[1], int(num_slices))
     if need < 0:
         raise RuntimeError("num_slices must be in [2, 7]")
-    key = (z.device.index, torch.cuda.current_stream().cuda_stream)
-    ws = _TC_WORKSPACE.get(key)
-    if ws is None or ws.numel() < need:          # grow-only per (device, stream): no allocation in steady state
-        ws = torch.empty(need, dtype=torch.uint8, device=z.device)
-        _TC_WORKSPACE[key] = ws
+    ws = _tc_workspace(z.device, need)
     check(lib.xgpr_b200_ztz_accum_tc_f64(z.data_ptr(), z.shape[0], z.shape[1], ztz.data_ptr(), int(num_slices),
                                          1 if mirror else 0, ws.data_ptr(), ws.numel(), _stream()))
 
