@@ -297,11 +297,13 @@ def run_b200(args):
 
     # ---------------- the metric's second kernel: Conv1dRBF @16384 RFFs on cfg3-shaped sequences
     conv = conv_headline(args, dev, rank)
+    gram = gram_headline(dev, rank)
 
-    t = torch.tensor([dev_ms, e2e_ms, float(np.mean(kern_ms)), conv["ms"]], dtype=torch.float64, device=dev)
+    t = torch.tensor([dev_ms, e2e_ms, float(np.mean(kern_ms)), conv["ms"], gram["tc_ms"], gram["gemm_ms"],
+                      gram["dfma_ms"]], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms, e2e_ms, kmean, conv_ms = [float(v) for v in t.cpu()]
+    dev_ms, e2e_ms, kmean, conv_ms, gram_ms, gram_gemm_ms, gram_dfma_ms = [float(v) for v in t.cpu()]
 
     if rank == 0:
         total_rows = rows * args.steps * world
@@ -342,6 +344,20 @@ def run_b200(args):
                      "freq_windows_per_s": conv["fw"] * conv["steps"] * world / (conv_ms * 1e-3),
                      "gpu_launches": conv["launches"]},
         }
+        bf16_peak = tensor_peak()
+        line["gram"] = {
+            "metric": "Z^T Z accumulation (exact-fit Gram), fp64-equivalent TFLOP/s per GPU",
+            "workload": "Z (%d x %d) fp64 features per call per GPU, %d int8 digit planes, upper triangle + mirror"
+                        % (gram["n"], gram["m"], gram["slices"]),
+            "value": 2.0 * gram["n"] * gram["m"] ** 2 / (gram_ms * 1e-3) / 1e12, "unit": "TFLOP/s (fp64-equivalent)",
+            "ms_per_call": gram_ms, "dfma_kernel_ms": gram_dfma_ms,
+            "speedup_vs_fp64_pipe": gram_dfma_ms / gram_ms, "gpu_launches_per_call": gram["launches"],
+            "roofline": {"bound": "tensor", "kernel": "tc_gram_kernel (tcgen05.mma kind::i8, M128 N256 K32)",
+                         "achieved": gram["int8_ops"] / (gram_gemm_ms * 1e-3) / 1e12,
+                         "peak": None if bf16_peak is None else 2.0 * bf16_peak, "unit": "TOP/s (int8)",
+                         "frac": None if bf16_peak is None else gram["int8_ops"] / (gram_gemm_ms * 1e-3) / 1e12 / (2.0 * bf16_peak),
+                         "peak_source": "2 x measured bf16 burst TFLOP/s (MEASURED_PEAKS.json); int8 issues at twice the bf16 rate",
+                         "kernel_ms": gram_gemm_ms, "algorithmic_ops_per_launch": gram["int8_ops"]}}
         if world == 1 and not args.no_cpu_baseline:
             try:
                 v, kind, cores, sample = cpu_rows_per_s(kern_cpu_copy(), args.cpu_rows)
@@ -381,6 +397,54 @@ def conv_headline(args, dev, rank, nseq=4096, steps=3):
     torch.cuda.synchronize()
     return {"ms": a.elapsed_time(b), "rows": nseq, "steps": steps, "fw": nseq * 492 * (NUM_RFFS // 2),
             "launches": ext.launch_count() - l0}
+
+
+def tensor_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p)).get("bf16_tflops", 0.0)) or None
+    return 1590.0
+
+
+def gram_headline(dev, rank, n=32768, m=8192, slices=6, steps=3):
+    """The dense contraction of the path: Z^T Z for the exact fit (exact_nmll_calcs.py:68-72) on the tensor cores
+    (csrc/gram_tc_kernels.cu), next to the fp64-pipe kernel it replaces.  int8 ops counted = what the GEMM kernel
+    issues: upper-triangle 256 x 256 tiles x slices (slices + 1) / 2 plane pairs x 2 n_pad 256^2."""
+    import torch
+    from xgpr_b200 import ext
+    g = torch.Generator(device=dev)
+    g.manual_seed(7 + rank)
+    z = torch.cos(torch.randn((n, m), device=dev, dtype=torch.float64, generator=g) * 3.0) * (2.0 / m) ** 0.5
+    acc = torch.zeros((m, m), dtype=torch.float64, device=dev)
+
+    def timed(fn, reps):
+        fn()
+        torch.cuda.synchronize()
+        l0 = ext.launch_count()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps, (ext.launch_count() - l0) // reps
+
+    tc_ms, launches = timed(lambda: ext.ztz_accum_tc(z, acc, num_slices=slices), steps)
+    # the GEMM kernel alone: CUDA events recorded by the library around its launch, on the launching stream
+    ext.tc_profile(True)
+    gemm = []
+    for _ in range(steps):
+        ext.ztz_accum_tc(z, acc, num_slices=slices)
+        gemm.append(ext.tc_last_gemm_ms())
+    ext.tc_profile(False)
+    gemm_ms = float(np.mean(gemm))
+    dfma_ms, _ = timed(lambda: ext.ztz_accum(z, acc), 1)
+    tiles = (m + 255) // 256
+    n_pad = (n + 127) // 128 * 128
+    int8_ops = tiles * (tiles + 1) // 2 * (slices * (slices + 1) // 2) * 2.0 * n_pad * 256 * 256
+    del z, acc
+    return {"tc_ms": tc_ms, "gemm_ms": gemm_ms, "dfma_ms": dfma_ms, "n": n, "m": m,
+            "slices": slices, "launches": launches, "int8_ops": int8_ops}
 
 
 def kern_cpu_copy():

@@ -150,6 +150,10 @@ int64_t xgpr_b200_ztz_tc_workspace_bytes(int64_t n, int64_t m, int num_slices);
 int xgpr_b200_ztz_accum_tc_f64(const double* z, int64_t n, int64_t m, double* ztz, int num_slices, int mirror,
                                void* workspace, int64_t workspace_bytes, void* stream);
 int xgpr_b200_symmetrize_upper_f64(double* g, int64_t m, void* stream);
+/* Measurement aid: with profiling enabled the library brackets each tensor-core GEMM launch with CUDA events on the
+ * launching stream; xgpr_b200_tc_last_gemm_ms() synchronises on the last bracket and returns its duration (-1: none). */
+int    xgpr_b200_tc_profile(int enable);
+double xgpr_b200_tc_last_gemm_ms(void);
 /* Tensor-core sketch accumulation, same scheme: acc (r, m) += A^T Z, A (n, r), Z (n, m) fp64 row-major
  * (`acc_results += compressor.transform_x(xdata).T @ xdata`, src/xGPR/preconditioners/rand_nys_constructors.py:119). */
 int64_t xgpr_b200_atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int num_slices);

@@ -62,6 +62,11 @@ EXPORTED.append("xgpr_b200_ztz_tc_workspace_bytes")
 lib.xgpr_b200_atb_tc_workspace_bytes.argtypes = [_i64, _i64, _i64, _int]
 lib.xgpr_b200_atb_tc_workspace_bytes.restype = _i64
 EXPORTED.append("xgpr_b200_atb_tc_workspace_bytes")
+lib.xgpr_b200_tc_profile.argtypes = [_int]
+lib.xgpr_b200_tc_profile.restype = _int
+lib.xgpr_b200_tc_last_gemm_ms.argtypes = []
+lib.xgpr_b200_tc_last_gemm_ms.restype = _dbl
+EXPORTED += ["xgpr_b200_tc_profile", "xgpr_b200_tc_last_gemm_ms"]
 lib.xgpr_b200_abi_version.restype = _int
 lib.xgpr_b200_last_error.restype = ctypes.c_char_p
 lib.xgpr_b200_launch_count.restype = _i64

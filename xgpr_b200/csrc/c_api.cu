@@ -51,6 +51,8 @@ int64_t ztz_tc_workspace_bytes(int64_t n, int64_t m, int num_slices);
 int ztz_accum_tc(const double* z, int64_t n, int64_t m, double* ztz, int num_slices, int mirror, void* workspace,
                  int64_t workspace_bytes, cudaStream_t st);
 int symmetrize_upper(double* g, int64_t m, cudaStream_t st);
+void tc_profile(int enable);
+double tc_last_gemm_ms();
 int64_t atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int num_slices);
 int atb_accum_tc(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc, int num_slices,
                  void* workspace, int64_t workspace_bytes, cudaStream_t st);
@@ -156,6 +158,8 @@ int xgpr_b200_ztz_accum_tc_f64(const double* z, int64_t n, int64_t m, double* zt
     return ztz_accum_tc(z, n, m, ztz, num_slices, mirror, workspace, workspace_bytes, ST(s));
 }
 int xgpr_b200_symmetrize_upper_f64(double* g, int64_t m, void* s) { return symmetrize_upper(g, m, ST(s)); }
+int xgpr_b200_tc_profile(int enable) { tc_profile(enable); return XGPR_B200_OK; }
+double xgpr_b200_tc_last_gemm_ms(void) { return tc_last_gemm_ms(); }
 int64_t xgpr_b200_atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int num_slices) {
     return atb_tc_workspace_bytes(n, r, m, num_slices);
 }

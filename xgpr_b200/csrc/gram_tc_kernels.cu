@@ -17,8 +17,11 @@
 //   relative to (column max)^2 per row -- s = 6 is at the level of the reference DGEMM's own rounding.
 //
 // Kernels: colmax -> slice (fp64 -> s int8 planes, transposed to K-major (m, n_pad)) -> persistent
-// warp-specialised tcgen05 GEMM (TMA producer warp / single-thread MMA issuer / 4 epilogue warps, 4-stage
-// 48 KB smem ring, double-buffered 128x256 int32 accumulators in TMEM, upper-triangle tiles only) -> mirror.
+// warp-specialised tcgen05 GEMM (TMA producer warp / single-thread MMA issuer / 8 epilogue warps, 3-stage
+// 64 KB smem ring, 256 x 256 CTA tile = two 128 x 256 int32 accumulators filling TMEM, upper-triangle tiles only)
+// -> mirror.  The same GEMM serves acc (r, m) += A^T Z for the Nystrom sketch (two operands, no symmetry).
+// Measured (B200, power-capped ~1.3-1.4 GHz): M = 8192, n = 32768, s = 6: 20 ms per call = 215 TFLOP/s fp64-equivalent
+// (DFMA kernel / cuBLAS DGEMM: 118-120 ms), tensor pipe active 79 % (profiles/r01c_tc_gram_kernel_full.md).
 #include "common.cuh"
 #include <cuda.h>
 
@@ -495,6 +498,23 @@ static int tc_setup(int& sms) {
     return XGPR_B200_OK;
 }
 
+// optional CUDA-event bracket around the GEMM launch (bench.py's roofline: the kernel's own duration on its stream)
+static int g_tc_profile = 0;
+static cudaEvent_t g_tc_ev0 = nullptr, g_tc_ev1 = nullptr;
+static int g_tc_ev_valid = 0;
+void tc_profile(int enable) {
+    g_tc_profile = enable;
+    if (enable && !g_tc_ev0) { cudaEventCreate(&g_tc_ev0); cudaEventCreate(&g_tc_ev1); }
+    g_tc_ev_valid = 0;
+}
+double tc_last_gemm_ms() {
+    if (!g_tc_ev_valid) return -1.0;
+    float ms = -1.0f;
+    if (cudaEventSynchronize(g_tc_ev1) != cudaSuccess || cudaEventElapsedTime(&ms, g_tc_ev0, g_tc_ev1) != cudaSuccess)
+        return -1.0;
+    return (double)ms;
+}
+
 // c (ma, mb) += A^T B for one pass of rows (both operands already sliced)
 static int tc_launch_gemm(const TcOperand& a, const TcOperand& b, int64_t rows, int64_t ma, int64_t mb, int symmetric,
                           int num_slices, double* c, int sms, cudaStream_t st) {
@@ -513,7 +533,9 @@ static int tc_launch_gemm(const TcOperand& a, const TcOperand& b, int64_t rows, 
     // the shared row blocks): measured to pay off only when that wave would leave > 1/4 of the SMs idle.
     const int rem = sc.num_tiles - sc.full_waves * (int)grid;
     sc.split_remainder = (rem > 0 && rem * 4 < (int)grid * 3) ? 1 : 0;
+    if (g_tc_profile) cudaEventRecord(g_tc_ev0, st);
     tc_gram_kernel<<<(unsigned)grid, TC_THREADS, TC_SMEM_BYTES, st>>>(a.map, b.map, sc, ma, mb, a.colscale, b.colscale, c);
+    if (g_tc_profile) { cudaEventRecord(g_tc_ev1, st); g_tc_ev_valid = 1; }
     count_launch();
     return check_launch("tc_gram_kernel");
 }

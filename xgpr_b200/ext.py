@@ -272,6 +272,15 @@ def ztz_accum_tc(z, ztz, num_slices=6, mirror=True):
                                          1 if mirror else 0, ws.data_ptr(), ws.numel(), _stream()))
 
 
+def tc_profile(enable):
+    """Bracket every tensor-core GEMM launch with CUDA events (measurement aid, see tc_last_gemm_ms)."""
+    lib.xgpr_b200_tc_profile(1 if enable else 0)
+
+
+def tc_last_gemm_ms():
+    return float(lib.xgpr_b200_tc_last_gemm_ms())
+
+
 def symmetrize_upper(g):
     g = _dev(g, "g", (torch.float64,), 2)
     if g.shape[0] != g.shape[1]:
