@@ -51,6 +51,22 @@ class OracleKernel:
             z[:, 0] = 1.0
         return torch.from_numpy(z)
 
+    def gradient_x_y(self, x, y, sequence_length=None):
+        """(Z, dZ/dsigma, y) on the RAW input, as the reference's gradient entry points (kernel_baseclass.py:364-378)."""
+        k = self.k
+        dt = np.float64 if k.double_precision else np.float32
+        xin = np.ascontiguousarray(np.asarray(x), dtype=dt)
+        sigma = float(k.hyperparams[1])
+        if xin.ndim == 3:
+            z, dz = so.conv_rbf_grad(xin, k.radem_diag, k.chi_arr, np.asarray(sequence_length, np.int32), sigma,
+                                     k.conv_width, k.scaling_type)
+        else:
+            z, dz = so.rbf_grad(xin, k.radem_diag, k.chi_arr, sigma, k.fit_intercept)
+        if k.fit_intercept:
+            z[:, 0] = 1.0
+            dz[:, 0, :] = 0.0
+        return torch.from_numpy(z), torch.from_numpy(dz), torch.from_numpy(np.asarray(y, np.float64))
+
     def transform_x_y(self, x, y, sequence_length=None, classification=False):
         return self.transform_x(x, sequence_length), torch.from_numpy(np.asarray(y, np.float64))
 

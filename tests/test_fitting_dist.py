@@ -46,7 +46,7 @@ def _run(rank, world, port, name, q):
                                        kernel_spec_parms=parms)
     kern.set_hyperparams(np.log(g["hyperparams"]), logspace=True)
     ok = OracleKernel(kern)
-    res = {"mean": ds.get_ymean(), "std": ds.get_ystd(), "n": ds.get_ndatapoints()}
+    res = {"mean": ds.get_ymean(), "std": ds.get_ystd(), "n": ds.get_ndatapoints(), "name": name}
     w, _, _ = fitting.calc_weights_exact(ds, ok, comm, OracleOps)
     res["w_exact"] = w.numpy()
     for method in ("srht", "srht_2"):
@@ -54,6 +54,15 @@ def _run(rank, world, port, name, q):
         wcg, nit, _ = fitting.cg_fit_lib_internal(ok, ds, 1e-12, 500, pre, False, comm, OracleOps)
         res[f"ratio_{method}"], res[f"w_cg_{method}"], res[f"niter_{method}"] = pre.achieved_ratio, wcg.numpy(), nit
     res["var"] = fitting.calc_variance_exact(ok, ds, vrffs, comm, OracleOps).numpy()
+    # the NMLL call sites (xgpr_b200/scoring.py) on the same shards
+    from xgpr_b200 import scoring
+    gn = load_golden(os.path.join(GOLDEN, f"l3_nmll_{name}.npz"))
+    loghp = np.log(gn["hyperparams"])
+    res["nmll_exact"] = scoring.exact_nmll(loghp.copy(), ds, ok, comm, OracleOps)
+    res["nmll_grad_value"], res["nmll_grad"] = scoring.exact_nmll_gradient(loghp.copy(), ds, ok, 1, comm, OracleOps)
+    settings = {"max_rank": int(gn["approx_max_rank"]), "nsamples": int(gn["approx_nsamples"]),
+                "nmll_tol": float(gn["approx_tol"]), "nmll_iter": 500, "preconditioner_mode": "srht_2"}
+    res["nmll_approx"] = scoring.approximate_nmll(loghp.copy(), ds, ok, settings, 123, comm, OracleOps, OracleSRHT)
     res["n_allreduce"] = comm.n_allreduce
     if rank == 0:
         q.put(res)
@@ -73,6 +82,11 @@ def _check(res, g, world):
         assert abs(res[f"niter_{method}"] - int(g[f"niter_{method}"])) <= 1
     np.testing.assert_allclose(res["var"], g["var"], rtol=1e-6, atol=1e-10)
     assert (res["n_allreduce"] > 0) == (world > 1)
+    gn = load_golden(os.path.join(GOLDEN, f"l3_nmll_{res['name']}.npz"))
+    np.testing.assert_allclose(res["nmll_exact"], float(gn["nmll_exact"]), rtol=1e-8)
+    np.testing.assert_allclose(res["nmll_grad_value"], float(gn["nmll_grad_value"]), rtol=1e-8)
+    np.testing.assert_allclose(res["nmll_grad"], gn["nmll_grad"], rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(res["nmll_approx"], float(gn["nmll_approx"]), rtol=1e-6)
 
 
 @pytest.mark.parametrize("world", [1, 2])

@@ -493,11 +493,35 @@ class RandNysPreconditioner:
         xprod2 = xvec - (self.u_mat @ xprod)
         return xprod2 + xprod1
 
+    def rev_batch_matvec(self, xvec):
+        """Matvec with the NON-inverted preconditioner (rand_nys_preconditioners.py:75-81)."""
+        xprod = self.u_mat.T @ xvec
+        xprod1 = self.u_mat @ (self.eig[:, None] * xprod) / self.prefactor
+        xprod2 = xvec - (self.u_mat @ xprod)
+        return xprod2 + xprod1
+
     def get_zty(self):
         return self.z_trans_y
 
+    def get_yty(self):
+        return self.y_trans_y
+
     def get_rank(self):
         return self.inv_eig.shape[0]
+
+    def get_logdet(self):
+        """log det of the preconditioner (rand_nys_preconditioners.py:97-103)."""
+        logdet = 1 + (self.eig - self.prefactor) / self.prefactor
+        return float(torch.log(logdet.clamp(min=1e-12)).sum())
+
+    def matvec_for_sampling(self, xvec):
+        """P^(1/2) x: turns standard-normal probes into samples with covariance P (rand_nys_preconditioners.py:106-119)."""
+        eigvals = torch.sqrt(self.eig.clamp(min=0))
+        prefactor = float(np.sqrt(1 / self.prefactor))
+        xprod = self.u_mat.T @ xvec
+        xprod1 = self.u_mat @ (eigvals[:, None] * prefactor * xprod)
+        xprod2 = xvec - (self.u_mat @ xprod)
+        return xprod1 + xprod2
 
 
 # ----------------------------------------------------------------------------------------- predict
