@@ -199,6 +199,154 @@ atb_kernel(const double* __restrict__ a, const double* __restrict__ b, int64_t n
         }
 }
 
+// ------------------------------------------------------------------ multi-RHS CG matvec (r up to 32 per pass)
+// The SLQ / srht_2 passes apply Z^T (Z V) to r = 26 / `rank` right-hand sides (cg_tools.py:42-44 with a matrix `vec`,
+// rand_nys_constructors.py:18-36).  Two smem-tiled DFMA kernels, each reading the Z chunk once per 32 columns of V:
+//   zv_tile_kernel : T (n, 32) = Z (n, m) V (m, 32)         64 rows x 32 cols per CTA, K = m in chunks of 32
+//   ztt_tile_kernel: W (m, 32) += Z^T (m, n) T (n, 32)      64 Z-columns x 32 cols per CTA, K = n in chunks of 32
+// 128 threads, 4 x 4 fp64 micro-tile per thread (16 DFMA per 8 shared loads).
+constexpr int MR_ROWS = 64, MR_COLS = 32, MR_K = 32;
+
+// Both kernels prefetch the next K chunk from global memory into registers while the current one is multiplied out of
+// shared memory (one CTA's loads would otherwise sit exposed between two __syncthreads).
+__global__ void __launch_bounds__(128, 4)
+zv_tile_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double* __restrict__ v, int64_t ldv,
+               int r0, int rcount, double* __restrict__ t, int64_t ldt) {
+    __shared__ double zs[MR_ROWS][MR_K + 1];
+    __shared__ __align__(16) double vs[MR_K][MR_COLS];
+    const int64_t row0 = (int64_t)blockIdx.x * MR_ROWS;
+    const int tx = threadIdx.x & 7, ty = threadIdx.x >> 3;      // 8 column groups x 16 row groups
+    double acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+    double zr[16], vr[8];
+    auto fetch = [&](int64_t k0) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const int idx = i * 128 + threadIdx.x;
+            const int rr = idx / MR_K, kk = idx % MR_K;
+            const int64_t row = row0 + rr, k = k0 + kk;
+            zr[i] = (row < n && k < m) ? z[row * m + k] : 0.0;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int idx = i * 128 + threadIdx.x;
+            const int kk = idx / MR_COLS, cc = idx % MR_COLS;
+            const int64_t k = k0 + kk;
+            vr[i] = (k < m && cc < rcount) ? v[k * ldv + r0 + cc] : 0.0;
+        }
+    };
+    fetch(0);
+    for (int64_t k0 = 0; k0 < m; k0 += MR_K) {
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const int idx = i * 128 + threadIdx.x;
+            zs[idx / MR_K][idx % MR_K] = zr[i];
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int idx = i * 128 + threadIdx.x;
+            vs[idx / MR_COLS][idx % MR_COLS] = vr[i];
+        }
+        __syncthreads();
+        if (k0 + MR_K < m) fetch(k0 + MR_K);
+#pragma unroll 8
+        for (int kk = 0; kk < MR_K; ++kk) {
+            double zv[4], vv[4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) zv[a] = zs[ty * 4 + a][kk];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) vv[b] = vs[kk][tx * 4 + b];
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) acc[a][b] = fma(zv[a], vv[b], acc[a][b]);
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+        const int64_t row = row0 + ty * 4 + a;
+        if (row >= n) continue;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int cc = tx * 4 + b;
+            if (cc < rcount) t[row * ldt + r0 + cc] = acc[a][b];
+        }
+    }
+}
+
+__global__ void __launch_bounds__(128, 4)
+ztt_tile_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double* __restrict__ t, int64_t ldt,
+                int r0, int rcount, double* __restrict__ w, int64_t ldw) {
+    __shared__ __align__(16) double zs[MR_K][MR_ROWS];
+    __shared__ __align__(16) double ts[MR_K][MR_COLS];
+    const int64_t c0 = (int64_t)blockIdx.x * MR_ROWS;           // first Z column (= output row) of this CTA
+    const int tx = threadIdx.x & 7, ty = threadIdx.x >> 3;
+    double acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+    double zr[16], tr[8];
+    auto fetch = [&](int64_t k0) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const int idx = i * 128 + threadIdx.x;
+            const int kk = idx / MR_ROWS, cc = idx % MR_ROWS;
+            const int64_t row = k0 + kk, col = c0 + cc;
+            zr[i] = (row < n && col < m) ? z[row * m + col] : 0.0;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int idx = i * 128 + threadIdx.x;
+            const int kk = idx / MR_COLS, cc = idx % MR_COLS;
+            const int64_t row = k0 + kk;
+            tr[i] = (row < n && cc < rcount) ? t[row * ldt + r0 + cc] : 0.0;
+        }
+    };
+    fetch(0);
+    for (int64_t k0 = 0; k0 < n; k0 += MR_K) {
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const int idx = i * 128 + threadIdx.x;
+            zs[idx / MR_ROWS][idx % MR_ROWS] = zr[i];
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int idx = i * 128 + threadIdx.x;
+            ts[idx / MR_COLS][idx % MR_COLS] = tr[i];
+        }
+        __syncthreads();
+        if (k0 + MR_K < n) fetch(k0 + MR_K);
+#pragma unroll 8
+        for (int kk = 0; kk < MR_K; ++kk) {
+            double zv[4], tv[4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) zv[a] = zs[kk][ty * 4 + a];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) tv[b] = ts[kk][tx * 4 + b];
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) acc[a][b] = fma(zv[a], tv[b], acc[a][b]);
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+        const int64_t col = c0 + ty * 4 + a;
+        if (col >= m) continue;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int cc = tx * 4 + b;
+            if (cc < rcount) w[col * ldw + r0 + cc] += acc[a][b];
+        }
+    }
+}
+
 // ------------------------------------------------------------------ host
 int atb_accum(const double* a, const double* b, int64_t n, int64_t r, int64_t m, double* c, cudaStream_t st) {
     XB_REQUIRE(n > 0 && r > 0 && m > 0, "no datapoints");
@@ -258,15 +406,16 @@ int cg_matvec_accum(const double* z, int64_t n, int64_t m, const double* v, int6
     dim3 grid2((unsigned)colblocks, (unsigned)splits);
     int64_t wblocks = (n + 7) / 8;
     if (wblocks > 148 * 16) wblocks = 148 * 16;
-    for (int r0 = 0; r0 < r; r0 += 8) {
-        const int rc = (int)((r - r0 < 8) ? (r - r0) : 8);
-        if (rc == 1) {
-            z_times_kernel<1><<<(unsigned)wblocks, 256, 0, st>>>(z, n, m, v, r, r0, rc, scratch, r);
-            zt_times_kernel<1><<<grid2, 256, 0, st>>>(z, n, m, scratch, r, r0, rc, w, r, rows_per);
-        } else {
-            z_times_kernel<8><<<(unsigned)wblocks, 256, 0, st>>>(z, n, m, v, r, r0, rc, scratch, r);
-            zt_times_kernel<8><<<grid2, 256, 0, st>>>(z, n, m, scratch, r, r0, rc, w, r, rows_per);
-        }
+    if (r == 1) {
+        z_times_kernel<1><<<(unsigned)wblocks, 256, 0, st>>>(z, n, m, v, r, 0, 1, scratch, r);
+        zt_times_kernel<1><<<grid2, 256, 0, st>>>(z, n, m, scratch, r, 0, 1, w, r, rows_per);
+        count_launch(2);
+        return check_launch("cg_matvec");
+    }
+    for (int r0 = 0; r0 < r; r0 += MR_COLS) {
+        const int rc = (int)((r - r0 < MR_COLS) ? (r - r0) : MR_COLS);
+        zv_tile_kernel<<<(unsigned)((n + MR_ROWS - 1) / MR_ROWS), 128, 0, st>>>(z, n, m, v, r, r0, rc, scratch, r);
+        ztt_tile_kernel<<<(unsigned)((m + MR_ROWS - 1) / MR_ROWS), 128, 0, st>>>(z, n, m, scratch, r, r0, rc, w, r);
         count_launch(2);
     }
     return check_launch("cg_matvec");
