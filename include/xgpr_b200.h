@@ -93,6 +93,15 @@ int xgpr_b200_rbf_ztv_f32(const float*  x, int64_t n, int64_t d, const int8_t* r
 int xgpr_b200_rbf_ztv_f64(const double* x, int64_t n, int64_t d, const int8_t* radem, int64_t radem_len, const double* chi,
                           int64_t num_freqs, int fit_intercept, const double* t, double* w, void* stream);
 
+/* One-pass variant: w (2*num_freqs) f64 += Z^T (Z v) with the row's t = z . v reduced on chip (no t vector, one SORF per
+ * frequency).  Available when all repeats of a row fit one 512-thread CTA (num_freqs <= 8192 for d >= 64):
+ * xgpr_b200_rbf_zzv_supported() returns 1; otherwise use zv + ztv. */
+int xgpr_b200_rbf_zzv_supported(int64_t d, int64_t num_freqs);
+int xgpr_b200_rbf_zzv_f32(const float*  x, int64_t n, int64_t d, const int8_t* radem, int64_t radem_len, const float*  chi,
+                          int64_t num_freqs, int fit_intercept, const double* v, double* w, void* stream);
+int xgpr_b200_rbf_zzv_f64(const double* x, int64_t n, int64_t d, const int8_t* radem, int64_t radem_len, const double* chi,
+                          int64_t num_freqs, int fit_intercept, const double* v, double* w, void* stream);
+
 /* ---- cudaMiniARDGrad  (xgpr_cuda_rfgen_cpp_ext.cpp:50-59; gpu_rf_gen/rbf_ops/ard_ops.cu:87-148)
  * x (n, d); out (n, 2*num_freqs) f64; w (num_freqs, d) precomputed weights; sigma_map (d) i32;
  * sigma_vals (d) f64; grad (n, 2*num_freqs, num_lengthscales) f64.  All device pointers. */

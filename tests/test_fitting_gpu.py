@@ -95,7 +95,9 @@ def test_consumers_vs_numpy(shape):
 
 @pytest.mark.parametrize("dp", [False, True])
 @pytest.mark.parametrize("case", [(700, 64, 2048, True), (333, 20, 100, True), (129, 7, 6, False), (260, 512, 2048, True),
-                                  (50, 130, 1000, False), (1000, 64, 16384, True), (40, 1000, 300, True)])
+                                  (50, 130, 1000, False), (1000, 64, 16384, True), (40, 1000, 300, True),
+                                  (5000, 64, 16384, True), (777, 128, 16384, False), (300, 128, 32768, True),
+                                  (64, 9, 64, True), (100, 300, 8192, True)])
 def test_fused_matvec_equals_materialised(case, dp):
     """rbf_zv / rbf_ztv (features regenerated on chip) against transform_x(x) @ v and transform_x(x).T @ t."""
     from xgpr_b200.kernels import RBF, Matern
@@ -118,3 +120,14 @@ def test_fused_matvec_equals_materialised(case, dp):
     k.fused_ztv(xs, tin, w)
     np.testing.assert_allclose(t.cpu().numpy(), 0.5 + (z @ v).cpu().numpy(), rtol=1e-11, atol=1e-12)
     np.testing.assert_allclose(w.cpu().numpy(), -0.25 + (z.T @ tin).cpu().numpy(), rtol=1e-11, atol=1e-12)
+    # one-pass w += Z^T (Z v), wherever a row's repeats fit one CTA
+    from xgpr_b200 import ext
+    assert k.fused_zzv_ok() == ext.rbf_zzv_supported(d, k.num_freqs)
+    if k.fused_zzv_ok():
+        w2 = torch.full((m,), 0.125, dtype=torch.float64, device="cuda")
+        k.fused_zzv(xs, v, w2)
+        ref = 0.125 + (z.T @ (z @ v)).cpu().numpy()
+        np.testing.assert_allclose(w2.cpu().numpy(), ref, rtol=1e-10, atol=1e-11 * float(np.abs(ref).max()))
+    else:
+        with pytest.raises(RuntimeError):
+            k.fused_zzv(xs, v, torch.zeros(m, dtype=torch.float64, device="cuda"))

@@ -26,6 +26,7 @@ SIGNATURES = {
     "xgpr_b200_rbf_feature_gen": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _int, _ptr],
     "xgpr_b200_rbf_zv": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _int, _ptr, _ptr, _ptr],
     "xgpr_b200_rbf_ztv": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _int, _ptr, _ptr, _ptr],
+    "xgpr_b200_rbf_zzv": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _int, _ptr, _ptr, _ptr],
     "xgpr_b200_rbf_grad": [_ptr, _i64, _i64, _ptr, _ptr, _i64, _ptr, _i64, _ptr, _i64, _dbl, _int, _ptr],
     "xgpr_b200_ard_grad": [_ptr, _i64, _i64, _ptr, _ptr, _i64, _ptr, _ptr, _ptr, _i64, _int, _ptr],
     "xgpr_b200_conv1d_maxpool": [_ptr, _i64, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr, _int, _ptr],
@@ -62,6 +63,9 @@ EXPORTED.append("xgpr_b200_ztz_tc_workspace_bytes")
 lib.xgpr_b200_atb_tc_workspace_bytes.argtypes = [_i64, _i64, _i64, _int]
 lib.xgpr_b200_atb_tc_workspace_bytes.restype = _i64
 EXPORTED.append("xgpr_b200_atb_tc_workspace_bytes")
+lib.xgpr_b200_rbf_zzv_supported.argtypes = [_i64, _i64]
+lib.xgpr_b200_rbf_zzv_supported.restype = _int
+EXPORTED.append("xgpr_b200_rbf_zzv_supported")
 lib.xgpr_b200_tc_profile.argtypes = [_int]
 lib.xgpr_b200_tc_profile.restype = _int
 lib.xgpr_b200_tc_last_gemm_ms.argtypes = []

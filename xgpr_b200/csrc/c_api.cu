@@ -36,6 +36,10 @@ int rbf_dispatch(const T* x, int64_t n, int64_t d, double* out, double* grad, in
 template <typename T, int MODE>
 int rbf_matvec_dispatch(const T* x, int64_t n, int64_t d, const int8_t* radem, int64_t R, const T* chi, int64_t F,
                         int fit_intercept, const double* v, double* t, double* w, cudaStream_t st);
+template <typename T>
+int rbf_zzv_dispatch(const T* x, int64_t n, int64_t d, const int8_t* radem, int64_t R, const T* chi, int64_t F,
+                     int fit_intercept, const double* v, double* w, cudaStream_t st);
+int rbf_zzv_supported(int64_t d, int64_t F);
 template <typename T, int MODE>
 int conv_dispatch(const T* x, int64_t n, int64_t m, int64_t c, void* out, int64_t num_rffs, double* grad,
                   const int8_t* radem, int64_t R, const T* chi, int64_t F, const int32_t* seq_host,
@@ -110,6 +114,15 @@ int xgpr_b200_rbf_ztv_f32(const float* x, int64_t n, int64_t d, const int8_t* ra
 int xgpr_b200_rbf_ztv_f64(const double* x, int64_t n, int64_t d, const int8_t* radem, int64_t rl, const double* chi, int64_t nf, int fi,
                           const double* t, double* w, void* s) {
     return rbf_matvec_dispatch<double, 1>(x, n, d, radem, rl, chi, nf, fi, nullptr, const_cast<double*>(t), w, ST(s));
+}
+int xgpr_b200_rbf_zzv_supported(int64_t d, int64_t num_freqs) { return rbf_zzv_supported(d, num_freqs); }
+int xgpr_b200_rbf_zzv_f32(const float* x, int64_t n, int64_t d, const int8_t* radem, int64_t rl, const float* chi, int64_t nf, int fi,
+                          const double* v, double* w, void* s) {
+    return rbf_zzv_dispatch<float>(x, n, d, radem, rl, chi, nf, fi, v, w, ST(s));
+}
+int xgpr_b200_rbf_zzv_f64(const double* x, int64_t n, int64_t d, const int8_t* radem, int64_t rl, const double* chi, int64_t nf, int fi,
+                          const double* v, double* w, void* s) {
+    return rbf_zzv_dispatch<double>(x, n, d, radem, rl, chi, nf, fi, v, w, ST(s));
 }
 
 int xgpr_b200_ard_grad_f32(const float* x, int64_t n, int64_t d, double* out, const float* w, int64_t nf, const int32_t* smap,

@@ -129,6 +129,26 @@ def rbf_ztv(inputArr, radem, chiArr, fitIntercept, t, w):
         int(bool(fitIntercept)), t.data_ptr(), w.data_ptr(), _stream()))
 
 
+def rbf_zzv_supported(xdim_last, num_freqs):
+    """True when the one-pass fused matvec can hold all repeats of a row in one CTA."""
+    return bool(lib.xgpr_b200_rbf_zzv_supported(int(xdim_last), int(num_freqs)))
+
+
+def rbf_zzv(inputArr, radem, chiArr, fitIntercept, v, w):
+    """w (2F) += Z^T (Z v) in ONE pass over the rows (t reduced on chip), Z as in rbf_zv."""
+    x = _dev(inputArr, "inputArr", _SFX, 2)
+    r = _radem3(radem)
+    c = _dev(chiArr, "chiArr", _SFX, 1)
+    _same(x, c, "inputArr", "chiArr")
+    v = _dev(v, "v", (torch.float64,), 1)
+    w = _dev(w, "w", (torch.float64,), 1)
+    if w.shape[0] != 2 * c.shape[0] or v.shape[0] != 2 * c.shape[0]:
+        raise RuntimeError("wrong array sizes")
+    check(getattr(lib, "xgpr_b200_rbf_zzv" + _SFX[x.dtype])(
+        x.data_ptr(), x.shape[0], x.shape[1], r.data_ptr(), r.shape[2], c.data_ptr(), c.shape[0],
+        int(bool(fitIntercept)), v.data_ptr(), w.data_ptr(), _stream()))
+
+
 def cudaRBFGrad(inputArr, outputArr, gradArr, radem, chiArr, sigma, fitIntercept):
     x = _dev(inputArr, "inputArr", _SFX, 2)
     o = _dev(outputArr, "outputArr", (torch.float64,), 2)

@@ -245,6 +245,7 @@ class ConjugateGrad:
         self.ops = ops
         self._scratch = None
         self._staged = None
+        self.one_pass = True
 
     def _staged_blocks(self, dataset, kernel, budget_bytes=8 << 30):
         """The sigma-scaled device copies of the shard's x blocks for the fused passes.  x * sigma does not change during
@@ -278,7 +279,11 @@ class ConjugateGrad:
         if _fused_ok(kernel, self.ops) and vec.shape[1] == 1:
             # one right-hand side: two fused feature passes per block, Z never written to HBM
             v1, w1 = vec[:, 0].contiguous(), matvec[:, 0]
+            one_pass = self.one_pass and getattr(kernel, "fused_zzv_ok", lambda: False)()
             for xs, t in self._staged_blocks(dataset, kernel):
+                if one_pass:                     # t = z . v reduced on chip: one SORF per frequency per iteration
+                    kernel.fused_zzv(xs, v1, w1)
+                    continue
                 t.zero_()
                 kernel.fused_zv(xs, v1, t)
                 kernel.fused_ztv(xs, t, w1)

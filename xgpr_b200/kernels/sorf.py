@@ -70,6 +70,13 @@ class SORFKernelBaseclass(KernelBaseclass):
     def fused_ztv(self, xs, t, w):
         ext.rbf_ztv(xs, self.radem_diag, self.chi_arr, self.fit_intercept, t, w)
 
+    def fused_zzv_ok(self):
+        return ext.rbf_zzv_supported(self._xdim[-1], self.num_freqs)
+
+    def fused_zzv(self, xs, v, w):
+        """w += Z^T (Z v) in one pass (t reduced on chip); only when fused_zzv_ok()."""
+        ext.rbf_zzv(xs, self.radem_diag, self.chi_arr, self.fit_intercept, v, w)
+
     def kernel_specific_gradient(self, input_x, sequence_length=None):
         output_x = torch.empty((input_x.shape[0], self.num_rffs), dtype=torch.float64, device=input_x.device)
         dz_dsigma = torch.empty((input_x.shape[0], self.num_rffs, 1), dtype=torch.float64, device=input_x.device)
