@@ -347,8 +347,8 @@ def run_b200(args):
         bf16_peak = tensor_peak()
         line["gram"] = {
             "metric": "Z^T Z accumulation (exact-fit Gram), fp64-equivalent TFLOP/s per GPU",
-            "workload": "Z (%d x %d) fp64 features per call per GPU, %d int8 digit planes, upper triangle + mirror"
-                        % (gram["n"], gram["m"], gram["slices"]),
+            "workload": "Z (%d x %d) fp64 features per call per GPU, %d int8 digit planes of %d bits (element error "
+                        "<= n 2^-37 colmax^2), upper triangle + mirror" % (gram["n"], gram["m"], gram["slices"], gram["bits"]),
             "value": 2.0 * gram["n"] * gram["m"] ** 2 / (gram_ms * 1e-3) / 1e12, "unit": "TFLOP/s (fp64-equivalent)",
             "ms_per_call": gram_ms, "dfma_kernel_ms": gram_dfma_ms,
             "speedup_vs_fp64_pipe": gram_dfma_ms / gram_ms, "gpu_launches_per_call": gram["launches"],
@@ -406,7 +406,7 @@ def tensor_peak():
     return 1590.0
 
 
-def gram_headline(dev, rank, n=32768, m=8192, slices=6, steps=3):
+def gram_headline(dev, rank, n=32768, m=8192, slices=5, bits=8, steps=3):
     """The dense contraction of the path: Z^T Z for the exact fit (exact_nmll_calcs.py:68-72) on the tensor cores
     (csrc/gram_tc_kernels.cu), next to the fp64-pipe kernel it replaces.  int8 ops counted = what the GEMM kernel
     issues: upper-triangle 256 x 256 tiles x slices (slices + 1) / 2 plane pairs x 2 n_pad 256^2."""
@@ -429,12 +429,12 @@ def gram_headline(dev, rank, n=32768, m=8192, slices=6, steps=3):
         torch.cuda.synchronize()
         return a.elapsed_time(b) / reps, (ext.launch_count() - l0) // reps
 
-    tc_ms, launches = timed(lambda: ext.ztz_accum_tc(z, acc, num_slices=slices), steps)
+    tc_ms, launches = timed(lambda: ext.ztz_accum_tc(z, acc, num_slices=slices, digit_bits=bits), steps)
     # the GEMM kernel alone: CUDA events recorded by the library around its launch, on the launching stream
     ext.tc_profile(True)
     gemm = []
     for _ in range(steps):
-        ext.ztz_accum_tc(z, acc, num_slices=slices)
+        ext.ztz_accum_tc(z, acc, num_slices=slices, digit_bits=bits)
         gemm.append(ext.tc_last_gemm_ms())
     ext.tc_profile(False)
     gemm_ms = float(np.mean(gemm))
@@ -444,7 +444,7 @@ def gram_headline(dev, rank, n=32768, m=8192, slices=6, steps=3):
     int8_ops = tiles * (tiles + 1) // 2 * (slices * (slices + 1) // 2) * 2.0 * n_pad * 256 * 256
     del z, acc
     return {"tc_ms": tc_ms, "gemm_ms": gemm_ms, "dfma_ms": dfma_ms, "n": n, "m": m,
-            "slices": slices, "launches": launches, "int8_ops": int8_ops}
+            "slices": slices, "bits": bits, "launches": launches, "int8_ops": int8_ops}
 
 
 def kern_cpu_copy():

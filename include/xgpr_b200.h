@@ -150,14 +150,16 @@ int xgpr_b200_zty_accum_f64(const double* z, int64_t n, int64_t m, const double*
 /* ztz (m, m) += Z^T Z (full symmetric matrix written) */
 int xgpr_b200_ztz_accum_f64(const double* z, int64_t n, int64_t m, double* ztz, void* stream);
 /* Tensor-core Gram (tcgen05.mma kind::i8, int32 accumulators in TMEM): the upper triangle of
- * ztz (m, m) += Z^T Z, computed from `num_slices` (2..7) error-free int8 digit planes of Z with exact int32
- * accumulation; element error of the update <= ~ n * 2^(-7*num_slices) * colmax_i * colmax_j (6 slices: fp64 level).
+ * ztz (m, m) += Z^T Z, computed from `num_slices` (2..7) error-free int8 digit planes of Z (`digit_bits` = 7: balanced
+ * base-128 digits, or 8: base-256) with exact int32 accumulation; element error of the update
+ * <= n * 2^(3 - digit_bits*num_slices) * colmax_i * colmax_j  (6 x 7 bits: 2e-12 n, typical 1e-13 n: fp64 level;
+ * 5 x 8 bits: 4x that bound at 15 instead of 21 plane products).
  * mirror != 0: afterwards copy the upper triangle over the lower one (ztz must have been symmetric on entry, e.g.
  * zero or the result of earlier calls); mirror == 0: lower triangle untouched, call xgpr_b200_symmetrize_upper_f64
  * once after the last chunk.  workspace: device memory, 256-byte aligned, >= xgpr_b200_ztz_tc_workspace_bytes(). */
 int64_t xgpr_b200_ztz_tc_workspace_bytes(int64_t n, int64_t m, int num_slices);
-int xgpr_b200_ztz_accum_tc_f64(const double* z, int64_t n, int64_t m, double* ztz, int num_slices, int mirror,
-                               void* workspace, int64_t workspace_bytes, void* stream);
+int xgpr_b200_ztz_accum_tc_f64(const double* z, int64_t n, int64_t m, double* ztz, int num_slices, int digit_bits,
+                               int mirror, void* workspace, int64_t workspace_bytes, void* stream);
 int xgpr_b200_symmetrize_upper_f64(double* g, int64_t m, void* stream);
 /* Measurement aid: with profiling enabled the library brackets each tensor-core GEMM launch with CUDA events on the
  * launching stream; xgpr_b200_tc_last_gemm_ms() synchronises on the last bracket and returns its duration (-1: none). */
@@ -167,7 +169,7 @@ double xgpr_b200_tc_last_gemm_ms(void);
  * (`acc_results += compressor.transform_x(xdata).T @ xdata`, src/xGPR/preconditioners/rand_nys_constructors.py:119). */
 int64_t xgpr_b200_atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int num_slices);
 int xgpr_b200_atb_accum_tc_f64(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc,
-                               int num_slices, void* workspace, int64_t workspace_bytes, void* stream);
+                               int num_slices, int digit_bits, void* workspace, int64_t workspace_bytes, void* stream);
 /* acc (r, m) += A^T Z ;  A (n, r) row-major: the Nystrom sketch accumulation
  * `acc_results += compressor.transform_x(xdata).T @ xdata` (src/xGPR/preconditioners/rand_nys_constructors.py:119) */
 int xgpr_b200_atb_accum_f64(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc, void* stream);

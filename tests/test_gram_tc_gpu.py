@@ -30,9 +30,9 @@ def test_dyadic_inputs_bit_exact(shape, slices):
     ext = _ext()
     zt = torch.from_numpy(z).to(DEV)
     g = torch.zeros((m, m), dtype=torch.float64, device=DEV)
-    ext.ztz_accum_tc(zt, g, num_slices=slices)
+    ext.ztz_accum_tc(zt, g, num_slices=slices, digit_bits=7)
     assert np.array_equal(g.cpu().numpy(), ref)
-    ext.ztz_accum_tc(zt, g, num_slices=slices, mirror=False)      # accumulates; lower triangle untouched
+    ext.ztz_accum_tc(zt, g, num_slices=slices, mirror=False, digit_bits=7)      # accumulates; lower triangle untouched
     got = g.cpu().numpy()
     assert np.array_equal(np.triu(got), np.triu(2 * ref))
     assert np.array_equal(np.tril(got, -1), np.tril(ref, -1))
@@ -51,7 +51,7 @@ def test_feature_inputs_error_bound(shape, slices):
     ref = z.T @ z
     ext = _ext()
     g = torch.zeros((m, m), dtype=torch.float64, device=DEV)
-    ext.ztz_accum_tc(torch.from_numpy(z).to(DEV), g, num_slices=slices)
+    ext.ztz_accum_tc(torch.from_numpy(z).to(DEV), g, num_slices=slices, digit_bits=7)
     cmax = np.abs(z).max(axis=0)
     bound = n * 2.0 ** (-7 * slices + 2) * cmax[:, None] * cmax[None, :] + 1e-15 * n * cmax[:, None] * cmax[None, :]
     err = np.abs(g.cpu().numpy() - ref)
@@ -67,8 +67,14 @@ def test_row_passes_and_zero_columns():
     z[:, 5] = 0.0
     ext = _ext()
     g = torch.zeros((m, m), dtype=torch.float64, device=DEV)
-    ext.ztz_accum_tc(torch.from_numpy(z).to(DEV), g, num_slices=4)
+    ext.ztz_accum_tc(torch.from_numpy(z).to(DEV), g, num_slices=4, digit_bits=7)
     assert np.array_equal(g.cpu().numpy(), z.T @ z)
+    # 8-bit digits at full magnitude: every leading digit is +-127, so a weight group's accumulator would pass 2^31 after
+    # 133k row-pairs; the kernel must drain it in time (5 planes x 70,000 rows = 350k row-pairs in the heaviest group)
+    zz = np.where(rng.random((n, m)) < 0.5, -1.0, 1.0) * (127.0 / 256.0 + 127.0 / 65536.0)
+    g.zero_()
+    ext.ztz_accum_tc(torch.from_numpy(zz).to(DEV), g, num_slices=5, digit_bits=8)
+    assert np.array_equal(g.cpu().numpy(), zz.T @ zz)
 
 
 def test_matches_dfma_gram_on_large_tile_grid():
@@ -80,7 +86,7 @@ def test_matches_dfma_gram_on_large_tile_grid():
     g0 = torch.zeros((m, m), dtype=torch.float64, device=DEV)
     g1 = torch.zeros((m, m), dtype=torch.float64, device=DEV)
     ext.ztz_accum(z, g0)
-    ext.ztz_accum_tc(z, g1, num_slices=7)
+    ext.ztz_accum_tc(z, g1, num_slices=7, digit_bits=7)
     scale = float(g0.diagonal().max())
     assert float((g0 - g1).abs().max()) <= 1e-13 * scale * 8
 
@@ -92,6 +98,8 @@ def test_argument_errors():
         ext.ztz_accum_tc(z, torch.zeros((8, 7), dtype=torch.float64, device=DEV))
     with pytest.raises(RuntimeError):
         ext.ztz_accum_tc(z, torch.zeros((8, 8), dtype=torch.float64, device=DEV), num_slices=9)
+    with pytest.raises(RuntimeError):
+        ext.ztz_accum_tc(z, torch.zeros((8, 8), dtype=torch.float64, device=DEV), digit_bits=6)
     with pytest.raises(TypeError):
         ext.ztz_accum_tc(z.float(), torch.zeros((8, 8), dtype=torch.float64, device=DEV))
 
@@ -105,9 +113,9 @@ def test_atb_dyadic_bit_exact(shape):
     z = rng.integers(-100, 101, size=(n, m)).astype(np.float64) / 128.0
     ext = _ext()
     acc = torch.zeros((r, m), dtype=torch.float64, device=DEV)
-    ext.atb_accum_tc(torch.from_numpy(a).to(DEV), torch.from_numpy(z).to(DEV), acc, num_slices=4)
+    ext.atb_accum_tc(torch.from_numpy(a).to(DEV), torch.from_numpy(z).to(DEV), acc, num_slices=4, digit_bits=7)
     assert np.array_equal(acc.cpu().numpy(), a.T @ z)
-    ext.atb_accum_tc(torch.from_numpy(a).to(DEV), torch.from_numpy(z).to(DEV), acc, num_slices=4)
+    ext.atb_accum_tc(torch.from_numpy(a).to(DEV), torch.from_numpy(z).to(DEV), acc, num_slices=4, digit_bits=7)
     assert np.array_equal(acc.cpu().numpy(), 2 * (a.T @ z))
 
 
@@ -118,6 +126,45 @@ def test_atb_general_error_bound():
     z = np.cos(rng.standard_normal((n, m)) * 3) * np.sqrt(2.0 / m)
     ext = _ext()
     acc = torch.zeros((r, m), dtype=torch.float64, device=DEV)
-    ext.atb_accum_tc(torch.from_numpy(a).to(DEV), torch.from_numpy(z).to(DEV), acc, num_slices=6)
+    ext.atb_accum_tc(torch.from_numpy(a).to(DEV), torch.from_numpy(z).to(DEV), acc, num_slices=6, digit_bits=7)
     bound = n * 2.0 ** (-40) * np.abs(a).max(axis=0)[:, None] * np.abs(z).max(axis=0)[None, :]
     assert (np.abs(acc.cpu().numpy() - a.T @ z) <= bound).all()
+
+
+@pytest.mark.parametrize("shape", [(128, 256), (1000, 700), (20000, 300), (4096, 1024)])
+def test_base256_digits_bit_exact_and_bounded(shape):
+    """digit_bits = 8 (balanced base-256 digits, 16,384-row passes): dyadic inputs stay bit-exact, columns of ones / just
+    under a power of two (leading-digit guard) included; feature-shaped inputs within n * 2^(3 - 8 s) colmax_i colmax_j."""
+    n, m = shape
+    rng = np.random.default_rng(n + m)
+    z = rng.integers(-8000, 8001, size=(n, m)).astype(np.float64) / 16384.0
+    z[:, 0] = 1.0
+    z[:, 1] = 0.999
+    z[:, 2] = -0.5
+    ext = _ext()
+    g = torch.zeros((m, m), dtype=torch.float64, device=DEV)
+    ext.ztz_accum_tc(torch.from_numpy(z).to(DEV), g, num_slices=5, digit_bits=8)
+    zq = z.copy()
+    zq[:, 1] = np.round(z[:, 1] * 2.0 ** 38) / 2.0 ** 38          # 0.999 is not dyadic: compare against its 5 x 8-bit rounding
+    ref = zq.T @ zq
+    got = g.cpu().numpy()
+    mask = np.ones((m, m), bool)
+    mask[1, :] = mask[:, 1] = False
+    assert np.array_equal(got[mask], (z.T @ z)[mask])
+    np.testing.assert_allclose(got[1, :], ref[1, :], rtol=0, atol=n * 2.0 ** -36)
+    f = np.cos(rng.standard_normal((n, m)) * 3).astype(np.float32).astype(np.float64) * np.sqrt(2.0 / m)
+    f[:, 0] = 1.0
+    for s_, bits in ((5, 8), (6, 8), (4, 8)):
+        g.zero_()
+        ext.ztz_accum_tc(torch.from_numpy(f).to(DEV), g, num_slices=s_, digit_bits=bits)
+        cmax = np.abs(f).max(axis=0)
+        bound = n * (2.0 ** (3 - bits * s_) + 1e-15) * cmax[:, None] * cmax[None, :]
+        err = np.abs(g.cpu().numpy() - f.T @ f)
+        assert (err <= bound).all(), (s_, bits, float((err / bound).max()))
+    acc = torch.zeros((64, m), dtype=torch.float64, device=DEV)
+    a = rng.integers(-100, 101, size=(n, 64)).astype(np.float64) / 128.0
+    ext.atb_accum_tc(torch.from_numpy(a).to(DEV), torch.from_numpy(z).to(DEV), acc, num_slices=5, digit_bits=8)
+    got = acc.cpu().numpy()
+    keep = np.ones(m, bool)
+    keep[1] = False
+    assert np.array_equal(got[:, keep], (a.T @ z)[:, keep])

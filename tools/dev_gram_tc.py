@@ -33,12 +33,12 @@ def main():
         z = torch.cos(torch.randn((n, m), device=dev, dtype=torch.float64) * 3).float().double() * (2.0 / m) ** 0.5
         z[:, 0] = 1.0
         ref = z.T @ z
-        for s in (2, 3, 4, 5, 6, 7):
+        for s, bits in ((4, 7), (5, 7), (6, 7), (7, 7), (4, 8), (5, 8), (6, 8)):
             g = torch.zeros((m, m), dtype=torch.float64, device=dev)
-            ext.ztz_accum_tc(z, g, num_slices=s)
+            ext.ztz_accum_tc(z, g, num_slices=s, digit_bits=bits)
             err = (g - ref).abs()
             d = ref.diagonal().sqrt()
-            print(json.dumps({"case": "features", "n": n, "m": m, "s": s, "max_abs": float(err.max()),
+            print(json.dumps({"case": "features", "n": n, "m": m, "s": s, "bits": bits, "max_abs": float(err.max()),
                               "max_rel_to_diag": float((err / (d[:, None] * d[None, :])).max())}))
     # timing
     for (n, m) in [(32768, 8192), (32768, 4096), (65536, 2048)]:
@@ -48,10 +48,10 @@ def main():
         tt = timed(lambda: torch.addmm(g, z.T, z, out=g), 2)
         row = {"case": "timing", "n": n, "m": m, "dfma_ms": t64, "cublas_dgemm_ms": tt,
                "dfma_tflops": 2 * n * m * m / t64 / 1e9}
-        for s in (4, 6):
-            ts = timed(lambda: ext.ztz_accum_tc(z, g, num_slices=s), 3)
-            row[f"tc_s{s}_ms"] = ts
-            row[f"tc_s{s}_eff_tflops"] = 2 * n * m * m / ts / 1e9
+        for s, bits in ((4, 7), (6, 7), (5, 8), (4, 8)):
+            ts = timed(lambda: ext.ztz_accum_tc(z, g, num_slices=s, digit_bits=bits), 3)
+            row[f"tc_s{s}b{bits}_ms"] = ts
+            row[f"tc_s{s}b{bits}_eff_tflops"] = 2 * n * m * m / ts / 1e9
         print(json.dumps(row))
 
 

@@ -37,9 +37,9 @@ SIGNATURES = {
 F64_ONLY = {
     "xgpr_b200_zty_accum_f64": [_ptr, _i64, _i64, _ptr, _ptr, _ptr],
     "xgpr_b200_ztz_accum_f64": [_ptr, _i64, _i64, _ptr, _ptr],
-    "xgpr_b200_ztz_accum_tc_f64": [_ptr, _i64, _i64, _ptr, _int, _int, _ptr, _i64, _ptr],
+    "xgpr_b200_ztz_accum_tc_f64": [_ptr, _i64, _i64, _ptr, _int, _int, _int, _ptr, _i64, _ptr],
     "xgpr_b200_symmetrize_upper_f64": [_ptr, _i64, _ptr],
-    "xgpr_b200_atb_accum_tc_f64": [_ptr, _ptr, _i64, _i64, _i64, _ptr, _int, _ptr, _i64, _ptr],
+    "xgpr_b200_atb_accum_tc_f64": [_ptr, _ptr, _i64, _i64, _i64, _ptr, _int, _int, _ptr, _i64, _ptr],
     "xgpr_b200_atb_accum_f64": [_ptr, _ptr, _i64, _i64, _i64, _ptr, _ptr],
     "xgpr_b200_cg_matvec_accum_f64": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _ptr, _ptr],
 }

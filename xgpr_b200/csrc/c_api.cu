@@ -52,14 +52,14 @@ int zty_accum(const double* z, int64_t n, int64_t m, const double* y, double* zt
 int ztz_accum(const double* z, int64_t n, int64_t m, double* ztz, cudaStream_t st);
 int atb_accum(const double* a, const double* b, int64_t n, int64_t r, int64_t m, double* c, cudaStream_t st);
 int64_t ztz_tc_workspace_bytes(int64_t n, int64_t m, int num_slices);
-int ztz_accum_tc(const double* z, int64_t n, int64_t m, double* ztz, int num_slices, int mirror, void* workspace,
-                 int64_t workspace_bytes, cudaStream_t st);
+int ztz_accum_tc(const double* z, int64_t n, int64_t m, double* ztz, int num_slices, int digit_bits, int mirror,
+                 void* workspace, int64_t workspace_bytes, cudaStream_t st);
 int symmetrize_upper(double* g, int64_t m, cudaStream_t st);
 void tc_profile(int enable);
 double tc_last_gemm_ms();
 int64_t atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int num_slices);
 int atb_accum_tc(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc, int num_slices,
-                 void* workspace, int64_t workspace_bytes, cudaStream_t st);
+                 int digit_bits, void* workspace, int64_t workspace_bytes, cudaStream_t st);
 int cg_matvec_accum(const double* z, int64_t n, int64_t m, const double* v, int64_t r, double* w,
                     double* scratch, cudaStream_t st);
 
@@ -166,9 +166,9 @@ int xgpr_b200_zty_accum_f64(const double* z, int64_t n, int64_t m, const double*
 }
 int xgpr_b200_ztz_accum_f64(const double* z, int64_t n, int64_t m, double* ztz, void* s) { return ztz_accum(z, n, m, ztz, ST(s)); }
 int64_t xgpr_b200_ztz_tc_workspace_bytes(int64_t n, int64_t m, int num_slices) { return ztz_tc_workspace_bytes(n, m, num_slices); }
-int xgpr_b200_ztz_accum_tc_f64(const double* z, int64_t n, int64_t m, double* ztz, int num_slices, int mirror,
-                               void* workspace, int64_t workspace_bytes, void* s) {
-    return ztz_accum_tc(z, n, m, ztz, num_slices, mirror, workspace, workspace_bytes, ST(s));
+int xgpr_b200_ztz_accum_tc_f64(const double* z, int64_t n, int64_t m, double* ztz, int num_slices, int digit_bits,
+                               int mirror, void* workspace, int64_t workspace_bytes, void* s) {
+    return ztz_accum_tc(z, n, m, ztz, num_slices, digit_bits, mirror, workspace, workspace_bytes, ST(s));
 }
 int xgpr_b200_symmetrize_upper_f64(double* g, int64_t m, void* s) { return symmetrize_upper(g, m, ST(s)); }
 int xgpr_b200_tc_profile(int enable) { tc_profile(enable); return XGPR_B200_OK; }
@@ -177,8 +177,8 @@ int64_t xgpr_b200_atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int nu
     return atb_tc_workspace_bytes(n, r, m, num_slices);
 }
 int xgpr_b200_atb_accum_tc_f64(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc,
-                               int num_slices, void* workspace, int64_t workspace_bytes, void* s) {
-    return atb_accum_tc(a, z, n, r, m, acc, num_slices, workspace, workspace_bytes, ST(s));
+                               int num_slices, int digit_bits, void* workspace, int64_t workspace_bytes, void* s) {
+    return atb_accum_tc(a, z, n, r, m, acc, num_slices, digit_bits, workspace, workspace_bytes, ST(s));
 }
 int xgpr_b200_atb_accum_f64(const double* a, const double* b, int64_t n, int64_t r, int64_t m, double* c, void* s) {
     return atb_accum(a, b, n, r, m, c, ST(s));

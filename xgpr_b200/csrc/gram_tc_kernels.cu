@@ -53,19 +53,23 @@ tc_colmax_kernel(const double* __restrict__ z, int64_t n, int64_t m, unsigned lo
     atomicMax(cmax + col, (unsigned long long)__double_as_longlong(mx));
 }
 
-// exponent e with mx <= 2^(e-1); colscale = 2^e
-__global__ void tc_exponent_kernel(const unsigned long long* __restrict__ cmax, int64_t m, double* __restrict__ colscale) {
+// exponent e with mx <= 2^(e-1); colscale = 2^e.  With 8-bit digits the leading digit rint(x * 256) must stay <= 127, so a
+// column whose maximum lies within 1/128 below a power of two takes the next exponent.
+__global__ void tc_exponent_kernel(const unsigned long long* __restrict__ cmax, int64_t m, double* __restrict__ colscale,
+                                   int digit_bits) {
     const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (col >= m) return;
     const double mx = __longlong_as_double((long long)cmax[col]);
     int q = 0;
-    if (mx > 0.0 && mx < 1e300) frexp(mx, &q);    // mx = f * 2^q, f in [0.5, 1)  =>  mx <= 2^q
+    double f = 0.0;
+    if (mx > 0.0 && mx < 1e300) f = frexp(mx, &q);    // mx = f * 2^q, f in [0.5, 1)  =>  mx <= 2^q
+    if (digit_bits == 8 && f >= 0.9921875) ++q;
     colscale[col] = ldexp(1.0, q + 1);
 }
 
 // ------------------------------------------------------------------ fp64 -> s int8 digit planes, transposed
 // Tile: 128 rows (n) x 32 columns (m).  planes[k][col][row], row contiguous (K-major), row stride n_pad.
-template <int S>
+template <int S, int BITS>
 __global__ void __launch_bounds__(256)
 tc_slice_kernel(const double* __restrict__ z, int64_t n, int64_t m, int64_t n_pad,
                 const double* __restrict__ colscale, int8_t* __restrict__ planes) {
@@ -74,8 +78,9 @@ tc_slice_kernel(const double* __restrict__ z, int64_t n, int64_t m, int64_t n_pa
     const int64_t m0 = (int64_t)blockIdx.x * 32, n0 = (int64_t)blockIdx.y * 128;
     const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
     const int64_t col = m0 + lane;
-    // multiply by 2^(7S) / colscale: both powers of two, product exact
-    const double mul = (col < m) ? ldexp(1.0 / colscale[col], 7 * S) : 0.0;
+    // multiply by 2^(BITS * S) / colscale: both powers of two, product exact
+    constexpr long long HALF = 1ll << (BITS - 1), MASK = (1ll << BITS) - 1, TOP = BITS == 8 ? 127 : 64;
+    const double mul = (col < m) ? ldexp(1.0 / colscale[col], BITS * S) : 0.0;
 #pragma unroll 4
     for (int r = 0; r < 16; ++r) {
         const int row = r * 8 + wrp;
@@ -85,11 +90,11 @@ tc_slice_kernel(const double* __restrict__ z, int64_t n, int64_t m, int64_t n_pa
         long long X = __double2ll_rn(v * mul);
 #pragma unroll
         for (int k = S - 1; k >= 1; --k) {
-            const long long d = ((X + 64) & 127) - 64;      // balanced digit in [-64, 63]
+            const long long d = ((X + HALF) & MASK) - HALF;  // balanced digit in [-2^(BITS-1), 2^(BITS-1) - 1]
             dig[k][lane][row] = (int8_t)d;
-            X = (X - d) >> 7;
+            X = (X - d) >> BITS;
         }
-        X = X > 64 ? 64 : (X < -64 ? -64 : X);              // |X| <= 64 by construction; clamp guards Inf/NaN input
+        X = X > TOP ? TOP : (X < -TOP ? -TOP : X);          // |X| <= TOP by construction; clamp guards Inf/NaN input
         dig[0][lane][row] = (int8_t)X;
     }
     __syncthreads();
@@ -190,7 +195,7 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 // Per 128-byte K block: 64 KB of operands for 2 x 4 MMAs (1024 tensor-pipe cycles) = 64 B/clk/SM of smem fill, which
 // is what bounds this kernel (the int8 pipe outruns L2), hence the large tile.
 struct TcSched {
-    int num_slices, n_kblocks, tiles, num_tiles, full_waves, split_remainder, symmetric;
+    int num_slices, n_kblocks, tiles, num_tiles, full_waves, split_remainder, symmetric, digit_bits, max_kb_acc;
 };
 struct TcSeg { int tile, kb0, kb1; };
 
@@ -280,9 +285,12 @@ tc_gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 int ti, tj;
                 tc_tile_coords(sc, sg.tile, ti, tj);
                 for (int g = sc.num_slices - 1; g >= 0; --g) {
+                  const int step = sc.max_kb_acc / (g + 1);          // K blocks one int32 accumulator may take per pair
+                  for (int sb = sg.kb0; sb < sg.kb1; sb += step) {
+                    const int se = (sb + step < sg.kb1) ? sb + step : sg.kb1;
                     for (int k = 0; k <= g; ++k) {
                         const int l = g - k;
-                        for (int kb = sg.kb0; kb < sg.kb1; ++kb, ++ks) {
+                        for (int kb = sb; kb < se; ++kb, ++ks) {
                             const int st = ks % TC_STAGES;
                             mbar_wait(empty_bar(st), ((ks / TC_STAGES) & 1) ^ 1);
                             const uint32_t dst = smem_base + st * TC_STAGE_BYTES;
@@ -293,6 +301,7 @@ tc_gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                             tma_load_3d(dst + 3 * 16384, &map_b, full_bar(st), kb * TC_BK, tj * TC_TILE + 128, l);
                         }
                     }
+                  }
                 }
             }
         }
@@ -303,10 +312,13 @@ tc_gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             for (int si = 0; si < sc.full_waves + 2; ++si) {
                 const TcSeg sg = tc_segment(sc, si, blockIdx.x, gridDim.x);
                 if (sg.kb1 <= sg.kb0) continue;
-                for (int g = sc.num_slices - 1; g >= 0; --g, ++it) {
+                for (int g = sc.num_slices - 1; g >= 0; --g) {
+                  const int step = sc.max_kb_acc / (g + 1);
+                  for (int sb = sg.kb0; sb < sg.kb1; sb += step, ++it) {
+                    const int se = (sb + step < sg.kb1) ? sb + step : sg.kb1;
                     mbar_wait(tempty_bar, (it & 1) ^ 1);                 // epilogue has drained the accumulators
                     tc_fence_after();
-                    const int nblk = (g + 1) * (sg.kb1 - sg.kb0);
+                    const int nblk = (g + 1) * (se - sb);
                     for (int b = 0; b < nblk; ++b, ++ks) {
                         const int st = ks % TC_STAGES;
                         mbar_wait(full_bar(st), (ks / TC_STAGES) & 1);
@@ -323,6 +335,7 @@ tc_gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                         tc_commit(empty_bar(st));                       // smem slot free once these MMAs retire
                     }
                     tc_commit(tfull_bar);                               // accumulators complete
+                  }
                 }
             }
         }
@@ -343,10 +356,12 @@ tc_gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             const double rs = (row < ma) ? scale_a[row] : 0.0;
             const int64_t diag = sc.symmetric ? wrow0 : 0;          // first column this warp may write
             const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 256);
-            for (int g = sc.num_slices - 1; g >= 0; --g, ++it) {
+            for (int g = sc.num_slices - 1; g >= 0; --g) {
+              const int step = sc.max_kb_acc / (g + 1);
+              for (int sb = sg.kb0; sb < sg.kb1; sb += step, ++it) {
                 mbar_wait(tfull_bar, it & 1);
                 tc_fence_after();
-                const double rsg = rs * exp2(-7.0 * (g + 2));     // exact power of two
+                const double rsg = rs * exp2(-(double)(sc.digit_bits * (g + 2)));     // exact power of two
 #pragma unroll 1
                 for (int c = 0; c < TC_TILE / 32; ++c) {
                     const int64_t cb = col0 + c * 32;
@@ -371,6 +386,7 @@ tc_gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(tempty_bar);
+              }
             }
         }
     }
@@ -419,6 +435,8 @@ static EncodeTiledFn encode_tiled_fn() {
 static inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
 
 // One operand's share of the workspace: [cmax u64 (m)] [colscale f64 (m)] [planes int8 (S, m, n_pad)], 1024-byte aligned
+// rows per pass (one set of column exponents and digit planes); int32 exactness is enforced inside the GEMM (max_kb_acc)
+static inline int64_t tc_max_rows(int digit_bits) { (void)digit_bits; return TC_MAX_ROWS; }
 static inline int64_t tc_rows_per_pass(int64_t n) { return n < TC_MAX_ROWS ? n : TC_MAX_ROWS; }
 static inline int64_t tc_operand_bytes(int64_t n, int64_t m, int num_slices) {
     const int64_t n_pad = round_up(tc_rows_per_pass(n), TC_BK);
@@ -442,14 +460,15 @@ int64_t atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int num_slices) 
 
 template <int S>
 static void launch_slice(const double* z, int64_t n, int64_t m, int64_t n_pad, const double* cs, int8_t* planes,
-                         cudaStream_t st) {
+                         int digit_bits, cudaStream_t st) {
     dim3 grid((unsigned)((m + 31) / 32), (unsigned)(n_pad / 128));
-    tc_slice_kernel<S><<<grid, 256, 0, st>>>(z, n, m, n_pad, cs, planes);
+    if (digit_bits == 8) tc_slice_kernel<S, 8><<<grid, 256, 0, st>>>(z, n, m, n_pad, cs, planes);
+    else                 tc_slice_kernel<S, 7><<<grid, 256, 0, st>>>(z, n, m, n_pad, cs, planes);
 }
 
 // column exponents + digit planes + tensor map of one fp64 operand chunk z (rows, m); 3 launches
 static int tc_prepare_operand(TcOperand& op, uint8_t* ws, const double* z, int64_t rows, int64_t m, int num_slices,
-                              int sms, cudaStream_t st) {
+                              int digit_bits, int sms, cudaStream_t st) {
     const int64_t n_pad = round_up(rows, TC_BK);
     op.cmax = (unsigned long long*)ws;
     op.colscale = (double*)(ws + round_up(m * 8, 1024));
@@ -461,14 +480,14 @@ static int tc_prepare_operand(TcOperand& op, uint8_t* ws, const double* z, int64
     if (rows_per < 16) rows_per = 16;
     splits = (rows + rows_per - 1) / rows_per;
     tc_colmax_kernel<<<dim3((unsigned)colblocks, (unsigned)splits), 256, 0, st>>>(z, rows, m, op.cmax, rows_per);
-    tc_exponent_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(op.cmax, m, op.colscale);
+    tc_exponent_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(op.cmax, m, op.colscale, digit_bits);
     switch (num_slices) {
-        case 2: launch_slice<2>(z, rows, m, n_pad, op.colscale, op.planes, st); break;
-        case 3: launch_slice<3>(z, rows, m, n_pad, op.colscale, op.planes, st); break;
-        case 4: launch_slice<4>(z, rows, m, n_pad, op.colscale, op.planes, st); break;
-        case 5: launch_slice<5>(z, rows, m, n_pad, op.colscale, op.planes, st); break;
-        case 6: launch_slice<6>(z, rows, m, n_pad, op.colscale, op.planes, st); break;
-        default: launch_slice<7>(z, rows, m, n_pad, op.colscale, op.planes, st); break;
+        case 2: launch_slice<2>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, st); break;
+        case 3: launch_slice<3>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, st); break;
+        case 4: launch_slice<4>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, st); break;
+        case 5: launch_slice<5>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, st); break;
+        case 6: launch_slice<6>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, st); break;
+        default: launch_slice<7>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, st); break;
     }
     count_launch(3);
     EncodeTiledFn encode = encode_tiled_fn();
@@ -517,9 +536,14 @@ double tc_last_gemm_ms() {
 
 // c (ma, mb) += A^T B for one pass of rows (both operands already sliced)
 static int tc_launch_gemm(const TcOperand& a, const TcOperand& b, int64_t rows, int64_t ma, int64_t mb, int symmetric,
-                          int num_slices, double* c, int sms, cudaStream_t st) {
+                          int num_slices, int digit_bits, double* c, int sms, cudaStream_t st) {
     TcSched sc;
     sc.num_slices = num_slices;
+    sc.digit_bits = digit_bits;
+    // an int32 accumulator stays exact for (2^31 - 1) / max|d d'| products: 524,287 rows of 7-bit digit pairs
+    // (|d d'| <= 4096), 131,071 rows of 8-bit ones (<= 16384); in 128-row K blocks, shared by the g + 1 pairs of a group.
+    // The kernel drains the accumulators (one more epilogue) whenever a group would exceed it.
+    sc.max_kb_acc = digit_bits == 8 ? 1023 : 4095;
     sc.n_kblocks = (int)(round_up(rows, TC_BK) / TC_BK);
     sc.symmetric = symmetric;
     sc.tiles = (int)((mb + TC_TILE - 1) / TC_TILE);
@@ -540,8 +564,9 @@ static int tc_launch_gemm(const TcOperand& a, const TcOperand& b, int64_t rows, 
     return check_launch("tc_gram_kernel");
 }
 
-int ztz_accum_tc(const double* z, int64_t n, int64_t m, double* ztz, int num_slices, int mirror, void* workspace,
-                 int64_t workspace_bytes, cudaStream_t st) {
+int ztz_accum_tc(const double* z, int64_t n, int64_t m, double* ztz, int num_slices, int digit_bits, int mirror,
+                 void* workspace, int64_t workspace_bytes, cudaStream_t st) {
+    XB_REQUIRE(digit_bits == 7 || digit_bits == 8, "digit_bits must be 7 or 8");
     XB_REQUIRE(n > 0 && m > 0, "no datapoints");
     XB_REQUIRE(z && ztz && workspace, "null pointer");
     XB_REQUIRE(num_slices >= 2 && num_slices <= 7, "num_slices must be in [2, 7]");
@@ -549,12 +574,13 @@ int ztz_accum_tc(const double* z, int64_t n, int64_t m, double* ztz, int num_sli
     XB_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
     int sms, rc = tc_setup(sms);
     if (rc != XGPR_B200_OK) return rc;
-    for (int64_t r0 = 0; r0 < n; r0 += TC_MAX_ROWS) {
-        const int64_t rows = (n - r0 < TC_MAX_ROWS) ? (n - r0) : TC_MAX_ROWS;
+    const int64_t max_rows = tc_max_rows(digit_bits);
+    for (int64_t r0 = 0; r0 < n; r0 += max_rows) {
+        const int64_t rows = (n - r0 < max_rows) ? (n - r0) : max_rows;
         TcOperand op;
-        rc = tc_prepare_operand(op, (uint8_t*)workspace, z + r0 * m, rows, m, num_slices, sms, st);
+        rc = tc_prepare_operand(op, (uint8_t*)workspace, z + r0 * m, rows, m, num_slices, digit_bits, sms, st);
         if (rc != XGPR_B200_OK) return rc;
-        rc = tc_launch_gemm(op, op, rows, m, m, 1, num_slices, ztz, sms, st);
+        rc = tc_launch_gemm(op, op, rows, m, m, 1, num_slices, digit_bits, ztz, sms, st);
         if (rc != XGPR_B200_OK) return rc;
     }
     if (mirror) {
@@ -567,7 +593,8 @@ int ztz_accum_tc(const double* z, int64_t n, int64_t m, double* ztz, int num_sli
 
 // acc (r, m) += A^T Z ;  A (n, r), Z (n, m) fp64 row-major
 int atb_accum_tc(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc, int num_slices,
-                 void* workspace, int64_t workspace_bytes, cudaStream_t st) {
+                 int digit_bits, void* workspace, int64_t workspace_bytes, cudaStream_t st) {
+    XB_REQUIRE(digit_bits == 7 || digit_bits == 8, "digit_bits must be 7 or 8");
     XB_REQUIRE(n > 0 && m > 0 && r > 0, "no datapoints");
     XB_REQUIRE(a && z && acc && workspace, "null pointer");
     XB_REQUIRE(num_slices >= 2 && num_slices <= 7, "num_slices must be in [2, 7]");
@@ -577,14 +604,15 @@ int atb_accum_tc(const double* a, const double* z, int64_t n, int64_t r, int64_t
     if (rc != XGPR_B200_OK) return rc;
     uint8_t* ws_a = (uint8_t*)workspace;
     uint8_t* ws_b = ws_a + tc_operand_bytes(n, r, num_slices);
-    for (int64_t r0 = 0; r0 < n; r0 += TC_MAX_ROWS) {
-        const int64_t rows = (n - r0 < TC_MAX_ROWS) ? (n - r0) : TC_MAX_ROWS;
+    const int64_t max_rows = tc_max_rows(digit_bits);
+    for (int64_t r0 = 0; r0 < n; r0 += max_rows) {
+        const int64_t rows = (n - r0 < max_rows) ? (n - r0) : max_rows;
         TcOperand oa, ob;
-        rc = tc_prepare_operand(oa, ws_a, a + r0 * r, rows, r, num_slices, sms, st);
+        rc = tc_prepare_operand(oa, ws_a, a + r0 * r, rows, r, num_slices, digit_bits, sms, st);
         if (rc != XGPR_B200_OK) return rc;
-        rc = tc_prepare_operand(ob, ws_b, z + r0 * m, rows, m, num_slices, sms, st);
+        rc = tc_prepare_operand(ob, ws_b, z + r0 * m, rows, m, num_slices, digit_bits, sms, st);
         if (rc != XGPR_B200_OK) return rc;
-        rc = tc_launch_gemm(oa, ob, rows, r, m, 0, num_slices, acc, sms, st);
+        rc = tc_launch_gemm(oa, ob, rows, r, m, 0, num_slices, digit_bits, acc, sms, st);
         if (rc != XGPR_B200_OK) return rc;
     }
     return XGPR_B200_OK;

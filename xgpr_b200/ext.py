@@ -262,7 +262,7 @@ def _tc_workspace(device, need):
     return ws
 
 
-def atb_accum_tc(a, z, acc, num_slices=6):
+def atb_accum_tc(a, z, acc, num_slices=5, digit_bits=8):
     """acc (r, m) += a^T z on the tensor cores (same split-int8 scheme as ztz_accum_tc)."""
     a = _dev(a.contiguous(), "a", (torch.float64,), 2)
     z = _dev(z, "z", (torch.float64,), 2)
@@ -274,12 +274,14 @@ def atb_accum_tc(a, z, acc, num_slices=6):
         raise RuntimeError("num_slices must be in [2, 7]")
     ws = _tc_workspace(z.device, need)
     check(lib.xgpr_b200_atb_accum_tc_f64(a.data_ptr(), z.data_ptr(), z.shape[0], a.shape[1], z.shape[1],
-                                         acc.data_ptr(), int(num_slices), ws.data_ptr(), ws.numel(), _stream()))
+                                         acc.data_ptr(), int(num_slices), int(digit_bits), ws.data_ptr(), ws.numel(),
+                                         _stream()))
 
 
-def ztz_accum_tc(z, ztz, num_slices=6, mirror=True):
-    """Upper triangle of ztz += z^T z on the tensor cores (tcgen05 kind::i8 over `num_slices` exact int8 digit planes,
-    int32 accumulation in TMEM; csrc/gram_tc_kernels.cu).  mirror=True also refreshes the lower triangle."""
+def ztz_accum_tc(z, ztz, num_slices=5, mirror=True, digit_bits=8):
+    """Upper triangle of ztz += z^T z on the tensor cores (tcgen05 kind::i8 over `num_slices` exact int8 digit planes of
+    `digit_bits` bits, int32 accumulation in TMEM; csrc/gram_tc_kernels.cu).  Default 5 x 8 bits: element error
+    <= n * 2^-37 colmax_i colmax_j (typically 4e-13 per unit column scale).  mirror=True also refreshes the lower triangle."""
     z = _dev(z, "z", (torch.float64,), 2)
     ztz = _dev(ztz, "ztz", (torch.float64,), 2)
     if ztz.shape[0] != z.shape[1] or ztz.shape[1] != z.shape[1]:
@@ -289,7 +291,7 @@ def ztz_accum_tc(z, ztz, num_slices=6, mirror=True):
         raise RuntimeError("num_slices must be in [2, 7]")
     ws = _tc_workspace(z.device, need)
     check(lib.xgpr_b200_ztz_accum_tc_f64(z.data_ptr(), z.shape[0], z.shape[1], ztz.data_ptr(), int(num_slices),
-                                         1 if mirror else 0, ws.data_ptr(), ws.numel(), _stream()))
+                                         int(digit_bits), 1 if mirror else 0, ws.data_ptr(), ws.numel(), _stream()))
 
 
 def tc_profile(enable):

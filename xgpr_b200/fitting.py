@@ -169,16 +169,19 @@ def calc_zty(dataset, kernel, comm=None, ops=_cuda_ops):
 
 def _gram_accumulator(ops, gram, gram_slices):
     """Returns (accumulate(z, ztz), finish(ztz)).  gram="tc": tensor-core split-int8 Gram (tcgen05, exact int32
-    accumulation of `gram_slices` digit planes, csrc/gram_tc_kernels.cu), upper triangle per chunk and one mirror at the
+    accumulation of `gram_slices` = (planes, bits per digit) int8 digit planes -- default 5 x 8 bits, error ~4e-13 of the
+    column scale per row; an int means that many 7-bit planes -- csrc/gram_tc_kernels.cu), upper triangle per chunk and one mirror at the
     end; gram="f64": the DFMA kernel.  Providers without the tensor-core entry point (the CPU test provider) use f64."""
     if gram == "tc" and hasattr(ops, "ztz_accum_tc"):
-        return (lambda z, ztz: ops.ztz_accum_tc(z, ztz, num_slices=gram_slices, mirror=False)), ops.symmetrize_upper
+        ns, bits = gram_slices if isinstance(gram_slices, tuple) else (gram_slices, 7)
+        return (lambda z, ztz: ops.ztz_accum_tc(z, ztz, num_slices=ns, mirror=False, digit_bits=bits)), \
+            ops.symmetrize_upper
     if gram not in ("tc", "f64"):
         raise ValueError("gram must be 'tc' or 'f64'")
     return ops.ztz_accum, (lambda ztz: None)
 
 
-def calc_design_mat(dataset, kernel, comm=None, ops=_cuda_ops, gram="tc", gram_slices=6):
+def calc_design_mat(dataset, kernel, comm=None, ops=_cuda_ops, gram="tc", gram_slices=(5, 8)):
     """z^T z, z^T y, y^T y.  exact_nmll_calcs.py:42-78; one all-reduce of the M x M Gram per pass."""
     comm = comm or RowShardComm()
     dev = _device_of(kernel)
@@ -206,7 +209,7 @@ def direct_weight_calc(chol_z_trans_z, z_trans_y, kernel):
     return chol, w[:, 0]
 
 
-def calc_weights_exact(dataset, kernel, comm=None, ops=_cuda_ops, gram="tc", gram_slices=6):
+def calc_weights_exact(dataset, kernel, comm=None, ops=_cuda_ops, gram="tc", gram_slices=(5, 8)):
     """exact_fitting_toolkit.py:16-36.  lambda^2 is added here AND inside direct_weight_calc, exactly as
     the reference does: the exact fit solves (Z^T Z + 2 lambda^2 I) w = Z^T y."""
     z_trans_z, z_trans_y, _ = calc_design_mat(dataset, kernel, comm, ops, gram, gram_slices)
@@ -216,7 +219,7 @@ def calc_weights_exact(dataset, kernel, comm=None, ops=_cuda_ops, gram="tc", gra
     return weights, 1, []
 
 
-def calc_var_design_mat(dataset, kernel, variance_rffs, comm=None, ops=_cuda_ops, gram="tc", gram_slices=6):
+def calc_var_design_mat(dataset, kernel, variance_rffs, comm=None, ops=_cuda_ops, gram="tc", gram_slices=(5, 8)):
     """exact_nmll_calcs.py:116-139: Gram of the first variance_rffs columns."""
     comm = comm or RowShardComm()
     z_trans_z = _new((variance_rffs, variance_rffs), _device_of(kernel))

@@ -40,7 +40,7 @@ def optimize_alpha_beta(lambda_, nll_terms, ndatapoints, nrffs, beta_max=10., be
 
 
 # ----------------------------------------------------------------------------------------- exact NMLL
-def exact_nmll(hyperparams, dataset, kernel, comm=None, ops=_cuda_ops, gram="tc", gram_slices=6):
+def exact_nmll(hyperparams, dataset, kernel, comm=None, ops=_cuda_ops, gram="tc", gram_slices=(5, 8)):
     """xgp_regression.py:150-205: NMLL from the Cholesky factor of Z^T Z + lambda^2 I."""
     kernel.set_hyperparams(hyperparams, logspace=True)
     ndatapoints = dataset.get_ndatapoints()
@@ -59,7 +59,7 @@ def exact_nmll(hyperparams, dataset, kernel, comm=None, ops=_cuda_ops, gram="tc"
     return float(negloglik)
 
 
-def calc_gradient_terms(dataset, kernel, subsample=1, comm=None, ops=_cuda_ops, gram="tc", gram_slices=6):
+def calc_gradient_terms(dataset, kernel, subsample=1, comm=None, ops=_cuda_ops, gram="tc", gram_slices=(5, 8)):
     """nmll_gradient_tools.py:12-90.  Per chunk: Z, dZ/dsigma_i, then Z^T Z, Z^T y, y^T y, dZ_i^T y and dZ_i^T Z
     (one more M x M contraction per kernel-specific hyperparameter); inner_deriv is symmetrised at the end."""
     if subsample > 1 or subsample < 0.01:
@@ -147,7 +147,7 @@ def exact_nmll_reg_grad(z_trans_z, z_trans_y, y_trans_y, hparams, ndatapoints, d
     return negloglik, grad, beta
 
 
-def exact_nmll_gradient(hyperparams, dataset, kernel, subsample=1, comm=None, ops=_cuda_ops, gram="tc", gram_slices=6):
+def exact_nmll_gradient(hyperparams, dataset, kernel, subsample=1, comm=None, ops=_cuda_ops, gram="tc", gram_slices=(5, 8)):
     """xgp_regression.py:209-260."""
     init_hparams = kernel.get_hyperparams()
     kernel.set_hyperparams(hyperparams, logspace=True)
