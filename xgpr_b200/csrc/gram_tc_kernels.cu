@@ -24,6 +24,7 @@
 // (DFMA kernel / cuBLAS DGEMM: 118-120 ms), tensor pipe active 79 % (profiles/r01c_tc_gram_kernel_full.md).
 #include "common.cuh"
 #include <cuda.h>
+#include <stdlib.h>
 
 namespace xb {
 
@@ -195,20 +196,41 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 // Per 128-byte K block: 64 KB of operands for 2 x 4 MMAs (1024 tensor-pipe cycles) = 64 B/clk/SM of smem fill, which
 // is what bounds this kernel (the int8 pipe outruns L2), hence the large tile.
 struct TcSched {
-    int num_slices, n_kblocks, tiles, num_tiles, full_waves, split_remainder, symmetric, digit_bits, max_kb_acc;
+    int num_slices, n_kblocks, tiles, num_tiles, full_waves, split_remainder, symmetric, digit_bits, max_kb_acc, supertile;
 };
 struct TcSeg { int tile, kb0, kb1; };
 
-// linear tile index -> (ti, tj): symmetric = upper triangle (ti <= tj < tiles), else row-major over tiles_i x tiles
+// linear tile index -> (ti, tj).  symmetric: the upper triangle (ti <= tj < tiles) walked supertile by supertile
+// (sc.supertile x sc.supertile tiles, about one wave of CTAs each), so the tiles in flight together share few 256-row
+// plane blocks and those stay L2-resident; else row-major over tiles_i x tiles.
 __device__ __forceinline__ void tc_tile_coords(const TcSched& sc, int lin, int& ti, int& tj) {
-    if (sc.symmetric) {
-        ti = 0;
-        while (lin >= sc.tiles - ti) { lin -= sc.tiles - ti; ++ti; }
-        tj = ti + lin;
-    } else {
+    if (!sc.symmetric) {
         ti = lin / sc.tiles;
         tj = lin - ti * sc.tiles;
+        return;
     }
+    const int T = sc.tiles, SB = sc.supertile;
+    for (int r0 = 0; r0 < T; r0 += SB) {
+        const int h = (r0 + SB < T) ? SB : T - r0;
+        for (int c0 = r0; c0 < T; c0 += SB) {
+            const int w = (c0 + SB < T) ? SB : T - c0;
+            const int cnt = (c0 == r0) ? h * (h + 1) / 2 : h * w;
+            if (lin < cnt) {
+                if (c0 == r0) {
+                    int i = 0;
+                    while (lin >= h - i) { lin -= h - i; ++i; }
+                    ti = r0 + i;
+                    tj = r0 + i + lin;
+                } else {
+                    ti = r0 + lin / w;
+                    tj = c0 + lin % w;
+                }
+                return;
+            }
+            lin -= cnt;
+        }
+    }
+    ti = tj = 0;    // not reached
 }
 
 // segment i (0 <= i < full_waves + 2) of CTA b; kb1 <= kb0 means empty
@@ -544,6 +566,8 @@ static int tc_launch_gemm(const TcOperand& a, const TcOperand& b, int64_t rows, 
     // (|d d'| <= 4096), 131,071 rows of 8-bit ones (<= 16384); in 128-row K blocks, shared by the g + 1 pairs of a group.
     // The kernel drains the accumulators (one more epilogue) whenever a group would exceed it.
     sc.max_kb_acc = digit_bits == 8 ? 1023 : 4095;
+    sc.supertile = 12;                                   // 12 x 12 tiles ~ one wave of 148 CTAs
+    if (const char* e = getenv("XGPR_B200_TC_SUPERTILE")) { const int v = atoi(e); if (v > 0) sc.supertile = v; }
     sc.n_kblocks = (int)(round_up(rows, TC_BK) / TC_BK);
     sc.symmetric = symmetric;
     sc.tiles = (int)((mb + TC_TILE - 1) / TC_TILE);
