@@ -34,8 +34,10 @@ constexpr int TC_TILE = 256;        // CTA output tile (rows and cols): two UMMA
 constexpr int TC_BK = 128;          // K bytes per stage = one 128B swizzle atom row
 constexpr int TC_STAGES = 3;
 constexpr int TC_STAGE_BYTES = 2 * TC_TILE * TC_BK;  // A (256 x 128 B) + B (256 x 128 B) = 64 KB
-constexpr int TC_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 constexpr int TC_EPI_WARPS = 8;
+constexpr int TC_EPI_STAGE_WORDS = 32 * 33;         // per epilogue warp: 32 x 32 int32 transpose buffer, padded
+constexpr int TC_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ +
+                              TC_EPI_WARPS * TC_EPI_STAGE_WORDS * 4;
 constexpr int TC_THREADS = 64 + 32 * TC_EPI_WARPS;   // warp 0: TMA, warp 1: MMA, warps 2-9: epilogue
 constexpr int64_t TC_MAX_ROWS = 65536;   // int32 exactness bound for s <= 7
 
@@ -363,27 +365,31 @@ tc_gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         }
     } else {
         // ---------------------------------------------------------------- epilogue: TMEM -> fp64 -> G (upper triangle) +=
+        // A TMEM lane is a tile row, so after tcgen05.ld each thread holds 32 columns of ONE row; written straight out that
+        // is 32 different cache lines per warp instruction (measured: 120 us per tile drain, 14 % of the kernel).  Each warp
+        // therefore transposes its 32 x 32 block through a padded shared-memory buffer and updates G with one 256-byte row
+        // segment per instruction.
         const int quad = warp & 3;                      // TMEM lane quadrant this warp may read
         const int half = (warp - 2) >> 2;               // which accumulator (tile rows 0-127 / 128-255)
+        int* stage = reinterpret_cast<int*>(smem_raw + (bar_base + 256u - smem_u32(smem_raw))) +
+                     (warp - 2) * TC_EPI_STAGE_WORDS;
         uint32_t it = 0;
         for (int si = 0; si < sc.full_waves + 2; ++si) {
             const TcSeg sg = tc_segment(sc, si, blockIdx.x, gridDim.x);
             if (sg.kb1 <= sg.kb0) continue;
             int ti, tj;
             tc_tile_coords(sc, sg.tile, ti, tj);
-            const bool owned = (sg.kb0 == 0 && sg.kb1 == sc.n_kblocks);
             const int64_t wrow0 = (int64_t)ti * TC_TILE + half * 128 + quad * 32;
-            const int64_t row = wrow0 + lane;
             const int64_t col0 = (int64_t)tj * TC_TILE;
-            const double rs = (row < ma) ? scale_a[row] : 0.0;
+            const double rs = (wrow0 + lane < ma) ? scale_a[wrow0 + lane] : 0.0;     // lane r holds row (wrow0 + r)'s scale
             const int64_t diag = sc.symmetric ? wrow0 : 0;          // first column this warp may write
             const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 256);
             for (int g = sc.num_slices - 1; g >= 0; --g) {
               const int step = sc.max_kb_acc / (g + 1);
+              const double wg = exp2(-(double)(sc.digit_bits * (g + 2)));     // exact power of two
               for (int sb = sg.kb0; sb < sg.kb1; sb += step, ++it) {
                 mbar_wait(tfull_bar, it & 1);
                 tc_fence_after();
-                const double rsg = rs * exp2(-(double)(sc.digit_bits * (g + 2)));     // exact power of two
 #pragma unroll 1
                 for (int c = 0; c < TC_TILE / 32; ++c) {
                     const int64_t cb = col0 + c * 32;
@@ -391,19 +397,25 @@ tc_gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     uint32_t acc[32];
                     tmem_ld32(taddr + c * 32, acc);
                     tmem_ld_wait();
-                    if (row < ma) {
-                        double* gp = g_out + row * mb + cb;
-                        const int64_t cmin = sc.symmetric ? row : 0;
 #pragma unroll
-                        for (int uu = 0; uu < 32; ++uu) {
-                            const int64_t col = cb + uu;
-                            if (col < mb && col >= cmin) {
-                                const double v = (double)(int)acc[uu] * (rsg * __ldg(scale_b + col));
-                                if (owned) gp[uu] += v;
-                                else atomicAdd(gp + uu, v);
-                            }
+                    for (int uu = 0; uu < 32; ++uu) stage[lane * 33 + uu] = (int)acc[uu];
+                    __syncwarp();
+                    const int64_t col = cb + lane;
+                    const double cs = (col < mb) ? __ldg(scale_b + col) * wg : 0.0;
+#pragma unroll 4
+                    for (int r = 0; r < 32; ++r) {
+                        const int64_t row = wrow0 + r;
+                        const double rsr = __shfl_sync(0xffffffffu, rs, r);
+                        const int val = stage[r * 33 + lane];
+                        if (row < ma && col < mb && (!sc.symmetric || col >= row)) {
+                            const double v = (double)val * (rsr * cs);
+                            // red.add.f64 for every tile: fire-and-forget, so the drain is not a chain of L2 round trips
+                            // (a plain load-add-store measured 100 us per drain).  Adds to one address from one thread
+                            // stay in program order, so tiles owned by one CTA remain deterministic.
+                            atomicAdd(g_out + row * mb + col, v);
                         }
                     }
+                    __syncwarp();
                 }
                 tc_fence_before();
                 __syncwarp();
