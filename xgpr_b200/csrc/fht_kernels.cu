@@ -87,6 +87,88 @@ fht_cta_kernel(T* __restrict__ x, const int8_t* __restrict__ radem, int64_t N, i
     }
 }
 
+// ------------------------------------------------------------------ 2048 <= P <= 16384, row fits shared memory: v2
+// One warp per 1024-element segment (strides 1..512 in registers + shuffles), ONE transposition through shared memory,
+// then each thread finishes the NS = P / 1024 cross-segment strides in registers on {off + s * 1024} and writes straight to
+// global memory.  The next row is prefetched into registers while the current one is in its shared-memory phase, so HBM is
+// never idle behind a __syncthreads chain (the v1 kernel above ran 4 smem passes per row and 1.7 TB/s at P = 16384 fp64).
+// Same butterflies in the same (ascending-stride) order as the oracle: bit-identical.
+template <typename T, int NS, bool SRHT>
+__global__ void __launch_bounds__(32 * NS)
+fht_cta2_kernel(T* __restrict__ x, const int8_t* __restrict__ radem, int64_t N, T cnorm, int nseg) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T* buf = reinterpret_cast<T*>(smem_raw);
+    constexpr int E = 32, K = 32, SEG = 1024, P = NS * SEG, THREADS = 32 * NS, GROUPS = SEG / THREADS;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int off = warp * SEG;
+    T sc[E];
+    if (SRHT) {
+        // nseg > 1: the "rows" are consecutive P-element segments of longer rows (two-pass path); gridDim.x is a multiple
+        // of nseg there, so this CTA always sees segment (blockIdx.x % nseg) and its slice of the sign vector
+        const int8_t* rd = radem + (int64_t)(blockIdx.x % nseg) * P;
+#pragma unroll
+        for (int r = 0; r < E; ++r) sc[r] = (T)rd[off + lane + K * r] * cnorm;
+    }
+    T v[E];
+    int64_t row = blockIdx.x;
+    if (row < N) {
+#pragma unroll
+        for (int r = 0; r < E; ++r) v[r] = x[row * P + off + lane + K * r];
+    }
+    for (; row < N; row += gridDim.x) {
+        if (SRHT) {
+#pragma unroll
+            for (int r = 0; r < E; ++r) v[r] = mul_rn(v[r], sc[r]);
+        }
+        warp_fwht<T, E, K>(v, lane);
+#pragma unroll
+        for (int r = 0; r < E; ++r) buf[off + lane + K * r] = v[r];
+        __syncthreads();
+        const int64_t nxt = row + gridDim.x;
+        if (nxt < N) {                                   // loads in flight during the cross-segment phase
+#pragma unroll
+            for (int r = 0; r < E; ++r) v[r] = x[nxt * P + off + lane + K * r];
+        }
+        T* xr = x + row * P;
+#pragma unroll
+        for (int q = 0; q < GROUPS; ++q) {
+            const int o = threadIdx.x + q * THREADS;
+            T w[NS];
+#pragma unroll
+            for (int sidx = 0; sidx < NS; ++sidx) w[sidx] = buf[o + sidx * SEG];
+#pragma unroll
+            for (int h = 1; h < NS; h <<= 1)
+#pragma unroll
+                for (int i = 0; i < NS; ++i)
+                    if ((i & h) == 0) {
+                        const T a = w[i], b = w[i + h];
+                        w[i]     = add_rn(a, b);
+                        w[i + h] = sub_rn(a, b);
+                    }
+#pragma unroll
+            for (int sidx = 0; sidx < NS; ++sidx) xr[o + sidx * SEG] = w[sidx];
+        }
+        __syncthreads();                                 // buf is rewritten by the next row
+    }
+}
+
+template <typename T, int NS, bool SRHT>
+static int launch_fht_cta2(T* x, int64_t n, const int8_t* radem, cudaStream_t st, int nseg = 1, int64_t p_full = 0) {
+    constexpr int64_t P = (int64_t)NS * 1024;
+    const size_t smem = (size_t)P * sizeof(T);
+    auto kern = fht_cta2_kernel<T, NS, SRHT>;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int per_sm = (int)((220 * 1024) / smem);
+    if (per_sm < 1) per_sm = 1;
+    if (per_sm * 32 * NS > 2048) per_sm = 2048 / (32 * NS);
+    int64_t blocks = (int64_t)148 * per_sm;
+    if (blocks > n) blocks = n;
+    blocks -= blocks % nseg;                             // n is a multiple of nseg on the two-pass path
+    kern<<<(unsigned)blocks, 32 * NS, smem, st>>>(x, radem, n, norm_constant<T>(p_full ? p_full : P), nseg);
+    count_launch();
+    return check_launch("fht_cta2_kernel");
+}
+
 // ------------------------------------------------------------------ row larger than shared memory
 // Pass A: the CTA kernel above on SEGP-element segments (treated as rows).  Pass B: the remaining
 // strides SEGP..P/2 across segments, element-wise (each thread owns one offset within a segment and
@@ -171,6 +253,13 @@ int fht_dispatch(T* x, int64_t n, int64_t P, const int8_t* radem, int64_t radem_
         default: break;
     }
 #undef XB_CASE
+    switch (P) {
+        case 2048:  return launch_fht_cta2<T, 2, SRHT>(x, n, radem, st);
+        case 4096:  return launch_fht_cta2<T, 4, SRHT>(x, n, radem, st);
+        case 8192:  return launch_fht_cta2<T, 8, SRHT>(x, n, radem, st);
+        case 16384: return launch_fht_cta2<T, 16, SRHT>(x, n, radem, st);
+        default: break;
+    }
     constexpr int64_t SMEM_MAX = 128 * 1024;
     if (P * (int64_t)sizeof(T) <= SMEM_MAX) return launch_fht_cta<T, SRHT>(x, n, P, radem, st);
 
@@ -178,11 +267,17 @@ int fht_dispatch(T* x, int64_t n, int64_t P, const int8_t* radem, int64_t radem_
     const int64_t SEGP = SMEM_MAX / (int64_t)sizeof(T);
     const int64_t nseg = P / SEGP;
     XB_REQUIRE(nseg <= 64, "row too long for the FWHT");
-    if (SRHT) {
-        radem_scale_kernel<T><<<148 * 8, 256, 0, st>>>(x, radem, n, P, norm_constant<T>(P));
-        count_launch();
+    int rc;
+    if (SEGP == 16384) {
+        // segments through the v2 kernel, the sign diagonal folded into its load (no separate scaling pass)
+        rc = launch_fht_cta2<T, 16, SRHT>(x, n * nseg, radem, st, (int)nseg, P);
+    } else {
+        if (SRHT) {
+            radem_scale_kernel<T><<<148 * 8, 256, 0, st>>>(x, radem, n, P, norm_constant<T>(P));
+            count_launch();
+        }
+        rc = launch_fht_cta<T, false>(x, n * nseg, SEGP, nullptr, st);
     }
-    int rc = launch_fht_cta<T, false>(x, n * nseg, SEGP, nullptr, st);
     if (rc != XGPR_B200_OK) return rc;
     switch (nseg) {
         case 2:  fht_cross_kernel<T, 2><<<148 * 8, 256, 0, st>>>(x, n, P, SEGP); break;
