@@ -347,6 +347,208 @@ ztt_tile_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double
     }
 }
 
+// ------------------------------------------------------------------ multi-RHS matvec, v2 (cp.async pipeline)
+// The v1 kernels above issue one shared-memory wavefront per DFMA pair (4 x 4 micro-tile, 2-way conflicts on the V
+// loads) and run <= 2 CTAs of one K loop per SM: ncu r01g showed 31-33 % fp64-pipe activity, short-scoreboard stalls.
+// v2: 128 x 32 CTA tile, 8 x 4 micro-tile read with conflict-free LDS.128 (12 wavefronts per 64 DFMA), the Z and V/T
+// tiles double-buffered in shared memory by cp.async (no staging registers), K split across blockIdx.y so that the
+// grid fills 2 CTAs on each of the 148 SMs; partial sums are combined with red.add.f64.  Needs 16-byte-aligned Z rows
+// (m even, base aligned); the host falls back to v1 otherwise.
+constexpr int M2_ROWS = 128, M2_COLS = 32, M2_K = 32;
+constexpr int M2_ZV_LD = M2_K + 2;                               // padded row of the row-major Z tile (doubles)
+constexpr int M2_ZV_STAGE = M2_ROWS * M2_ZV_LD + M2_K * M2_COLS; // doubles per stage, zv2
+constexpr int M2_ZT_STAGE = M2_K * M2_ROWS + M2_K * M2_COLS;     // doubles per stage, ztt2
+constexpr int M2_ZV_SMEM = 2 * M2_ZV_STAGE * 8, M2_ZT_SMEM = 2 * M2_ZT_STAGE * 8;
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem, bool valid) {
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(smem);
+    const int bytes = valid ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(gmem), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void* smem, const void* gmem, bool valid) {
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(smem);
+    const int bytes = valid ? 8 : 0;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst), "l"(gmem), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// one K step of the 8 x 4 micro-tile: acc[a][0..3] += za[a] * (v0.x, v0.y, v1.x, v1.y)
+#define M2_FMA_STEP(ZEXPR)                                   \
+    _Pragma("unroll") for (int a = 0; a < 8; ++a) {          \
+        const double zq = (ZEXPR);                           \
+        acc[a][0] = fma(zq, v0.x, acc[a][0]);                \
+        acc[a][1] = fma(zq, v0.y, acc[a][1]);                \
+        acc[a][2] = fma(zq, v1.x, acc[a][2]);                \
+        acc[a][3] = fma(zq, v1.y, acc[a][3]);                \
+    }
+
+// T (n, 32) (+)= Z[:, k range] V[k range, r0:r0+32].  Thread (tx, ty): rows ty + 16 a, columns {2tx, 2tx+1, 16+2tx, 17+2tx}.
+__global__ void __launch_bounds__(128, 2)
+zv_tile2_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double* __restrict__ v, int64_t ldv,
+                int r0, int rcount, double* __restrict__ t, int64_t ldt, int64_t k_per, int atomic_out) {
+    extern __shared__ __align__(16) double m2_smem[];
+    const int64_t row0 = (int64_t)blockIdx.x * M2_ROWS;
+    const int64_t kbeg = (int64_t)blockIdx.y * k_per;
+    const int64_t kend = (kbeg + k_per < m) ? kbeg + k_per : m;
+    const int tx = threadIdx.x & 7, ty = threadIdx.x >> 3;
+    double acc[8][4];
+#pragma unroll
+    for (int a = 0; a < 8; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+    auto load = [&](int stage, int64_t k0) {
+        double* zs = m2_smem + stage * M2_ZV_STAGE;
+        double* vs = zs + M2_ROWS * M2_ZV_LD;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {                           // 128 rows x 16 pieces of 16 bytes
+            const int p = i * 128 + threadIdx.x;
+            const int rr = p >> 4, j = p & 15;
+            const int64_t row = row0 + rr, k = k0 + 2 * j;
+            const bool ok = row < n && k < kend;
+            cp_async16(zs + rr * M2_ZV_LD + 2 * j, ok ? z + row * m + k : z, ok);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {                            // 32 k x 32 columns of V, 8 bytes each
+            const int p = i * 128 + threadIdx.x;
+            const int kk = p >> 5, cc = p & 31;
+            const int64_t k = k0 + kk;
+            const bool ok = k < kend && cc < rcount;
+            cp_async8(vs + kk * M2_COLS + cc, ok ? v + k * ldv + r0 + cc : v, ok);
+        }
+    };
+    load(0, kbeg);
+    cp_async_commit();
+    int s = 0;
+    for (int64_t k0 = kbeg; k0 < kend; k0 += M2_K, s ^= 1) {
+        if (k0 + M2_K < kend) load(s ^ 1, k0 + M2_K);
+        cp_async_commit();
+        cp_async_wait<1>();
+        __syncthreads();
+        const double* zs = m2_smem + s * M2_ZV_STAGE + ty * M2_ZV_LD;
+        const double* vs = m2_smem + s * M2_ZV_STAGE + M2_ROWS * M2_ZV_LD + 2 * tx;
+#pragma unroll 4
+        for (int kp = 0; kp < M2_K / 2; ++kp) {
+            double2 zz[8];
+#pragma unroll
+            for (int a = 0; a < 8; ++a) zz[a] = *reinterpret_cast<const double2*>(zs + 16 * a * M2_ZV_LD + 2 * kp);
+            {
+                const double2 v0 = *reinterpret_cast<const double2*>(vs + (2 * kp) * M2_COLS);
+                const double2 v1 = *reinterpret_cast<const double2*>(vs + (2 * kp) * M2_COLS + 16);
+                M2_FMA_STEP(zz[a].x)
+            }
+            {
+                const double2 v0 = *reinterpret_cast<const double2*>(vs + (2 * kp + 1) * M2_COLS);
+                const double2 v1 = *reinterpret_cast<const double2*>(vs + (2 * kp + 1) * M2_COLS + 16);
+                M2_FMA_STEP(zz[a].y)
+            }
+        }
+        __syncthreads();
+    }
+    cp_async_wait<0>();
+#pragma unroll
+    for (int a = 0; a < 8; ++a) {
+        const int64_t row = row0 + ty + 16 * a;
+        if (row >= n) continue;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int cc = 2 * tx + (b & 1) + 16 * (b >> 1);
+            if (cc >= rcount) continue;
+            double* dst = t + row * ldt + r0 + cc;
+            if (atomic_out) atomicAdd(dst, acc[a][b]);
+            else *dst = acc[a][b];
+        }
+    }
+}
+
+// W (m, 32) += Z[row range, :]^T T[row range, r0:r0+32].  Thread (tx, ty): Z columns {2ty, 2ty+1} + 32 a, a < 4.
+__global__ void __launch_bounds__(128, 2)
+ztt_tile2_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double* __restrict__ t, int64_t ldt,
+                 int r0, int rcount, double* __restrict__ w, int64_t ldw, int64_t k_per) {
+    extern __shared__ __align__(16) double m2_smem[];
+    const int64_t c0 = (int64_t)blockIdx.x * M2_ROWS;
+    const int64_t kbeg = (int64_t)blockIdx.y * k_per;
+    const int64_t kend = (kbeg + k_per < n) ? kbeg + k_per : n;
+    const int tx = threadIdx.x & 7, ty = threadIdx.x >> 3;
+    double acc[8][4];
+#pragma unroll
+    for (int a = 0; a < 8; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+    auto load = [&](int stage, int64_t k0) {
+        double* zs = m2_smem + stage * M2_ZT_STAGE;
+        double* ts = zs + M2_K * M2_ROWS;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {                           // 32 rows x 64 pieces of 16 bytes
+            const int p = i * 128 + threadIdx.x;
+            const int kk = p >> 6, j = p & 63;
+            const int64_t row = k0 + kk, col = c0 + 2 * j;
+            const bool ok = row < kend && col < m;
+            cp_async16(zs + kk * M2_ROWS + 2 * j, ok ? z + row * m + col : z, ok);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int p = i * 128 + threadIdx.x;
+            const int kk = p >> 5, cc = p & 31;
+            const int64_t row = k0 + kk;
+            const bool ok = row < kend && cc < rcount;
+            cp_async8(ts + kk * M2_COLS + cc, ok ? t + row * ldt + r0 + cc : t, ok);
+        }
+    };
+    load(0, kbeg);
+    cp_async_commit();
+    int s = 0;
+    for (int64_t k0 = kbeg; k0 < kend; k0 += M2_K, s ^= 1) {
+        if (k0 + M2_K < kend) load(s ^ 1, k0 + M2_K);
+        cp_async_commit();
+        cp_async_wait<1>();
+        __syncthreads();
+        const double* zs = m2_smem + s * M2_ZT_STAGE + 2 * ty;
+        const double* ts = m2_smem + s * M2_ZT_STAGE + M2_K * M2_ROWS + 2 * tx;
+#pragma unroll 4
+        for (int kk = 0; kk < M2_K; ++kk) {
+            double2 zz[4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) zz[a] = *reinterpret_cast<const double2*>(zs + kk * M2_ROWS + 32 * a);
+            const double2 v0 = *reinterpret_cast<const double2*>(ts + kk * M2_COLS);
+            const double2 v1 = *reinterpret_cast<const double2*>(ts + kk * M2_COLS + 16);
+            M2_FMA_STEP((a & 1) ? zz[a >> 1].y : zz[a >> 1].x)
+        }
+        __syncthreads();
+    }
+    cp_async_wait<0>();
+    const bool atomic_out = gridDim.y > 1;
+#pragma unroll
+    for (int a = 0; a < 8; ++a) {
+        const int64_t col = c0 + 2 * ty + 32 * (a >> 1) + (a & 1);
+        if (col >= m) continue;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int cc = 2 * tx + (b & 1) + 16 * (b >> 1);
+            if (cc >= rcount) continue;
+            double* dst = w + col * ldw + r0 + cc;
+            if (atomic_out) atomicAdd(dst, acc[a][b]);
+            else *dst += acc[a][b];
+        }
+    }
+}
+
+// K split that fills 2 CTAs on each SM with the smallest tail (each split at least 8 K chunks long)
+static int64_t m2_k_per(int64_t tiles, int64_t k_total) {
+    const int64_t slots = 148 * 2;
+    int best = 1;
+    double best_eff = 0.0;
+    for (int ks = 1; ks <= 64; ++ks) {
+        if (ks > 1 && k_total / ks < 8 * M2_K) break;
+        const int64_t units = tiles * ks;
+        const double eff = (double)units / (double)(((units + slots - 1) / slots) * slots);
+        if (eff > best_eff + 0.02) { best_eff = eff; best = ks; }
+    }
+    int64_t k_per = (k_total + best - 1) / best;
+    return ((k_per + M2_K - 1) / M2_K) * M2_K;
+}
+
 // ------------------------------------------------------------------ host
 int atb_accum(const double* a, const double* b, int64_t n, int64_t r, int64_t m, double* c, cudaStream_t st) {
     XB_REQUIRE(n > 0 && r > 0 && m > 0, "no datapoints");
@@ -410,6 +612,27 @@ int cg_matvec_accum(const double* z, int64_t n, int64_t m, const double* v, int6
         z_times_kernel<1><<<(unsigned)wblocks, 256, 0, st>>>(z, n, m, v, r, 0, 1, scratch, r);
         zt_times_kernel<1><<<grid2, 256, 0, st>>>(z, n, m, scratch, r, 0, 1, w, r, rows_per);
         count_launch(2);
+        return check_launch("cg_matvec");
+    }
+    const bool v2 = (m % 2 == 0) && (reinterpret_cast<uintptr_t>(z) % 16 == 0) && !getenv("XGPR_B200_MATVEC_V1");
+    if (v2) {
+        static bool attr_done = false;
+        if (!attr_done) {
+            cudaFuncSetAttribute(zv_tile2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, M2_ZV_SMEM);
+            cudaFuncSetAttribute(ztt_tile2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, M2_ZT_SMEM);
+            attr_done = true;
+        }
+        const int64_t rt = (n + M2_ROWS - 1) / M2_ROWS, ct = (m + M2_ROWS - 1) / M2_ROWS;
+        const int64_t kz = m2_k_per(rt, m), kt = m2_k_per(ct, n);
+        const unsigned sz = (unsigned)((m + kz - 1) / kz), stt = (unsigned)((n + kt - 1) / kt);
+        if (sz > 1) cudaMemsetAsync(scratch, 0, sizeof(double) * (size_t)n * (size_t)r, st);
+        for (int r0 = 0; r0 < r; r0 += M2_COLS) {
+            const int rc = (int)((r - r0 < M2_COLS) ? (r - r0) : M2_COLS);
+            zv_tile2_kernel<<<dim3((unsigned)rt, sz), 128, M2_ZV_SMEM, st>>>(z, n, m, v, r, r0, rc, scratch, r, kz,
+                                                                              sz > 1 ? 1 : 0);
+            ztt_tile2_kernel<<<dim3((unsigned)ct, stt), 128, M2_ZT_SMEM, st>>>(z, n, m, scratch, r, r0, rc, w, r, kt);
+            count_launch(2);
+        }
         return check_launch("cg_matvec");
     }
     for (int r0 = 0; r0 < r; r0 += MR_COLS) {
