@@ -170,6 +170,12 @@ double xgpr_b200_tc_last_gemm_ms(void);
 int64_t xgpr_b200_atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int num_slices);
 int xgpr_b200_atb_accum_tc_f64(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc,
                                int num_slices, int digit_bits, void* workspace, int64_t workspace_bytes, void* stream);
+/* Tensor-core second Nystrom pass: acc (m, r) += Z^T (Z Q), Q (m, r) fp64 row-major, m <= 65,536
+ * (`acc_results += xdata.T @ (xdata @ q_mat)`, src/xGPR/preconditioners/rand_nys_constructors.py:18-36).  Z Q contracts
+ * over the features (row-wise exponents, Z's own layout is K-major); Z^T T over the rows (column-wise exponents). */
+int64_t xgpr_b200_ztzq_tc_workspace_bytes(int64_t n, int64_t m, int64_t r, int num_slices);
+int xgpr_b200_ztzq_accum_tc_f64(const double* z, int64_t n, int64_t m, const double* q, int64_t r, double* acc,
+                                int num_slices, int digit_bits, void* workspace, int64_t workspace_bytes, void* stream);
 /* acc (r, m) += A^T Z ;  A (n, r) row-major: the Nystrom sketch accumulation
  * `acc_results += compressor.transform_x(xdata).T @ xdata` (src/xGPR/preconditioners/rand_nys_constructors.py:119) */
 int xgpr_b200_atb_accum_f64(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc, void* stream);

@@ -168,3 +168,53 @@ def test_base256_digits_bit_exact_and_bounded(shape):
     keep = np.ones(m, bool)
     keep[1] = False
     assert np.array_equal(got[:, keep], (a.T @ z)[:, keep])
+
+
+@pytest.mark.parametrize("shape", [(300, 200, 64), (1000, 384, 70), (2049, 1000, 130)])
+def test_ztzq_dyadic_exact_products(shape):
+    """Second Nystrom pass acc += Z^T (Z Q) (rand_nys_constructors.py:18-36) on the tensor cores.  One-digit dyadic Z and Q:
+    T = Z Q is exact, and its entries (|T| < 2^13, multiples of 2^-8) fit the digit planes, so the whole product equals
+    float64 NumPy bit for bit; accumulation over two calls included."""
+    n, m, r = shape
+    rng = np.random.default_rng(n + m + r)
+    z = rng.integers(-16, 17, size=(n, m)).astype(np.float64) / 16.0
+    q = rng.integers(-16, 17, size=(m, r)).astype(np.float64) / 16.0
+    ref = z.T @ (z @ q)
+    ext = _ext()
+    acc = torch.zeros((m, r), dtype=torch.float64, device=DEV)
+    ext.ztzq_accum_tc(torch.from_numpy(z).to(DEV), torch.from_numpy(q).to(DEV), acc)
+    assert np.array_equal(acc.cpu().numpy(), ref)
+    ext.ztzq_accum_tc(torch.from_numpy(z).to(DEV), torch.from_numpy(q).to(DEV), acc)
+    assert np.array_equal(acc.cpu().numpy(), 2 * ref)
+
+
+def test_ztzq_general_error_and_matches_matvec():
+    """Feature-shaped Z (|z| <= scale, rows of very different magnitude) and an orthonormal Q: error against float64 NumPy
+    below 1e-10 of the result's scale (5 x 8-bit planes: ~4e-13 per product term), and agreement with cg_matvec_accum."""
+    n, m, r = 5000, 2048, 96
+    rng = np.random.default_rng(8)
+    z = rng.uniform(-1, 1, size=(n, m)) * (2.0 / m) ** 0.5
+    z[::7] *= 1e-3                                            # row exponents differ
+    z[:, ::5] *= 4.0                                          # column exponents differ
+    q, _ = np.linalg.qr(rng.standard_normal((m, r)))
+    ref = z.T @ (z @ q)
+    ext = _ext()
+    zt, qt = torch.from_numpy(z).to(DEV), torch.from_numpy(q).to(DEV)
+    acc = torch.zeros((m, r), dtype=torch.float64, device=DEV)
+    ext.ztzq_accum_tc(zt, qt, acc)
+    scale = float(np.abs(ref).max())
+    assert float(np.abs(acc.cpu().numpy() - ref).max()) < 1e-10 * scale
+    w = torch.zeros((m, r), dtype=torch.float64, device=DEV)
+    ext.cg_matvec_accum(zt, qt, w, torch.empty((n, r), dtype=torch.float64, device=DEV))
+    assert float((w - acc).abs().max()) < 1e-10 * scale
+
+
+def test_ztzq_argument_errors():
+    ext = _ext()
+    z = torch.zeros((64, 128), dtype=torch.float64, device=DEV)
+    with pytest.raises(RuntimeError):
+        ext.ztzq_accum_tc(z, torch.zeros((100, 8), dtype=torch.float64, device=DEV),
+                          torch.zeros((128, 8), dtype=torch.float64, device=DEV))
+    with pytest.raises(RuntimeError):
+        ext.ztzq_accum_tc(z, torch.zeros((128, 8), dtype=torch.float64, device=DEV),
+                          torch.zeros((128, 9), dtype=torch.float64, device=DEV))

@@ -40,6 +40,7 @@ F64_ONLY = {
     "xgpr_b200_ztz_accum_tc_f64": [_ptr, _i64, _i64, _ptr, _int, _int, _int, _ptr, _i64, _ptr],
     "xgpr_b200_symmetrize_upper_f64": [_ptr, _i64, _ptr],
     "xgpr_b200_atb_accum_tc_f64": [_ptr, _ptr, _i64, _i64, _i64, _ptr, _int, _int, _ptr, _i64, _ptr],
+    "xgpr_b200_ztzq_accum_tc_f64": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _int, _int, _ptr, _i64, _ptr],
     "xgpr_b200_atb_accum_f64": [_ptr, _ptr, _i64, _i64, _i64, _ptr, _ptr],
     "xgpr_b200_cg_matvec_accum_f64": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _ptr, _ptr],
 }
@@ -63,6 +64,9 @@ EXPORTED.append("xgpr_b200_ztz_tc_workspace_bytes")
 lib.xgpr_b200_atb_tc_workspace_bytes.argtypes = [_i64, _i64, _i64, _int]
 lib.xgpr_b200_atb_tc_workspace_bytes.restype = _i64
 EXPORTED.append("xgpr_b200_atb_tc_workspace_bytes")
+lib.xgpr_b200_ztzq_tc_workspace_bytes.argtypes = [_i64, _i64, _i64, _int]
+lib.xgpr_b200_ztzq_tc_workspace_bytes.restype = _i64
+EXPORTED.append("xgpr_b200_ztzq_tc_workspace_bytes")
 lib.xgpr_b200_rbf_zzv_supported.argtypes = [_i64, _i64]
 lib.xgpr_b200_rbf_zzv_supported.restype = _int
 EXPORTED.append("xgpr_b200_rbf_zzv_supported")

@@ -60,6 +60,9 @@ double tc_last_gemm_ms();
 int64_t atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int num_slices);
 int atb_accum_tc(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc, int num_slices,
                  int digit_bits, void* workspace, int64_t workspace_bytes, cudaStream_t st);
+int64_t ztzq_tc_workspace_bytes(int64_t n, int64_t m, int64_t r, int num_slices);
+int ztzq_accum_tc(const double* z, int64_t n, int64_t m, const double* q, int64_t r, double* acc, int num_slices,
+                  int digit_bits, void* workspace, int64_t workspace_bytes, cudaStream_t st);
 int cg_matvec_accum(const double* z, int64_t n, int64_t m, const double* v, int64_t r, double* w,
                     double* scratch, cudaStream_t st);
 
@@ -179,6 +182,13 @@ int64_t xgpr_b200_atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int nu
 int xgpr_b200_atb_accum_tc_f64(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc,
                                int num_slices, int digit_bits, void* workspace, int64_t workspace_bytes, void* s) {
     return atb_accum_tc(a, z, n, r, m, acc, num_slices, digit_bits, workspace, workspace_bytes, ST(s));
+}
+int64_t xgpr_b200_ztzq_tc_workspace_bytes(int64_t n, int64_t m, int64_t r, int num_slices) {
+    return ztzq_tc_workspace_bytes(n, m, r, num_slices);
+}
+int xgpr_b200_ztzq_accum_tc_f64(const double* z, int64_t n, int64_t m, const double* q, int64_t r, double* acc,
+                                int num_slices, int digit_bits, void* workspace, int64_t workspace_bytes, void* s) {
+    return ztzq_accum_tc(z, n, m, q, r, acc, num_slices, digit_bits, workspace, workspace_bytes, ST(s));
 }
 int xgpr_b200_atb_accum_f64(const double* a, const double* b, int64_t n, int64_t r, int64_t m, double* c, void* s) {
     return atb_accum(a, b, n, r, m, c, ST(s));

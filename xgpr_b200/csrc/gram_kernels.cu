@@ -354,11 +354,10 @@ ztt_tile_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double
 // tiles double-buffered in shared memory by cp.async (no staging registers), K split across blockIdx.y so that the
 // grid fills 2 CTAs on each of the 148 SMs; partial sums are combined with red.add.f64.  Needs 16-byte-aligned Z rows
 // (m even, base aligned); the host falls back to v1 otherwise.
-constexpr int M2_ROWS = 128, M2_COLS = 32, M2_K = 32;
-constexpr int M2_ZV_LD = M2_K + 2;                               // padded row of the row-major Z tile (doubles)
-constexpr int M2_ZV_STAGE = M2_ROWS * M2_ZV_LD + M2_K * M2_COLS; // doubles per stage, zv2
-constexpr int M2_ZT_STAGE = M2_K * M2_ROWS + M2_K * M2_COLS;     // doubles per stage, ztt2
-constexpr int M2_ZV_SMEM = 2 * M2_ZV_STAGE * 8, M2_ZT_SMEM = 2 * M2_ZT_STAGE * 8;
+constexpr int M2_ROWS = 128, M2_COLS = 32;
+// KC = K chunk (doubles per Z row per stage); the row-major Z tile of zv2 is padded by 2 doubles per row
+__host__ __device__ constexpr int m2_zv_stage(int kc) { return M2_ROWS * (kc + 2) + kc * M2_COLS; }   // doubles per stage, zv2
+__host__ __device__ constexpr int m2_zt_stage(int kc) { return kc * M2_ROWS + kc * M2_COLS; }         // doubles per stage, ztt2
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem, bool valid) {
     const unsigned dst = (unsigned)__cvta_generic_to_shared(smem);
@@ -385,10 +384,12 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
     }
 
 // T (n, 32) (+)= Z[:, k range] V[k range, r0:r0+32].  Thread (tx, ty): rows ty + 16 a, columns {2tx, 2tx+1, 16+2tx, 17+2tx}.
-__global__ void __launch_bounds__(128, 2)
+template <int M2_K, int MINB>
+__global__ void __launch_bounds__(128, MINB)
 zv_tile2_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double* __restrict__ v, int64_t ldv,
                 int r0, int rcount, double* __restrict__ t, int64_t ldt, int64_t k_per, int atomic_out) {
     extern __shared__ __align__(16) double m2_smem[];
+    constexpr int M2_ZV_LD = M2_K + 2, M2_ZV_STAGE = m2_zv_stage(M2_K), PCS = M2_K / 2;   // PCS 16-byte pieces per row
     const int64_t row0 = (int64_t)blockIdx.x * M2_ROWS;
     const int64_t kbeg = (int64_t)blockIdx.y * k_per;
     const int64_t kend = (kbeg + k_per < m) ? kbeg + k_per : m;
@@ -402,15 +403,15 @@ zv_tile2_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double
         double* zs = m2_smem + stage * M2_ZV_STAGE;
         double* vs = zs + M2_ROWS * M2_ZV_LD;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {                           // 128 rows x 16 pieces of 16 bytes
+        for (int i = 0; i < PCS; ++i) {                          // 128 rows x PCS pieces of 16 bytes
             const int p = i * 128 + threadIdx.x;
-            const int rr = p >> 4, j = p & 15;
+            const int rr = p / PCS, j = p % PCS;
             const int64_t row = row0 + rr, k = k0 + 2 * j;
             const bool ok = row < n && k < kend;
             cp_async16(zs + rr * M2_ZV_LD + 2 * j, ok ? z + row * m + k : z, ok);
         }
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {                            // 32 k x 32 columns of V, 8 bytes each
+        for (int i = 0; i < M2_K / 4; ++i) {                     // M2_K k x 32 columns of V, 8 bytes each
             const int p = i * 128 + threadIdx.x;
             const int kk = p >> 5, cc = p & 31;
             const int64_t k = k0 + kk;
@@ -428,7 +429,7 @@ zv_tile2_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double
         __syncthreads();
         const double* zs = m2_smem + s * M2_ZV_STAGE + ty * M2_ZV_LD;
         const double* vs = m2_smem + s * M2_ZV_STAGE + M2_ROWS * M2_ZV_LD + 2 * tx;
-#pragma unroll 4
+#pragma unroll 2
         for (int kp = 0; kp < M2_K / 2; ++kp) {
             double2 zz[8];
 #pragma unroll
@@ -463,10 +464,12 @@ zv_tile2_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double
 }
 
 // W (m, 32) += Z[row range, :]^T T[row range, r0:r0+32].  Thread (tx, ty): Z columns {2ty, 2ty+1} + 32 a, a < 4.
-__global__ void __launch_bounds__(128, 2)
+template <int M2_K, int MINB>
+__global__ void __launch_bounds__(128, MINB)
 ztt_tile2_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double* __restrict__ t, int64_t ldt,
                  int r0, int rcount, double* __restrict__ w, int64_t ldw, int64_t k_per) {
     extern __shared__ __align__(16) double m2_smem[];
+    constexpr int M2_ZT_STAGE = m2_zt_stage(M2_K);
     const int64_t c0 = (int64_t)blockIdx.x * M2_ROWS;
     const int64_t kbeg = (int64_t)blockIdx.y * k_per;
     const int64_t kend = (kbeg + k_per < n) ? kbeg + k_per : n;
@@ -480,7 +483,7 @@ ztt_tile2_kernel(const double* __restrict__ z, int64_t n, int64_t m, const doubl
         double* zs = m2_smem + stage * M2_ZT_STAGE;
         double* ts = zs + M2_K * M2_ROWS;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {                           // 32 rows x 64 pieces of 16 bytes
+        for (int i = 0; i < M2_K / 2; ++i) {                     // M2_K rows x 64 pieces of 16 bytes
             const int p = i * 128 + threadIdx.x;
             const int kk = p >> 6, j = p & 63;
             const int64_t row = k0 + kk, col = c0 + 2 * j;
@@ -488,7 +491,7 @@ ztt_tile2_kernel(const double* __restrict__ z, int64_t n, int64_t m, const doubl
             cp_async16(zs + kk * M2_ROWS + 2 * j, ok ? z + row * m + col : z, ok);
         }
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < M2_K / 4; ++i) {
             const int p = i * 128 + threadIdx.x;
             const int kk = p >> 5, cc = p & 31;
             const int64_t row = k0 + kk;
@@ -534,19 +537,189 @@ ztt_tile2_kernel(const double* __restrict__ z, int64_t n, int64_t m, const doubl
     }
 }
 
+// ------------------------------------------------------------------ multi-RHS matvec, v3 (fp64 tensor cores)
+// The DFMA kernels above level off at ~21 TFLOP/s whatever the tile shape or occupancy (ncu r01h: fp64 pipe "57 %",
+// math-pipe-throttle stalls) -- the same ceiling the DFMA Gram hit, half of what cuBLAS's DMMA DGEMM sustains (36.6
+// TFLOP/s).  tcgen05 has no fp64 kind, so the fp64 tensor-core route on sm_100a is mma.sync.m8n8k4.f64 (full IEEE
+// fp64 FMA, only the summation order differs).  Same 128 x 32 CTA tile, cp.async double buffering and K split as v2;
+// each of the 4 warps owns 32 rows x 32 columns = 4 x 4 fragments (16 DMMA per 8 conflict-free LDS.64).
+constexpr int M3_KC = 16;                                        // K chunk per stage
+constexpr int M3_ZV_LD = M3_KC + 4;                              // row-major Z tile: row stride == 8 words (mod 32)
+constexpr int M3_B_LD = M2_COLS + 8;                             // V / T tile: row stride == 16 words (mod 32)
+constexpr int M3_ZT_LD = M2_ROWS + 8;                            // Z^T operand read from a [k][column] tile
+constexpr int M3_ZV_STAGE = M2_ROWS * M3_ZV_LD + M3_KC * M3_B_LD;
+constexpr int M3_ZT_STAGE = M3_KC * M3_ZT_LD + M3_KC * M3_B_LD;
+constexpr int M3_ZV_SMEM = 2 * M3_ZV_STAGE * 8, M3_ZT_SMEM = 2 * M3_ZT_STAGE * 8;
+
+__device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
+
+// fragment coordinates (PTX ISA, m8n8k4 .f64): g = lane >> 2, t = lane & 3;  A[g][t], B[t][g], C[g][2t], C[g][2t+1]
+__global__ void __launch_bounds__(128, 4)
+zv_mma_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double* __restrict__ v, int64_t ldv,
+              int r0, int rcount, double* __restrict__ tt, int64_t ldt, int64_t k_per, int atomic_out) {
+    extern __shared__ __align__(16) double m2_smem[];
+    const int64_t row0 = (int64_t)blockIdx.x * M2_ROWS;
+    const int64_t kbeg = (int64_t)blockIdx.y * k_per;
+    const int64_t kend = (kbeg + k_per < m) ? kbeg + k_per : m;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+    double acc[4][4][2];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+    auto load = [&](int stage, int64_t k0) {
+        double* zs = m2_smem + stage * M3_ZV_STAGE;
+        double* vs = zs + M2_ROWS * M3_ZV_LD;
+#pragma unroll
+        for (int i = 0; i < M3_KC / 2; ++i) {                    // 128 rows x 8 pieces of 16 bytes
+            const int p = i * 128 + threadIdx.x;
+            const int rr = p / (M3_KC / 2), j = p % (M3_KC / 2);
+            const int64_t row = row0 + rr, k = k0 + 2 * j;
+            const bool ok = row < n && k < kend;
+            cp_async16(zs + rr * M3_ZV_LD + 2 * j, ok ? z + row * m + k : z, ok);
+        }
+#pragma unroll
+        for (int i = 0; i < M3_KC / 4; ++i) {
+            const int p = i * 128 + threadIdx.x;
+            const int kk = p >> 5, cc = p & 31;
+            const int64_t k = k0 + kk;
+            const bool ok = k < kend && cc < rcount;
+            cp_async8(vs + kk * M3_B_LD + cc, ok ? v + k * ldv + r0 + cc : v, ok);
+        }
+    };
+    load(0, kbeg);
+    cp_async_commit();
+    int s = 0;
+    for (int64_t k0 = kbeg; k0 < kend; k0 += M3_KC, s ^= 1) {
+        if (k0 + M3_KC < kend) load(s ^ 1, k0 + M3_KC);
+        cp_async_commit();
+        cp_async_wait<1>();
+        __syncthreads();
+        const double* zs = m2_smem + s * M3_ZV_STAGE + (warp * 32 + g) * M3_ZV_LD + t;
+        const double* vs = m2_smem + s * M3_ZV_STAGE + M2_ROWS * M3_ZV_LD + t * M3_B_LD + g;
+#pragma unroll
+        for (int k4 = 0; k4 < M3_KC / 4; ++k4) {
+            double fa[4], fb[4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) fa[a] = zs[a * 8 * M3_ZV_LD + 4 * k4];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) fb[b] = vs[4 * k4 * M3_B_LD + 8 * b];
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) dmma884(acc[a][b], fa[a], fb[b]);
+        }
+        __syncthreads();
+    }
+    cp_async_wait<0>();
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+        const int64_t row = row0 + warp * 32 + a * 8 + g;
+        if (row >= n) continue;
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int cc = b * 8 + 2 * t + e;
+                if (cc >= rcount) continue;
+                double* dst = tt + row * ldt + r0 + cc;
+                if (atomic_out) atomicAdd(dst, acc[a][b][e]);
+                else *dst = acc[a][b][e];
+            }
+    }
+}
+
+__global__ void __launch_bounds__(128, 4)
+ztt_mma_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double* __restrict__ tt, int64_t ldt,
+               int r0, int rcount, double* __restrict__ w, int64_t ldw, int64_t k_per) {
+    extern __shared__ __align__(16) double m2_smem[];
+    const int64_t c0 = (int64_t)blockIdx.x * M2_ROWS;
+    const int64_t kbeg = (int64_t)blockIdx.y * k_per;
+    const int64_t kend = (kbeg + k_per < n) ? kbeg + k_per : n;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+    double acc[4][4][2];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+    auto load = [&](int stage, int64_t k0) {
+        double* zs = m2_smem + stage * M3_ZT_STAGE;
+        double* ts = zs + M3_KC * M3_ZT_LD;
+#pragma unroll
+        for (int i = 0; i < M3_KC / 2; ++i) {                    // 16 rows x 64 pieces of 16 bytes
+            const int p = i * 128 + threadIdx.x;
+            const int kk = p >> 6, j = p & 63;
+            const int64_t row = k0 + kk, col = c0 + 2 * j;
+            const bool ok = row < kend && col < m;
+            cp_async16(zs + kk * M3_ZT_LD + 2 * j, ok ? z + row * m + col : z, ok);
+        }
+#pragma unroll
+        for (int i = 0; i < M3_KC / 4; ++i) {
+            const int p = i * 128 + threadIdx.x;
+            const int kk = p >> 5, cc = p & 31;
+            const int64_t row = k0 + kk;
+            const bool ok = row < kend && cc < rcount;
+            cp_async8(ts + kk * M3_B_LD + cc, ok ? tt + row * ldt + r0 + cc : tt, ok);
+        }
+    };
+    load(0, kbeg);
+    cp_async_commit();
+    int s = 0;
+    for (int64_t k0 = kbeg; k0 < kend; k0 += M3_KC, s ^= 1) {
+        if (k0 + M3_KC < kend) load(s ^ 1, k0 + M3_KC);
+        cp_async_commit();
+        cp_async_wait<1>();
+        __syncthreads();
+        const double* zs = m2_smem + s * M3_ZT_STAGE + t * M3_ZT_LD + warp * 32 + g;
+        const double* ts = m2_smem + s * M3_ZT_STAGE + M3_KC * M3_ZT_LD + t * M3_B_LD + g;
+#pragma unroll
+        for (int k4 = 0; k4 < M3_KC / 4; ++k4) {
+            double fa[4], fb[4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) fa[a] = zs[4 * k4 * M3_ZT_LD + 8 * a];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) fb[b] = ts[4 * k4 * M3_B_LD + 8 * b];
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) dmma884(acc[a][b], fa[a], fb[b]);
+        }
+        __syncthreads();
+    }
+    cp_async_wait<0>();
+    const bool atomic_out = gridDim.y > 1;
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+        const int64_t col = c0 + warp * 32 + a * 8 + g;
+        if (col >= m) continue;
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int cc = b * 8 + 2 * t + e;
+                if (cc >= rcount) continue;
+                double* dst = w + col * ldw + r0 + cc;
+                if (atomic_out) atomicAdd(dst, acc[a][b][e]);
+                else *dst += acc[a][b][e];
+            }
+    }
+}
+
 // K split that fills 2 CTAs on each SM with the smallest tail (each split at least 8 K chunks long)
-static int64_t m2_k_per(int64_t tiles, int64_t k_total) {
-    const int64_t slots = 148 * 2;
+static int64_t m2_k_per(int64_t tiles, int64_t k_total, int64_t slots) {
     int best = 1;
     double best_eff = 0.0;
     for (int ks = 1; ks <= 64; ++ks) {
-        if (ks > 1 && k_total / ks < 8 * M2_K) break;
+        if (ks > 1 && k_total / ks < 256) break;
         const int64_t units = tiles * ks;
         const double eff = (double)units / (double)(((units + slots - 1) / slots) * slots);
         if (eff > best_eff + 0.02) { best_eff = eff; best = ks; }
     }
     int64_t k_per = (k_total + best - 1) / best;
-    return ((k_per + M2_K - 1) / M2_K) * M2_K;
+    return ((k_per + 31) / 32) * 32;
 }
 
 // ------------------------------------------------------------------ host
@@ -616,21 +789,32 @@ int cg_matvec_accum(const double* z, int64_t n, int64_t m, const double* v, int6
     }
     const bool v2 = (m % 2 == 0) && (reinterpret_cast<uintptr_t>(z) % 16 == 0) && !getenv("XGPR_B200_MATVEC_V1");
     if (v2) {
+        // default: fp64 tensor-core kernels (4 CTAs per SM); XGPR_B200_MATVEC_DFMA selects the v2 DFMA kernels
+        static const bool dfma = getenv("XGPR_B200_MATVEC_DFMA") != nullptr;
+        constexpr int ZV16 = 2 * m2_zv_stage(16) * 8, ZT16 = 2 * m2_zt_stage(16) * 8;
         static bool attr_done = false;
         if (!attr_done) {
-            cudaFuncSetAttribute(zv_tile2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, M2_ZV_SMEM);
-            cudaFuncSetAttribute(ztt_tile2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, M2_ZT_SMEM);
+            cudaFuncSetAttribute(zv_tile2_kernel<16, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ZV16);
+            cudaFuncSetAttribute(ztt_tile2_kernel<16, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ZT16);
+            cudaFuncSetAttribute(zv_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, M3_ZV_SMEM);
+            cudaFuncSetAttribute(ztt_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, M3_ZT_SMEM);
             attr_done = true;
         }
+        const int64_t slots = 148 * (dfma ? 3 : 4);
         const int64_t rt = (n + M2_ROWS - 1) / M2_ROWS, ct = (m + M2_ROWS - 1) / M2_ROWS;
-        const int64_t kz = m2_k_per(rt, m), kt = m2_k_per(ct, n);
+        const int64_t kz = m2_k_per(rt, m, slots), kt = m2_k_per(ct, n, slots);
         const unsigned sz = (unsigned)((m + kz - 1) / kz), stt = (unsigned)((n + kt - 1) / kt);
         if (sz > 1) cudaMemsetAsync(scratch, 0, sizeof(double) * (size_t)n * (size_t)r, st);
+        const dim3 gz((unsigned)rt, sz), gt((unsigned)ct, stt);
         for (int r0 = 0; r0 < r; r0 += M2_COLS) {
             const int rc = (int)((r - r0 < M2_COLS) ? (r - r0) : M2_COLS);
-            zv_tile2_kernel<<<dim3((unsigned)rt, sz), 128, M2_ZV_SMEM, st>>>(z, n, m, v, r, r0, rc, scratch, r, kz,
-                                                                              sz > 1 ? 1 : 0);
-            ztt_tile2_kernel<<<dim3((unsigned)ct, stt), 128, M2_ZT_SMEM, st>>>(z, n, m, scratch, r, r0, rc, w, r, kt);
+            if (dfma) {
+                zv_tile2_kernel<16, 3><<<gz, 128, ZV16, st>>>(z, n, m, v, r, r0, rc, scratch, r, kz, sz > 1 ? 1 : 0);
+                ztt_tile2_kernel<16, 3><<<gt, 128, ZT16, st>>>(z, n, m, scratch, r, r0, rc, w, r, kt);
+            } else {
+                zv_mma_kernel<<<gz, 128, M3_ZV_SMEM, st>>>(z, n, m, v, r, r0, rc, scratch, r, kz, sz > 1 ? 1 : 0);
+                ztt_mma_kernel<<<gt, 128, M3_ZT_SMEM, st>>>(z, n, m, scratch, r, r0, rc, w, r, kt);
+            }
             count_launch(2);
         }
         return check_launch("cg_matvec");

@@ -116,6 +116,53 @@ tc_slice_kernel(const double* __restrict__ z, int64_t n, int64_t m, int64_t n_pa
     }
 }
 
+// ------------------------------------------------------------------ row operand: contraction along the contiguous axis
+// For T = Z Q the contraction runs over Z's columns, so Z's own row-major layout is already K-major: one exponent per ROW
+// (max over the row) and digit planes[k][row][col] with no transposition.  One warp per row for the maxima.
+__global__ void __launch_bounds__(256)
+tc_rowmax_kernel(const double* __restrict__ z, int64_t n, int64_t m, unsigned long long* __restrict__ rmax) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= n) return;
+    const double* p = z + row * m;
+    double mx = 0.0;
+    for (int64_t k = lane; k < m; k += 32) mx = fmax(mx, fabs(p[k]));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) rmax[row] = (unsigned long long)__double_as_longlong(mx);
+}
+
+// planes[k][row][col], col contiguous with stride m_pad (zero beyond m); each thread slices 4 consecutive columns
+template <int S, int BITS>
+__global__ void __launch_bounds__(256)
+tc_slice_rows_kernel(const double* __restrict__ z, int64_t n, int64_t m, int64_t m_pad,
+                     const double* __restrict__ rowscale, int8_t* __restrict__ planes) {
+    const int64_t row = blockIdx.y;
+    const int64_t c0 = ((int64_t)blockIdx.x * 256 + threadIdx.x) * 4;
+    if (c0 >= m_pad) return;
+    constexpr long long HALF = 1ll << (BITS - 1), MASK = (1ll << BITS) - 1, TOP = BITS == 8 ? 127 : 64;
+    const double mul = ldexp(1.0 / rowscale[row], BITS * S);
+    uint32_t packed[S];
+#pragma unroll
+    for (int k = 0; k < S; ++k) packed[k] = 0u;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const double v = (c0 + j < m) ? z[row * m + c0 + j] : 0.0;
+        long long X = __double2ll_rn(v * mul);
+#pragma unroll
+        for (int k = S - 1; k >= 1; --k) {
+            const long long d = ((X + HALF) & MASK) - HALF;
+            packed[k] |= ((uint32_t)(uint8_t)(int8_t)d) << (8 * j);
+            X = (X - d) >> BITS;
+        }
+        X = X > TOP ? TOP : (X < -TOP ? -TOP : X);
+        packed[0] |= ((uint32_t)(uint8_t)(int8_t)X) << (8 * j);
+    }
+    const int64_t plane_stride = n * m_pad;
+#pragma unroll
+    for (int k = 0; k < S; ++k) *reinterpret_cast<uint32_t*>(planes + k * plane_stride + row * m_pad + c0) = packed[k];
+}
+
 // ------------------------------------------------------------------ PTX wrappers (sm_100a)
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -649,6 +696,101 @@ int atb_accum_tc(const double* a, const double* z, int64_t n, int64_t r, int64_t
         rc = tc_prepare_operand(ob, ws_b, z + r0 * m, rows, m, num_slices, digit_bits, sms, st);
         if (rc != XGPR_B200_OK) return rc;
         rc = tc_launch_gemm(oa, ob, rows, r, m, 0, num_slices, digit_bits, acc, sms, st);
+        if (rc != XGPR_B200_OK) return rc;
+    }
+    return XGPR_B200_OK;
+}
+
+// ------------------------------------------------------------------ acc (m, r) += Z^T (Z Q): the Nystrom second pass
+// [rmax u64 (rows)] [rowscale f64 (rows)] [planes int8 (S, rows, m_pad)]
+static inline int64_t tc_row_operand_bytes(int64_t rows, int64_t m, int num_slices) {
+    return round_up(rows * 8, 1024) * 2 + round_up((int64_t)num_slices * rows * round_up(m, TC_BK), 1024);
+}
+
+template <int S>
+static void launch_slice_rows(const double* z, int64_t n, int64_t m, int64_t m_pad, const double* rs, int8_t* planes,
+                              int digit_bits, cudaStream_t st) {
+    dim3 grid((unsigned)((m_pad / 4 + 255) / 256), (unsigned)n);
+    if (digit_bits == 8) tc_slice_rows_kernel<S, 8><<<grid, 256, 0, st>>>(z, n, m, m_pad, rs, planes);
+    else                 tc_slice_rows_kernel<S, 7><<<grid, 256, 0, st>>>(z, n, m, m_pad, rs, planes);
+}
+
+static int tc_prepare_row_operand(TcOperand& op, uint8_t* ws, const double* z, int64_t rows, int64_t m, int num_slices,
+                                  int digit_bits, cudaStream_t st) {
+    const int64_t m_pad = round_up(m, TC_BK);
+    op.cmax = (unsigned long long*)ws;
+    op.colscale = (double*)(ws + round_up(rows * 8, 1024));
+    op.planes = (int8_t*)(ws + 2 * round_up(rows * 8, 1024));
+    tc_rowmax_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(z, rows, m, op.cmax);
+    tc_exponent_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(op.cmax, rows, op.colscale, digit_bits);
+    switch (num_slices) {
+        case 2: launch_slice_rows<2>(z, rows, m, m_pad, op.colscale, op.planes, digit_bits, st); break;
+        case 3: launch_slice_rows<3>(z, rows, m, m_pad, op.colscale, op.planes, digit_bits, st); break;
+        case 4: launch_slice_rows<4>(z, rows, m, m_pad, op.colscale, op.planes, digit_bits, st); break;
+        case 5: launch_slice_rows<5>(z, rows, m, m_pad, op.colscale, op.planes, digit_bits, st); break;
+        case 6: launch_slice_rows<6>(z, rows, m, m_pad, op.colscale, op.planes, digit_bits, st); break;
+        default: launch_slice_rows<7>(z, rows, m, m_pad, op.colscale, op.planes, digit_bits, st); break;
+    }
+    count_launch(3);
+    EncodeTiledFn encode = encode_tiled_fn();
+    if (!encode) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return XGPR_B200_ECUDA; }
+    const cuuint64_t gdim[3] = {(cuuint64_t)m_pad, (cuuint64_t)rows, (cuuint64_t)num_slices};
+    const cuuint64_t gstride[2] = {(cuuint64_t)m_pad, (cuuint64_t)(rows * m_pad)};
+    const cuuint32_t box[3] = {TC_BK, 128, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult cr = encode(&op.map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, op.planes, gdim, gstride, box, estr,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d)", (int)cr); return XGPR_B200_ECUDA; }
+    return check_launch("tc_prepare_row_operand");
+}
+
+// workspace: [Z planes: row-major for Z Q, then reused column-major for Z^T T] [Q planes, then reused for T planes]
+// plus the fp64 product T (rows per pass, r)
+static inline int64_t ztzq_rows_per_pass(int64_t n) { return n < 32768 ? n : 32768; }
+int64_t ztzq_tc_workspace_bytes(int64_t n, int64_t m, int64_t r, int num_slices) {
+    if (n <= 0 || m <= 0 || r <= 0 || num_slices < 2 || num_slices > 7 || m > TC_MAX_ROWS) return -1;
+    const int64_t rows = ztzq_rows_per_pass(n);
+    const int64_t za = tc_row_operand_bytes(rows, m, num_slices), zb = tc_operand_bytes(rows, m, num_slices);
+    const int64_t qa = tc_operand_bytes(m, r, num_slices), qb = tc_operand_bytes(rows, r, num_slices);
+    return (za > zb ? za : zb) + (qa > qb ? qa : qb) + round_up(rows * r * 8, 1024);
+}
+
+int ztzq_accum_tc(const double* z, int64_t n, int64_t m, const double* q, int64_t r, double* acc, int num_slices,
+                  int digit_bits, void* workspace, int64_t workspace_bytes, cudaStream_t st) {
+    XB_REQUIRE(digit_bits == 7 || digit_bits == 8, "digit_bits must be 7 or 8");
+    XB_REQUIRE(n > 0 && m > 0 && r > 0, "no datapoints");
+    XB_REQUIRE(z && q && acc && workspace, "null pointer");
+    XB_REQUIRE(num_slices >= 2 && num_slices <= 7, "num_slices must be in [2, 7]");
+    XB_REQUIRE(m <= TC_MAX_ROWS, "more than 65,536 features: use cg_matvec_accum");
+    XB_REQUIRE(workspace_bytes >= ztzq_tc_workspace_bytes(n, m, r, num_slices), "workspace too small");
+    XB_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+    int sms, rc = tc_setup(sms);
+    if (rc != XGPR_B200_OK) return rc;
+    const int64_t pass = ztzq_rows_per_pass(n);
+    const int64_t za = tc_row_operand_bytes(pass, m, num_slices), zb = tc_operand_bytes(pass, m, num_slices);
+    const int64_t qa = tc_operand_bytes(m, r, num_slices), qb = tc_operand_bytes(pass, r, num_slices);
+    uint8_t* ws_z = (uint8_t*)workspace;
+    uint8_t* ws_q = ws_z + (za > zb ? za : zb);
+    double* t = (double*)(ws_q + (qa > qb ? qa : qb));
+    for (int64_t r0 = 0; r0 < n; r0 += pass) {
+        const int64_t rows = (n - r0 < pass) ? (n - r0) : pass;
+        const double* zc = z + r0 * m;
+        TcOperand oz, oq;
+        // T (rows, r) = Z Q : contraction over the m features
+        rc = tc_prepare_row_operand(oz, ws_z, zc, rows, m, num_slices, digit_bits, st);
+        if (rc != XGPR_B200_OK) return rc;
+        rc = tc_prepare_operand(oq, ws_q, q, m, r, num_slices, digit_bits, sms, st);
+        if (rc != XGPR_B200_OK) return rc;
+        cudaMemsetAsync(t, 0, sizeof(double) * (size_t)rows * (size_t)r, st);
+        rc = tc_launch_gemm(oz, oq, m, rows, r, 0, num_slices, digit_bits, t, sms, st);
+        if (rc != XGPR_B200_OK) return rc;
+        // acc (m, r) += Z^T T : contraction over the rows
+        rc = tc_prepare_operand(oz, ws_z, zc, rows, m, num_slices, digit_bits, sms, st);
+        if (rc != XGPR_B200_OK) return rc;
+        rc = tc_prepare_operand(oq, ws_q, t, rows, r, num_slices, digit_bits, sms, st);
+        if (rc != XGPR_B200_OK) return rc;
+        rc = tc_launch_gemm(oz, oq, rows, m, r, 0, num_slices, digit_bits, acc, sms, st);
         if (rc != XGPR_B200_OK) return rc;
     }
     return XGPR_B200_OK;

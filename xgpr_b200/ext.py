@@ -278,6 +278,22 @@ def atb_accum_tc(a, z, acc, num_slices=5, digit_bits=8):
                                          _stream()))
 
 
+def ztzq_accum_tc(z, q, acc, num_slices=5, digit_bits=8):
+    """acc (m, r) += z^T (z q) on the tensor cores: the second Nystrom pass (rand_nys_constructors.py:18-36)."""
+    z = _dev(z, "z", (torch.float64,), 2)
+    q = _dev(q.contiguous(), "q", (torch.float64,), 2)
+    acc = _dev(acc, "acc", (torch.float64,), 2)
+    if q.shape[0] != z.shape[1] or acc.shape[0] != z.shape[1] or acc.shape[1] != q.shape[1]:
+        raise RuntimeError("wrong array sizes")
+    need = lib.xgpr_b200_ztzq_tc_workspace_bytes(z.shape[0], z.shape[1], q.shape[1], int(num_slices))
+    if need < 0:
+        raise RuntimeError("num_slices must be in [2, 7] and at most 65,536 features")
+    ws = _tc_workspace(z.device, need)
+    check(lib.xgpr_b200_ztzq_accum_tc_f64(z.data_ptr(), z.shape[0], z.shape[1], q.data_ptr(), q.shape[1],
+                                          acc.data_ptr(), int(num_slices), int(digit_bits), ws.data_ptr(), ws.numel(),
+                                          _stream()))
+
+
 def ztz_accum_tc(z, ztz, num_slices=5, mirror=True, digit_bits=8):
     """Upper triangle of ztz += z^T z on the tensor cores (tcgen05 kind::i8 over `num_slices` exact int8 digit planes of
     `digit_bits` bits, int32 accumulation in TMEM; csrc/gram_tc_kernels.cu).  Default 5 x 8 bits: element error

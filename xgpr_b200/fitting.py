@@ -392,6 +392,12 @@ def _single_pass_srht_zty(dataset, kernel, compressor, acc_results, z_trans_y, o
 def _single_pass_gauss(dataset, kernel, q_mat, acc_results, ops, scratch_holder):
     """rand_nys_constructors.py:18-36: acc (M, rank) += Z^T (Z Q) -- the CG matvec with `rank` right-hand sides."""
     q_mat = q_mat.contiguous()
+    tc = getattr(ops, "ztzq_accum_tc", None)
+    if tc is not None and q_mat.shape[0] <= 65536 and q_mat.shape[1] >= 64:
+        # wide Q: both GEMMs on the tensor cores (exact int8 digit planes, ~1e-12 of the row / column scale)
+        for xdata, ldata in dataset.get_chunked_x_data():
+            tc(kernel.transform_x(xdata, ldata), q_mat, acc_results)
+        return
     for xdata, ldata in dataset.get_chunked_x_data():
         z = kernel.transform_x(xdata, ldata)
         s = scratch_holder.get("s")
