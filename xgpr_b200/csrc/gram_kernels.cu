@@ -538,10 +538,10 @@ ztt_tile2_kernel(const double* __restrict__ z, int64_t n, int64_t m, const doubl
 }
 
 // ------------------------------------------------------------------ multi-RHS matvec, v3 (fp64 tensor cores)
-// The DFMA kernels above level off at ~21 TFLOP/s whatever the tile shape or occupancy (ncu r01h: fp64 pipe "57 %",
-// math-pipe-throttle stalls) -- the same ceiling the DFMA Gram hit, half of what cuBLAS's DMMA DGEMM sustains (36.6
-// TFLOP/s).  tcgen05 has no fp64 kind, so the fp64 tensor-core route on sm_100a is mma.sync.m8n8k4.f64 (full IEEE
-// fp64 FMA, only the summation order differs).  Same 128 x 32 CTA tile, cp.async double buffering and K split as v2;
+// The DFMA kernels above stall at ~21 TFLOP/s whatever the K chunk or occupancy (ncu r01h: fp64 pipe 57 % active, wait +
+// math-pipe-throttle stalls; the roof is 36.6 TFLOP/s, which cuBLAS's DMMA DGEMM reaches).  tcgen05 has no fp64 kind,
+// so the fp64 tensor-core route on sm_100a is mma.sync.m8n8k4.f64: one instruction does the work of 8 DFMAs on the same
+// pipe with one operand load per fragment (full IEEE fp64 FMAs, only the summation order differs).  Same 128 x 32 CTA tile, cp.async double buffering and K split as v2;
 // each of the 4 warps owns 32 rows x 32 columns = 4 x 4 fragments (16 DMMA per 8 conflict-free LDS.64).
 constexpr int M3_KC = 16;                                        // K chunk per stage
 constexpr int M3_ZV_LD = M3_KC + 4;                              // row-major Z tile: row stride == 8 words (mod 32)
