@@ -6,7 +6,7 @@ Metric : RFF feature rows/s @ 16384 RFFs, RBF kernel (configs[1]: 64 input featu
 Step   : one pass of the fused SORF+RBF kernel over one chunk of ``--rows`` synthetic rows
          (output chunk = rows x 131,072 B  >>  126 MB L2, so every step streams through HBM).
 value  : whole-job rows/s with the chunk resident in HBM (all ranks; rows shard, no collective).
-e2e    : the same metric through the kernel-plugin call ``RBF.transform_x(host_chunk)`` -- host
+e2e    : the same metric through the kernel-plugin call ``RBF.transform_stream(host chunks)`` -- host
          (pinned) input, H2D inside the timed region, and a D2H read of the chunk's first feature row.
 roofline: achieved algorithmic GB/s of the feature kernel (CUDA events around each launch) / measured
          HBM copy bandwidth (MEASURED_PEAKS.json).
@@ -276,19 +276,20 @@ def run_b200(args):
     kern_ms = [a.elapsed_time(b) for a, b in evs]
     dev_ms = evs[0][0].elapsed_time(evs[-1][1])
     # ---------------- end to end through the plugin API (host input, H2D, D2H of a result row)
-    def e2e_step():
-        z = kern.transform_x(x_pinned)             # H2D + sigma scale + fused kernel + intercept column
-        return z[0].cpu()                          # D2H read of the first feature row (131 KB)
+    # The plugin's streaming call: every step copies its chunk from pinned host memory (H2D inside the timed region, issued
+    # on a side stream one chunk ahead), scales it, runs the fused kernel, sets the intercept column, and the loop reads
+    # the step's first feature row back to the host (131 KB, a synchronising D2H) before taking the next chunk.
+    def e2e_steps(k):
+        for z in kern.transform_stream((x_pinned, None) for _ in range(k)):
+            z[0].cpu()
 
-    for _ in range(max(args.warmup, 3)):
-        e2e_step()
+    e2e_steps(max(args.warmup, 3))
     torch.cuda.synchronize()
     barrier()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(args.steps):
-        e2e_step()
+    e2e_steps(args.steps)
     e1.record()
     torch.cuda.synchronize()
     barrier()
@@ -329,7 +330,7 @@ def run_b200(args):
                              % (rows * NUM_RFFS * 8 / 1e9),
                        "sharding": "rows, no collective"},
             "e2e": {"value": e2e_val, "unit": "rows/s", "h2d_bytes_per_step": rows * D_IN * 4,
-                    "d2h_bytes_per_step": NUM_RFFS * 8, "api": "xgpr_b200.kernels.RBF.transform_x(pinned host chunk)"},
+                    "d2h_bytes_per_step": NUM_RFFS * 8, "api": "xgpr_b200.kernels.RBF.transform_stream(pinned host chunks): transform_x per chunk, next chunk's H2D double-buffered"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": how,

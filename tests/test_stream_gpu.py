@@ -1,0 +1,85 @@
+"""GPU: the double-buffered chunk stream (KernelBaseclass.transform_stream) and the resident-Z CG matvec give exactly
+what the per-chunk reference loop gives (`for xdata, ldata in dataset.get_chunked_x_data(): kernel.transform_x(...)`,
+fitting_toolkit/cg_tools.py:40-44).  Bit-exact: the same kernels run on the same staged inputs."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _chunks(x, lens, size):
+    for lo in range(0, x.shape[0], size):
+        yield x[lo:lo + size], None if lens is None else lens[lo:lo + size]
+
+
+@pytest.mark.parametrize("source", ["numpy", "pinned", "pageable", "cuda"])
+def test_stream_equals_transform_x_rbf(source):
+    from xgpr_b200.kernels import RBF
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((5000, 40)).astype(np.float32)
+    kern = RBF(x.shape, 1024, random_seed=123, device="cuda")
+    kern.set_hyperparams(np.log(np.asarray([0.3, 0.2])), logspace=True)
+    src = {"numpy": x, "pinned": torch.from_numpy(x).pin_memory(), "pageable": torch.from_numpy(x),
+           "cuda": torch.from_numpy(x).cuda()}[source]
+    ref = [kern.transform_x(c) for c, _ in _chunks(src, None, 777)]
+    got = list(kern.transform_stream(_chunks(src, None, 777)))
+    assert len(got) == len(ref) == 7
+    for a, b in zip(got, ref):
+        assert torch.equal(a, b)
+    assert list(kern.transform_stream(iter(()))) == []
+
+
+def test_stream_equals_transform_x_conv_with_lengths():
+    from xgpr_b200.kernels import Conv1dRBF
+    rng = np.random.default_rng(1)
+    x = rng.standard_normal((300, 30, 8)).astype(np.float32)
+    lens = rng.integers(9, 31, size=300).astype(np.int32)
+    kern = Conv1dRBF(x.shape, 512, random_seed=123, device="cuda", kernel_spec_parms={"conv_width": 9})
+    kern.set_hyperparams(np.log(np.asarray([0.3, 0.4])), logspace=True)
+    ref = [kern.transform_x(c, l) for c, l in _chunks(x, lens, 64)]
+    got = list(kern.transform_stream(_chunks(x, lens, 64)))
+    for a, b in zip(got, ref):
+        assert torch.equal(a, b)
+
+
+def test_stream_many_chunks_no_reuse_hazard():
+    """Staging buffers are allocated on the side stream and consumed on the main one: 200 small chunks queued without any
+    host synchronisation must still match (a missing record_stream / event wait shows up as corrupted inputs)."""
+    from xgpr_b200.kernels import RBF
+    rng = np.random.default_rng(2)
+    x = torch.from_numpy(rng.standard_normal((200 * 256, 64)).astype(np.float32)).pin_memory()
+    kern = RBF(tuple(x.shape), 2048, random_seed=123, device="cuda")
+    kern.set_hyperparams(np.log(np.asarray([0.3, 0.2])), logspace=True)
+    sums = [z.sum(dim=0) for z in kern.transform_stream(_chunks(x, None, 256))]          # no sync inside the loop
+    torch.cuda.synchronize()
+    ref = [kern.transform_x(c).sum(dim=0) for c, _ in _chunks(x, None, 256)]
+    for a, b in zip(sums, ref):
+        assert torch.equal(a, b)
+
+
+def test_cg_resident_z_equals_regenerated():
+    """Multi-RHS CG matvec with the shard's Z kept in HBM across iterations == regenerating Z per iteration."""
+    from xgpr_b200 import fitting
+    from xgpr_b200.kernels import RBF
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((3000, 24)).astype(np.float32)
+    y = rng.standard_normal(3000)
+    ds = fitting.build_shard_dataset(x, y, None, chunk_size=700)
+    kern = RBF(x.shape, 512, random_seed=123, device="cuda")
+    kern.set_hyperparams(np.log(np.asarray([0.5, 0.3])), logspace=True)
+    vec = torch.from_numpy(rng.standard_normal((512, 5))).cuda()
+    outs = []
+    for keep in (True, False):
+        cg = fitting.ConjugateGrad()
+        cg.keep_resident = keep
+        w = torch.zeros_like(vec)
+        for _ in range(3):                              # second and third calls use the resident copy
+            cg._matvec(ds, kern, vec, w)
+        assert (cg._resident is not None) == keep
+        outs.append(w.clone())
+    # same Z, same kernels; only the fp64 atomics' order differs between runs
+    assert float((outs[0] - outs[1]).abs().max()) <= 1e-12 * float(outs[0].abs().max())
+    z = torch.cat([kern.transform_x(c) for c, _ in ds.get_chunked_x_data()])
+    ref = z.T @ (z @ vec) + kern.get_lambda() ** 2 * vec
+    assert float((outs[0] - ref).abs().max()) <= 1e-11 * float(ref.abs().max())

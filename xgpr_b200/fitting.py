@@ -137,6 +137,17 @@ def _new(shape, like_device):
     return torch.zeros(shape, dtype=torch.float64, device=like_device)
 
 
+def _transformed_chunks(dataset, kernel):
+    """kernel.transform_x over the shard's chunks; on the GPU through the kernel's double-buffered transform_stream, so
+    a host-resident chunk's copy runs under the previous chunk's feature generation."""
+    stream = getattr(kernel, "transform_stream", None)
+    if stream is not None and kernel.device == "cuda":
+        yield from stream(dataset.get_chunked_x_data())
+        return
+    for xdata, ldata in dataset.get_chunked_x_data():
+        yield kernel.transform_x(xdata, ldata)
+
+
 def _device_of(kernel):
     return torch.device("cuda", torch.cuda.current_device()) if kernel.device == "cuda" else torch.device("cpu")
 
@@ -320,8 +331,7 @@ class ConjugateGrad:
             free, _ = torch.cuda.mem_get_info(dev)
             if rows * kernel.get_num_rffs() * 8 <= fraction * free:
                 keep = []
-        for x, lengths in dataset.get_chunked_x_data():
-            z = kernel.transform_x(x, lengths)
+        for z in _transformed_chunks(dataset, kernel):
             if keep is not None:
                 keep.append(z)
             yield z
@@ -421,8 +431,8 @@ def _single_pass_gauss(dataset, kernel, q_mat, acc_results, ops, scratch_holder)
     tc = getattr(ops, "ztzq_accum_tc", None)
     if tc is not None and q_mat.shape[0] <= 65536 and q_mat.shape[1] >= 64:
         # wide Q: both GEMMs on the tensor cores (exact int8 digit planes, ~1e-12 of the row / column scale)
-        for xdata, ldata in dataset.get_chunked_x_data():
-            tc(kernel.transform_x(xdata, ldata), q_mat, acc_results)
+        for z in _transformed_chunks(dataset, kernel):
+            tc(z, q_mat, acc_results)
         return
     for xdata, ldata in dataset.get_chunked_x_data():
         z = kernel.transform_x(xdata, ldata)

@@ -150,6 +150,50 @@ class KernelBaseclass(abc.ABC):
             xtrans[:, 0] = 1.0
         return xtrans
 
+    def transform_stream(self, chunks):
+        """transform_x over an iterable of (input_x, sequence_length) chunks, double-buffered: the host->device copy of
+        chunk i+1 is issued on a side stream before chunk i's kernels are launched, so the copy (pinned memory: fully
+        asynchronous; pageable: staged by the driver) runs under the previous chunk's feature generation.  Yields exactly
+        what transform_x(input_x, sequence_length) returns, in order.  This is how the L4 chunk loops of the reference
+        (`for xdata, ldata in dataset.get_chunked_x_data(): kernel.transform_x(xdata, ldata)`, e.g.
+        fitting_toolkit/cg_tools.py:40-44) are meant to be driven when the dataset lives on the host."""
+        if self.device != "cuda":
+            raise RuntimeError("xgpr_b200 generates features on device='cuda' only (no CPU fallback).")
+        side = getattr(self, "_copy_stream", None)
+        if side is None:
+            side = self._copy_stream = torch.cuda.Stream()
+
+        def stage(item):
+            input_x, seqlen = item
+            main = torch.cuda.current_stream()
+            if isinstance(input_x, torch.Tensor) and input_x.is_cuda:
+                return self._stage_input(input_x), seqlen, None
+            with torch.cuda.stream(side):
+                xin = self._stage_input(input_x)
+                done = torch.cuda.Event()
+                done.record(side)
+            xin.record_stream(main)
+            return xin, seqlen, done
+
+        it = iter(chunks)
+        try:
+            nxt = stage(next(it))
+        except StopIteration:
+            return
+        while nxt is not None:
+            xin, seqlen, done = nxt
+            try:
+                nxt = stage(next(it))
+            except StopIteration:
+                nxt = None
+            if done is not None:
+                torch.cuda.current_stream().wait_event(done)
+            xtrans = self.kernel_specific_transform(xin, self._stage_seqlen(seqlen))
+            if self.fit_intercept:
+                xtrans[:, 0] = 1.0
+            yield xtrans
+            del xtrans                                   # one output chunk alive besides the consumer's
+
     def transform_x_y(self, input_x, input_y, sequence_length=None, classification=False):
         xtrans = self.transform_x(input_x, sequence_length)
         ydt = torch.int32 if classification else torch.float64
