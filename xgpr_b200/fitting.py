@@ -148,6 +148,28 @@ def _transformed_chunks(dataset, kernel):
         yield kernel.transform_x(xdata, ldata)
 
 
+def _transformed_xy_chunks(dataset, kernel):
+    """(Z, y) per chunk, as kernel.transform_x_y over dataset.get_chunked_data(), through the double-buffered stream."""
+    stream = getattr(kernel, "transform_stream", None)
+    if stream is None or kernel.device != "cuda":
+        for xin, yin, ldata in dataset.get_chunked_data():
+            yield kernel.transform_x_y(xin, yin, ldata)
+        return
+    from .kernels.base import to_device
+    ys = []
+
+    def x_chunks():
+        for xin, yin, ldata in dataset.get_chunked_data():
+            ys.append(yin)
+            yield xin, ldata
+
+    for z in stream(x_chunks()):
+        yin = ys.pop(0)
+        if isinstance(yin, np.ndarray):
+            yin = yin.astype(np.float64)
+        yield z, to_device(yin, torch.float64)
+
+
 def _device_of(kernel):
     return torch.device("cuda", torch.cuda.current_device()) if kernel.device == "cuda" else torch.device("cpu")
 
@@ -170,8 +192,7 @@ def calc_zty(dataset, kernel, comm=None, ops=_cuda_ops):
             y_trans_y += y @ y
         comm.all_reduce_(z_trans_y, y_trans_y)
         return z_trans_y, float(y_trans_y[0])
-    for xin, yin, ldata in dataset.get_chunked_data():
-        z, y = kernel.transform_x_y(xin, yin, ldata)
+    for z, y in _transformed_xy_chunks(dataset, kernel):
         ops.zty_accum(z, y, z_trans_y)
         y_trans_y += y @ y
     comm.all_reduce_(z_trans_y, y_trans_y)
@@ -199,8 +220,7 @@ def calc_design_mat(dataset, kernel, comm=None, ops=_cuda_ops, gram="tc", gram_s
     m = kernel.get_num_rffs()
     z_trans_z, z_trans_y, y_trans_y = _new((m, m), dev), _new((m,), dev), _new((1,), dev)
     accumulate, finish = _gram_accumulator(ops, gram, gram_slices)
-    for xin, yin, ldata in dataset.get_chunked_data():
-        z, y = kernel.transform_x_y(xin, yin, ldata)
+    for z, y in _transformed_xy_chunks(dataset, kernel):
         ops.zty_accum(z, y, z_trans_y)
         accumulate(z, z_trans_z)
         y_trans_y += y @ y
@@ -235,8 +255,7 @@ def calc_var_design_mat(dataset, kernel, variance_rffs, comm=None, ops=_cuda_ops
     comm = comm or RowShardComm()
     z_trans_z = _new((variance_rffs, variance_rffs), _device_of(kernel))
     accumulate, finish = _gram_accumulator(ops, gram, gram_slices)
-    for xdata, ldata in dataset.get_chunked_x_data():
-        z = kernel.transform_x(xdata, ldata)
+    for z in _transformed_chunks(dataset, kernel):
         accumulate(z[:, :variance_rffs].contiguous(), z_trans_z)
     finish(z_trans_z)
     comm.all_reduce_(z_trans_z)
@@ -417,8 +436,7 @@ def _single_pass_srht_zty(dataset, kernel, compressor, acc_results, z_trans_y, o
     The sketch product runs on the tensor cores (exact-int8 planes, fp64-level error) when the provider has it."""
     y_trans_y = _new((1,), acc_results.device)
     atb = getattr(ops, "atb_accum_tc", None) or ops.atb_accum
-    for xin, yin, ldata in dataset.get_chunked_data():
-        z, y = kernel.transform_x_y(xin, yin, ldata)
+    for z, y in _transformed_xy_chunks(dataset, kernel):
         ops.zty_accum(z, y, z_trans_y)
         y_trans_y += y @ y
         atb(compressor.transform_x(z), z, acc_results)
@@ -587,10 +605,15 @@ def predict(kernel, weights, input_x, sequence_lengths=None, chunk_size=2000, tr
     """xgp_regression.py:105-134: (Z * w).sum(1), de-standardised; optional exact variance (:120-126)."""
     preds, pvar = [], []
     lambda_ = kernel.get_lambda()
-    for i in range(0, input_x.shape[0], chunk_size):
-        cutoff = min(i + chunk_size, input_x.shape[0])
-        sl = None if sequence_lengths is None else sequence_lengths[i:cutoff]
-        z = kernel.transform_x(input_x[i:cutoff, ...], sl)
+    def chunks():
+        for i in range(0, input_x.shape[0], chunk_size):
+            cutoff = min(i + chunk_size, input_x.shape[0])
+            yield input_x[i:cutoff, ...], None if sequence_lengths is None else sequence_lengths[i:cutoff]
+
+    stream = getattr(kernel, "transform_stream", None)
+    zs = stream(chunks()) if stream is not None and kernel.device == "cuda" else \
+        (kernel.transform_x(xc, sl) for xc, sl in chunks())
+    for z in zs:
         preds.append((z * weights[None, :]).sum(dim=1))
         if var is not None:
             zv = z[:, :variance_rffs]
