@@ -176,6 +176,17 @@ int xgpr_b200_atb_accum_tc_f64(const double* a, const double* z, int64_t n, int6
 int64_t xgpr_b200_ztzq_tc_workspace_bytes(int64_t n, int64_t m, int64_t r, int num_slices);
 int xgpr_b200_ztzq_accum_tc_f64(const double* z, int64_t n, int64_t m, const double* q, int64_t r, double* acc,
                                 int num_slices, int digit_bits, void* workspace, int64_t workspace_bytes, void* stream);
+/* Resident-feature CG matvec (no counterpart in the reference, which regenerates the chunk's features in every
+ * iteration: src/xGPR/fitting_toolkit/cg_tools.py:40-44).  A sine-cosine feature is double(c) * scale with c the float32
+ * cos / sin value (cpu/shared_fht_functions/shared_rfgen_ops.cpp:91-114), so the float32 matrix C is a lossless 4-byte
+ * encoding of Z that fits HBM (cfg2: 65.5 GB).
+ *   unscale_to_f32 : c[i] = float(z[i] / scale), exact for z produced by the feature generators
+ *   cres_zzv       : w (m) += Z^T (Z v) in ONE pass over C; vs = v * scale (vs[0] = v[0] when fit_intercept, whose
+ *                    column 0 is the constant 1); num_rffs m in {4096, 8192, 16384} (xgpr_b200_cres_zzv_supported) */
+int xgpr_b200_unscale_to_f32(const double* z, int64_t count, double scale, float* c, void* stream);
+int xgpr_b200_cres_zzv_supported(int64_t m);
+int xgpr_b200_cres_zzv_f32(const float* c, int64_t n, int64_t m, const double* vs, double* w, double scale,
+                           int fit_intercept, void* stream);
 /* acc (r, m) += A^T Z ;  A (n, r) row-major: the Nystrom sketch accumulation
  * `acc_results += compressor.transform_x(xdata).T @ xdata` (src/xGPR/preconditioners/rand_nys_constructors.py:119) */
 int xgpr_b200_atb_accum_f64(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc, void* stream);

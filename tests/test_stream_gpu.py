@@ -83,3 +83,56 @@ def test_cg_resident_z_equals_regenerated():
     z = torch.cat([kern.transform_x(c) for c, _ in ds.get_chunked_x_data()])
     ref = z.T @ (z @ vec) + kern.get_lambda() ** 2 * vec
     assert float((outs[0] - ref).abs().max()) <= 1e-11 * float(ref.abs().max())
+
+
+@pytest.mark.parametrize("m", [4096, 8192, 16384])
+@pytest.mark.parametrize("n,intercept", [(1, True), (3, False), (1000, True), (5001, True)])
+def test_resident_encoding_is_lossless_and_matvec_matches(m, n, intercept):
+    """float32 encoding C of sine-cosine features: double(C) * scale == Z bit for bit (the features ARE a float32 cos / sin
+    value times a constant, shared_rfgen_ops.cpp:91-114); the one-pass resident matvec equals Z^T (Z v) in float64."""
+    from xgpr_b200 import ext
+    from xgpr_b200.kernels import RBF
+    rng = np.random.default_rng(n + m)
+    x = rng.standard_normal((n, 20)).astype(np.float32)
+    kern = RBF(x.shape, m, random_seed=123, device="cuda")
+    kern.fit_intercept = intercept
+    kern.set_hyperparams(np.log(np.asarray([0.3, 0.25])), logspace=True)
+    assert kern.resident_ok()
+    z = kern.transform_x(x)
+    c = kern.resident_encode(z, torch.empty(z.shape, dtype=torch.float32, device="cuda"))
+    back = c.double() * kern.feature_scale()
+    if intercept:
+        assert torch.equal(back[:, 1:], z[:, 1:])
+    else:
+        assert torch.equal(back, z)
+    v = torch.from_numpy(rng.standard_normal(m)).cuda()
+    w = torch.ones(m, dtype=torch.float64, device="cuda")
+    kern.resident_zzv(c, v, w)
+    ref = z.T @ (z @ v) + 1.0
+    assert float((w - ref).abs().max()) <= 1e-12 * float(ref.abs().max()) * max(1, n) ** 0.5
+    assert not ext.cres_zzv_supported(2048) and not ext.cres_zzv_supported(32768)
+
+
+def test_cg_fit_resident_equals_fused():
+    """CG fit with the resident float32 encoding == CG fit with the fused regenerate-per-iteration kernels."""
+    from xgpr_b200 import fitting
+    from xgpr_b200.kernels import RBF
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal((6000, 30)).astype(np.float32)
+    y = np.sin(x[:, :4].sum(1)) + 0.1 * rng.standard_normal(6000)
+    ds = fitting.build_shard_dataset(x, y, None, chunk_size=2500)
+    kern = RBF(x.shape, 4096, random_seed=123, device="cuda")
+    kern.set_hyperparams(np.log(np.asarray([0.5, 0.2])), logspace=True)
+    pre = fitting.RandNysPreconditioner(kern, ds, 256, False, 123, "srht")
+    out = []
+    for keep in (True, False):
+        cg = fitting.ConjugateGrad()
+        cg.keep_resident = keep
+        resid = torch.zeros((4096, 2, 1), dtype=torch.float64, device="cuda")
+        resid[:, 0, :] = pre.get_zty()[:, None] / ds.get_ndatapoints()
+        wts, conv, niter, _ = cg.fit(ds, kern, pre, resid, 200, 1e-8, False)
+        assert conv
+        assert (cg._resident_c is not None and cg._resident_c[1] is not None) == keep
+        out.append((wts.clone(), niter))
+    assert abs(out[0][1] - out[1][1]) <= 1
+    assert float((out[0][0] - out[1][0]).abs().max()) <= 1e-7 * float(out[1][0].abs().max())

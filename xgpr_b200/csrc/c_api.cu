@@ -60,6 +60,10 @@ double tc_last_gemm_ms();
 int64_t atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int num_slices);
 int atb_accum_tc(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc, int num_slices,
                  int digit_bits, void* workspace, int64_t workspace_bytes, cudaStream_t st);
+int unscale_to_f32(const double* z, int64_t count, double scale, float* c, cudaStream_t st);
+int cres_zzv_supported(int64_t m);
+int cres_zzv(const float* c, int64_t n, int64_t m, const double* vs, double* w, double scale, int fit_intercept,
+             cudaStream_t st);
 int64_t ztzq_tc_workspace_bytes(int64_t n, int64_t m, int64_t r, int num_slices);
 int ztzq_accum_tc(const double* z, int64_t n, int64_t m, const double* q, int64_t r, double* acc, int num_slices,
                   int digit_bits, void* workspace, int64_t workspace_bytes, cudaStream_t st);
@@ -182,6 +186,14 @@ int64_t xgpr_b200_atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int nu
 int xgpr_b200_atb_accum_tc_f64(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc,
                                int num_slices, int digit_bits, void* workspace, int64_t workspace_bytes, void* s) {
     return atb_accum_tc(a, z, n, r, m, acc, num_slices, digit_bits, workspace, workspace_bytes, ST(s));
+}
+int xgpr_b200_unscale_to_f32(const double* z, int64_t count, double scale, float* c, void* s) {
+    return unscale_to_f32(z, count, scale, c, ST(s));
+}
+int xgpr_b200_cres_zzv_supported(int64_t m) { return cres_zzv_supported(m); }
+int xgpr_b200_cres_zzv_f32(const float* c, int64_t n, int64_t m, const double* vs, double* w, double scale,
+                           int fit_intercept, void* s) {
+    return cres_zzv(c, n, m, vs, w, scale, fit_intercept, ST(s));
 }
 int64_t xgpr_b200_ztzq_tc_workspace_bytes(int64_t n, int64_t m, int64_t r, int num_slices) {
     return ztzq_tc_workspace_bytes(n, m, r, num_slices);

@@ -149,6 +149,32 @@ def rbf_zzv(inputArr, radem, chiArr, fitIntercept, v, w):
         int(bool(fitIntercept)), v.data_ptr(), w.data_ptr(), _stream()))
 
 
+def unscale_to_f32(z, scale, out):
+    """out (float32, same shape) = float(z / scale): the lossless 4-byte encoding of sine-cosine features."""
+    z = _dev(z, "z", (torch.float64,), 2)
+    out = _dev(out, "out", (torch.float32,), 2)
+    if out.shape != z.shape:
+        raise RuntimeError("wrong array sizes")
+    check(lib.xgpr_b200_unscale_to_f32(z.data_ptr(), z.numel(), float(scale), out.data_ptr(), _stream()))
+    return out
+
+
+def cres_zzv_supported(num_rffs):
+    return bool(lib.xgpr_b200_cres_zzv_supported(int(num_rffs)))
+
+
+def cres_zzv(c, vs, w, scale, fitIntercept):
+    """w (m) += Z^T (Z v) in one pass over the resident float32 encoding c of Z (Z = double(c) * scale, column 0 = 1 when
+    fitIntercept); vs = v * scale with vs[0] = v[0] when fitIntercept."""
+    c = _dev(c, "c", (torch.float32,), 2)
+    vs = _dev(vs, "vs", (torch.float64,), 1)
+    w = _dev(w, "w", (torch.float64,), 1)
+    if vs.shape[0] != c.shape[1] or w.shape[0] != c.shape[1]:
+        raise RuntimeError("wrong array sizes")
+    check(lib.xgpr_b200_cres_zzv_f32(c.data_ptr(), c.shape[0], c.shape[1], vs.data_ptr(), w.data_ptr(), float(scale),
+                                     int(bool(fitIntercept)), _stream()))
+
+
 def cudaRBFGrad(inputArr, outputArr, gradArr, radem, chiArr, sigma, fitIntercept):
     x = _dev(inputArr, "inputArr", _SFX, 2)
     o = _dev(outputArr, "outputArr", (torch.float64,), 2)

@@ -170,6 +170,12 @@ def _transformed_xy_chunks(dataset, kernel):
         yield z, to_device(yin, torch.float64)
 
 
+def _available_hbm(dev):
+    """Bytes a new allocation can use: free device memory plus what torch's caching allocator holds but is not using."""
+    free, _ = torch.cuda.mem_get_info(dev)
+    return free + torch.cuda.memory_reserved(dev) - torch.cuda.memory_allocated(dev)
+
+
 def _device_of(kernel):
     return torch.device("cuda", torch.cuda.current_device()) if kernel.device == "cuda" else torch.device("cpu")
 
@@ -279,6 +285,7 @@ class ConjugateGrad:
         self._scratch = None
         self._staged = None
         self._resident = None
+        self._resident_c = None
         self.keep_resident = True
         self.one_pass = True
 
@@ -314,6 +321,12 @@ class ConjugateGrad:
         if _fused_ok(kernel, self.ops) and vec.shape[1] == 1:
             # one right-hand side: two fused feature passes per block, Z never written to HBM
             v1, w1 = vec[:, 0].contiguous(), matvec[:, 0]
+            resident = self._resident_encoding(dataset, kernel)
+            if resident is not None:             # one pass over the float32 encoding of Z kept in HBM
+                kernel.resident_zzv(resident, v1, w1)
+                self.comm.all_reduce_(matvec)
+                matvec.add_(vec, alpha=kernel.get_lambda() ** 2)
+                return
             one_pass = self.one_pass and getattr(kernel, "fused_zzv_ok", lambda: False)()
             for xs, t in self._staged_blocks(dataset, kernel):
                 if one_pass:                     # t = z . v reduced on chip: one SORF per frequency per iteration
@@ -333,6 +346,33 @@ class ConjugateGrad:
         self.comm.all_reduce_(matvec)
         matvec.add_(vec, alpha=kernel.get_lambda() ** 2)
 
+    def _resident_encoding(self, dataset, kernel, fraction=0.6, piece=65536):
+        """The shard's features as ONE resident float32 matrix C (Z = double(C) * scale exactly; 4 M bytes per row: cfg2's
+        1M x 16,384 = 65.5 GB), built once per solve when the kernel supports it and C plus one fp64 staging piece fit in
+        `fraction` of the free HBM; None otherwise (the fused regenerate-per-iteration kernels are used instead)."""
+        if not self.keep_resident or not getattr(kernel, "resident_ok", lambda: False)():
+            return None
+        key = (id(dataset), id(kernel), tuple(np.asarray(kernel.get_hyperparams(logspace=False)).tolist()))
+        if self._resident_c is not None and self._resident_c[0] == key:
+            return self._resident_c[1]
+        self._resident_c = None
+        dev = _device_of(kernel)
+        rows, m = dataset.get_local_ndatapoints(), kernel.get_num_rffs()
+        free = _available_hbm(dev)
+        if rows * m * 4 + min(piece, rows) * m * 8 > fraction * free:
+            self._resident_c = (key, None)
+            return None
+        c = torch.empty((rows, m), dtype=torch.float32, device=dev)
+        lo = 0
+        for xdata, ldata in dataset.get_chunked_x_data():
+            for p0 in range(0, xdata.shape[0], piece):
+                z = kernel.transform_x(xdata[p0:p0 + piece], None if ldata is None else ldata[p0:p0 + piece])
+                kernel.resident_encode(z, c[lo:lo + z.shape[0]])
+                lo += z.shape[0]
+                del z
+        self._resident_c = (key, c)
+        return c
+
     def _feature_chunks(self, dataset, kernel, fraction=0.5):
         """The shard's feature chunks for the materialised (multi-RHS) matvec.  Z does not change during a solve, so when
         the whole shard's Z (8 M bytes per row) fits in `fraction` of the free HBM it is generated ONCE and kept resident
@@ -347,8 +387,7 @@ class ConjugateGrad:
         keep = None
         if self.keep_resident and dev.type == "cuda":
             rows = dataset.get_local_ndatapoints()
-            free, _ = torch.cuda.mem_get_info(dev)
-            if rows * kernel.get_num_rffs() * 8 <= fraction * free:
+            if rows * kernel.get_num_rffs() * 8 <= fraction * _available_hbm(dev):
                 keep = []
         for z in _transformed_chunks(dataset, kernel):
             if keep is not None:

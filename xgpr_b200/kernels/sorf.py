@@ -77,6 +77,28 @@ class SORFKernelBaseclass(KernelBaseclass):
         """w += Z^T (Z v) in one pass (t reduced on chip); only when fused_zzv_ok()."""
         ext.rbf_zzv(xs, self.radem_diag, self.chi_arr, self.fit_intercept, v, w)
 
+    # ---- resident float32 encoding of Z for the CG matvec (xgpr_b200 extension; see csrc/resident_matvec_kernels.cu)
+    def feature_scale(self):
+        """The constant the feature generators multiply cos / sin by (rbf_ops.cpp:64-69), as the kernels round it."""
+        f = float(self.num_freqs)
+        s = np.sqrt(1.0 / (f - 0.5)) if self.fit_intercept else np.sqrt(1.0 / f)
+        return float(s if self.double_precision else np.float32(s))
+
+    def resident_ok(self):
+        return (not self.double_precision) and ext.cres_zzv_supported(self.num_rffs)
+
+    def resident_encode(self, z, out):
+        """out (float32) <- the unscaled cos / sin values of the feature chunk z: lossless, since z = double(c) * scale."""
+        return ext.unscale_to_f32(z, self.feature_scale(), out)
+
+    def resident_zzv(self, c, v, w):
+        """w += Z^T (Z v) from the resident encoding c, one pass."""
+        scale = self.feature_scale()
+        vs = v * scale
+        if self.fit_intercept:
+            vs[0] = v[0]
+        ext.cres_zzv(c, vs, w, scale, self.fit_intercept)
+
     def kernel_specific_gradient(self, input_x, sequence_length=None):
         output_x = torch.empty((input_x.shape[0], self.num_rffs), dtype=torch.float64, device=input_x.device)
         dz_dsigma = torch.empty((input_x.shape[0], self.num_rffs, 1), dtype=torch.float64, device=input_x.device)
