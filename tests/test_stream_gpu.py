@@ -136,3 +136,34 @@ def test_cg_fit_resident_equals_fused():
         out.append((wts.clone(), niter))
     assert abs(out[0][1] - out[1][1]) <= 1
     assert float((out[0][0] - out[1][0]).abs().max()) <= 1e-7 * float(out[1][0].abs().max())
+
+
+def test_resident_matvec_special_values():
+    """Zeros, denormals and extreme normals in the float32 encoding behave exactly as float64(c); all-zero rows (and the
+    kernel's own zero padding rows) contribute exactly nothing; a NaN feature poisons the result as in `Z.T @ (Z @ v)`."""
+    from xgpr_b200 import ext
+    n, m = 37, 4096
+    g = torch.Generator(device="cuda")
+    g.manual_seed(9)
+    c = torch.rand((n, m), generator=g, device="cuda", dtype=torch.float32) * 2 - 1
+    c[3] = 0.0                                                    # an all-zero row
+    c[5, ::3] = 0.0
+    c[7, ::2] = 1e-41                                             # denormals
+    c[8, 1::2] = -3e-39
+    c[9, 5] = torch.finfo(torch.float32).tiny                     # smallest normal
+    c[10, 6] = -torch.finfo(torch.float32).max
+    v = torch.randn(m, generator=g, device="cuda", dtype=torch.float64)
+    scale = 0.0221
+    z = c.double() * scale
+    ref = z.T @ (z @ v)
+    w = torch.zeros(m, dtype=torch.float64, device="cuda")
+    ext.cres_zzv(c, v * scale, w, scale, False)
+    assert float((w - ref).abs().max()) <= 1e-13 * float(ref.abs().max())
+    # rows of zeros contribute exactly nothing: a matrix of zeros leaves w untouched, bit for bit
+    w2 = torch.full((m,), 0.5, dtype=torch.float64, device="cuda")
+    ext.cres_zzv(torch.zeros((n, m), dtype=torch.float32, device="cuda"), v, w2, scale, False)
+    assert torch.equal(w2, torch.full_like(w2, 0.5))
+    c[11, 100] = float("nan")
+    w3 = torch.zeros(m, dtype=torch.float64, device="cuda")
+    ext.cres_zzv(c, v * scale, w3, scale, False)
+    assert bool(torch.isnan(w3).all())

@@ -9,9 +9,13 @@
 //     scale * v and of the fp64 accumulators in registers (EPT columns per thread, 512 threads);
 //   * rows arrive through a 3-stage cp.async ring in which every thread copies exactly the 16-byte pieces it will read
 //     itself (thread-private staging: no block barrier around the ring);
-//   * per step of 2 rows: partial dots -> warp shuffle -> shared memory -> the peer CTA's shared memory (DSMEM) ->
-//     one cluster barrier -> t = z . v for both rows -> acc += t * double(c) from the same staged values.
-// Bound: HBM (4 bytes per feature per iteration) with the XU pipe close behind (two F2F.F64.F32 per feature).
+//   * per batch of 4 rows (16,384 RFFs; 8 / 16 rows at 8,192 / 4,096): partial dots -> warp reduce-scatter -> shared
+//     memory -> warp 0 -> the peer CTA's shared memory (DSMEM) -> one cluster barrier -> t = z . v for the batch's rows
+//     -> acc += t * double(c) from the same staged values.  The barrier chain costs ~1 us whatever the batch, hence
+//     batches as long as the ring allows (two of its three stages; the third is in flight).
+// Bound: the MIO queue -- two F2F.F64.F32 (XU, 16 lanes/clk/SM), two LDS and one LDGSTS per feature, ~0.22 clk per
+// feature per SM = 5 TB/s of C, against 6.5 TB/s of HBM.  (Measured dead end: widening on the integer pipe instead of F2F
+// costs ~7 ALU instructions per value and is slower, 4.0 TB/s.)
 // The intercept column (Z[:, 0] = 1, not representable as c * scale) is handled by value: its owner substitutes 1 and
 // the host passes v[0] unscaled; the epilogue leaves that accumulator unscaled.
 #include "common.cuh"
@@ -22,8 +26,9 @@ namespace cg = cooperative_groups;
 namespace xb {
 
 constexpr int CR_THREADS = 512;
-constexpr int CR_ROWS = 2;           // rows per step
 constexpr int CR_STAGES = 3;
+// rows per batch (one cluster barrier each): 192 KB of ring = 3 stages of half a batch
+__host__ __device__ constexpr int cr_batch_rows(int ept) { return 64 / ept; }
 
 __device__ __forceinline__ void cr_cp16(void* smem, const void* gmem, bool valid) {
     const unsigned dst = (unsigned)__cvta_generic_to_shared(smem);
@@ -48,11 +53,15 @@ cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict
                 double scale, int fit_intercept, int64_t rows_per_cluster) {
     constexpr int HC = CR_THREADS * EPT;                 // columns per CTA; m = 2 * HC
     constexpr int PCS = EPT / 4;                         // 16-byte pieces per thread per row
+    constexpr int RB = cr_batch_rows(EPT);               // rows per batch = per cluster barrier
+    constexpr int SR = RB / 2;                           // rows per ring stage (a batch is two stages)
+    constexpr int LOG_RB = RB == 4 ? 2 : (RB == 8 ? 3 : 4);
+    constexpr int WARPS = CR_THREADS / 32;
     extern __shared__ __align__(16) unsigned char cr_smem[];
-    float* ring = reinterpret_cast<float*>(cr_smem);                                  // STAGES x ROWS x HC
-    double* wpart = reinterpret_cast<double*>(ring + CR_STAGES * CR_ROWS * HC);       // [2][ROWS][16 warps]
-    double* own = wpart + 2 * CR_ROWS * (CR_THREADS / 32);                            // [2][ROWS]
-    double* peer = own + 2 * CR_ROWS;                                                 // [2][ROWS], written by the peer CTA
+    float* ring = reinterpret_cast<float*>(cr_smem);                                  // STAGES x SR x HC
+    double* wpart = reinterpret_cast<double*>(ring + CR_STAGES * SR * HC);            // [2][RB][WARPS]
+    double* own = wpart + 2 * RB * WARPS;                                             // [2][RB]
+    double* peer = own + 2 * RB;                                                      // [2][RB], written by the peer CTA
 
     cg::cluster_group cluster = cg::this_cluster();
     const unsigned crank = cluster.block_rank();
@@ -63,7 +72,7 @@ cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict
     const int64_t cl = blockIdx.x >> 1;
     const int64_t row_beg = cl * rows_per_cluster;
     const int64_t row_end = (row_beg + rows_per_cluster < n) ? row_beg + rows_per_cluster : n;
-    const int64_t steps = (row_end > row_beg) ? (row_end - row_beg + CR_ROWS - 1) / CR_ROWS : 0;
+    const int64_t batches = (row_end > row_beg) ? (row_end - row_beg + RB - 1) / RB : 0;
     const bool icpt = fit_intercept && crank == 0 && tid == 0;      // owns global column 0 (piece 0, element 0)
 
     double v[EPT], acc[EPT];
@@ -75,39 +84,37 @@ cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict
             acc[4 * k + i] = 0.0;
         }
 
-    auto issue = [&](int64_t s) {
-        float* st = ring + (s % CR_STAGES) * CR_ROWS * HC;
+    // stage g holds rows [row_beg + g * SR, + SR); every thread copies exactly the pieces it reads itself
+    auto issue = [&](int64_t g) {
+        float* st = ring + (g % CR_STAGES) * SR * HC;
 #pragma unroll
-        for (int r = 0; r < CR_ROWS; ++r) {
-            const int64_t row = row_beg + s * CR_ROWS + r;
-            const bool ok = s < steps && row < row_end;
+        for (int r = 0; r < SR; ++r) {
+            const int64_t row = row_beg + g * SR + r;
+            const bool ok = row < row_end;
             const float* src = c + (ok ? row : 0) * m + col0 + 4 * tid;
 #pragma unroll
             for (int k = 0; k < PCS; ++k)
                 cr_cp16(st + r * HC + 4 * tid + k * 4 * CR_THREADS, src + k * 4 * CR_THREADS, ok);
         }
+        cr_commit();
     };
     issue(0);
-    cr_commit();
     issue(1);
-    cr_commit();
-    for (int64_t s = 0; s < steps; ++s) {
-        issue(s + 2);
-        cr_commit();
-        cr_wait<2>();                                    // this thread's pieces of step s have landed
-        const float* st = ring + (s % CR_STAGES) * CR_ROWS * HC + 4 * tid;
-        const int par = (int)(s & 1);
-        double dot[CR_ROWS];
-        bool one[CR_ROWS];                               // intercept owner: the row exists (padding rows stay zero)
+    issue(2);
+    for (int64_t b = 0; b < batches; ++b) {
+        cr_wait<1>();                                    // stages 2b and 2b+1 have landed; 2b+2 stays in flight
+        const int par = (int)(b & 1);
+        const int64_t brow = row_beg + b * RB;
+        double dot[RB];
 #pragma unroll
-        for (int r = 0; r < CR_ROWS; ++r) one[r] = icpt && (row_beg + s * CR_ROWS + r < row_end);
-#pragma unroll
-        for (int r = 0; r < CR_ROWS; ++r) {
+        for (int r = 0; r < RB; ++r) {
+            const float* st = ring + ((2 * b + r / SR) % CR_STAGES) * SR * HC + (r % SR) * HC + 4 * tid;
+            const bool one = icpt && (brow + r < row_end);                    // padding rows stay zero
             double d0 = 0.0, d1 = 0.0;
 #pragma unroll
             for (int k = 0; k < PCS; ++k) {
-                float4 q = *reinterpret_cast<const float4*>(st + r * HC + k * 4 * CR_THREADS);
-                if (one[r] && k == 0) q.x = 1.0f;
+                float4 q = *reinterpret_cast<const float4*>(st + k * 4 * CR_THREADS);
+                if (one && k == 0) q.x = 1.0f;
                 d0 = fma((double)q.x, v[4 * k], d0);
                 d1 = fma((double)q.y, v[4 * k + 1], d1);
                 d0 = fma((double)q.z, v[4 * k + 2], d0);
@@ -115,42 +122,59 @@ cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict
             }
             dot[r] = d0 + d1;
         }
+        // warp reduce-scatter: after LOG_RB halvings lane l holds the partial of row l >> (5 - LOG_RB)
 #pragma unroll
-        for (int r = 0; r < CR_ROWS; ++r)
+        for (int lvl = 0; lvl < LOG_RB; ++lvl) {
+            const int o = 16 >> lvl, cnt = RB >> lvl;
+            const bool up = (lane & o) != 0;
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) dot[r] += __shfl_xor_sync(0xffffffffu, dot[r], o);
-        if (lane == 0) {
-#pragma unroll
-            for (int r = 0; r < CR_ROWS; ++r) wpart[(par * CR_ROWS + r) * (CR_THREADS / 32) + warp] = dot[r];
+            for (int i = 0; i < cnt / 2; ++i) {
+                const double send = up ? dot[i] : dot[i + cnt / 2];
+                const double keep = up ? dot[i + cnt / 2] : dot[i];
+                dot[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+            }
         }
+#pragma unroll
+        for (int o = 16 >> LOG_RB; o > 0; o >>= 1) dot[0] += __shfl_xor_sync(0xffffffffu, dot[0], o);
+        if ((lane & ((32 >> LOG_RB) - 1)) == 0) wpart[(par * RB + (lane >> (5 - LOG_RB))) * WARPS + warp] = dot[0];
         __syncthreads();
-        if (tid < CR_ROWS) {
+        if (warp == 0) {                                 // RB x WARPS partials -> RB totals, RB * WARPS / 32 per lane
+            constexpr int PER = RB * WARPS / 32;         // consecutive partials of one row
             double p = 0.0;
 #pragma unroll
-            for (int j = 0; j < CR_THREADS / 32; ++j) p += wpart[(par * CR_ROWS + tid) * (CR_THREADS / 32) + j];
-            own[par * CR_ROWS + tid] = p;
-            peer_remote[par * CR_ROWS + tid] = p;
+            for (int j = 0; j < PER; ++j) p += wpart[par * RB * WARPS + lane * PER + j];
+#pragma unroll
+            for (int o = WARPS / PER / 2; o > 0; o >>= 1) p += __shfl_xor_sync(0xffffffffu, p, o);
+            if ((lane & (WARPS / PER - 1)) == 0) {
+                const int r = lane / (WARPS / PER);
+                own[par * RB + r] = p;
+                peer_remote[par * RB + r] = p;
+            }
         }
         cluster.sync();                                  // both halves' partial dots are visible in both CTAs
 #pragma unroll
-        for (int r = 0; r < CR_ROWS; ++r) {
+        for (int r = 0; r < RB; ++r) {
             // rank 0's half is added first in both CTAs: the two halves of a row see the same t bit for bit
-            const double a = own[par * CR_ROWS + r], b = peer[par * CR_ROWS + r];
-            const double t = crank == 0 ? a + b : b + a;
+            const double a = own[par * RB + r], bb = peer[par * RB + r];
+            const double t = crank == 0 ? a + bb : bb + a;
+            const float* st = ring + ((2 * b + r / SR) % CR_STAGES) * SR * HC + (r % SR) * HC + 4 * tid;
+            const bool one = icpt && (brow + r < row_end);
 #pragma unroll
             for (int k = 0; k < PCS; ++k) {
-                float4 q = *reinterpret_cast<const float4*>(st + r * HC + k * 4 * CR_THREADS);
-                if (one[r] && k == 0) q.x = 1.0f;
+                float4 q = *reinterpret_cast<const float4*>(st + k * 4 * CR_THREADS);
+                if (one && k == 0) q.x = 1.0f;
                 acc[4 * k] = fma((double)q.x, t, acc[4 * k]);
                 acc[4 * k + 1] = fma((double)q.y, t, acc[4 * k + 1]);
                 acc[4 * k + 2] = fma((double)q.z, t, acc[4 * k + 2]);
                 acc[4 * k + 3] = fma((double)q.w, t, acc[4 * k + 3]);
             }
         }
+        issue(2 * b + 3);                                // into the two stages this batch has just finished with
+        issue(2 * b + 4);
     }
     cr_wait<0>();
     cluster.sync();                                      // no CTA exits while its peer may still write into it
-    if (steps > 0) {
+    if (batches > 0) {
 #pragma unroll
         for (int k = 0; k < PCS; ++k)
 #pragma unroll
@@ -176,7 +200,8 @@ template <int EPT>
 static int launch_cres(const float* c, int64_t n, const double* vs, double* w, double scale, int fit_intercept,
                        cudaStream_t st) {
     constexpr int HC = CR_THREADS * EPT;
-    constexpr int SMEM = CR_STAGES * CR_ROWS * HC * 4 + (2 * CR_ROWS * (CR_THREADS / 32) + 4 * CR_ROWS) * 8;
+    constexpr int RB = cr_batch_rows(EPT);
+    constexpr int SMEM = CR_STAGES * (RB / 2) * HC * 4 + (2 * RB * (CR_THREADS / 32) + 4 * RB) * 8;
     auto kern = cres_zzv_kernel<EPT>;
     static int clusters = 0;
     if (clusters == 0) {
@@ -198,9 +223,9 @@ static int launch_cres(const float* c, int64_t n, const double* vs, double* w, d
         clusters = nc;
     }
     int64_t nclusters = clusters;
-    if (nclusters * CR_ROWS > n) nclusters = (n + CR_ROWS - 1) / CR_ROWS;
+    if (nclusters * RB > n) nclusters = (n + RB - 1) / RB;
     int64_t rows_per = (n + nclusters - 1) / nclusters;
-    rows_per = ((rows_per + CR_ROWS - 1) / CR_ROWS) * CR_ROWS;
+    rows_per = ((rows_per + RB - 1) / RB) * RB;
     nclusters = (n + rows_per - 1) / rows_per;
     kern<<<(unsigned)(2 * nclusters), CR_THREADS, SMEM, st>>>(c, n, vs, w, scale, fit_intercept, rows_per);
     count_launch();
