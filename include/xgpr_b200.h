@@ -184,6 +184,11 @@ int xgpr_b200_ztzq_accum_tc_f64(const double* z, int64_t n, int64_t m, const dou
  *   cres_zzv       : w (m) += Z^T (Z v) in ONE pass over C; vs = v * scale (vs[0] = v[0] when fit_intercept, whose
  *                    column 0 is the constant 1); num_rffs m in {4096, 8192, 16384} (xgpr_b200_cres_zzv_supported) */
 int xgpr_b200_unscale_to_f32(const double* z, int64_t count, double scale, float* c, void* stream);
+/*   rbf_feature_gen_c32 : the encoding straight from the feature kernel -- c (n, num_rffs) float32 holds the cos / sin
+ *                    values rbfFeatureGen multiplies by its constant (same x, radem, chi arguments; x already scaled by
+ *                    sigma; column 0 holds cos of frequency 0, the consumer substitutes the intercept) */
+int xgpr_b200_rbf_feature_gen_c32(const float* x, int64_t n, int64_t d, float* c, int64_t num_rffs, const int8_t* radem,
+                                  int64_t radem_len, const float* chi, int64_t num_freqs, void* stream);
 int xgpr_b200_cres_zzv_supported(int64_t m);
 int xgpr_b200_cres_zzv_f32(const float* c, int64_t n, int64_t m, const double* vs, double* w, double scale,
                            int fit_intercept, void* stream);

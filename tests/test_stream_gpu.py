@@ -167,3 +167,18 @@ def test_resident_matvec_special_values():
     w3 = torch.zeros(m, dtype=torch.float64, device="cuda")
     ext.cres_zzv(c, v * scale, w3, scale, False)
     assert bool(torch.isnan(w3).all())
+
+
+@pytest.mark.parametrize("d,m", [(20, 4096), (64, 16384), (300, 8192)])
+def test_resident_generate_equals_encoded_transform(d, m):
+    """The feature kernel's float32 output mode writes exactly the values the fp64 features are made of."""
+    from xgpr_b200.kernels import RBF
+    rng = np.random.default_rng(d)
+    x = rng.standard_normal((777, d)).astype(np.float32)
+    kern = RBF(x.shape, m, random_seed=123, device="cuda")
+    kern.set_hyperparams(np.log(np.asarray([0.3, 0.25])), logspace=True)
+    z = kern.transform_x(x)
+    enc = kern.resident_encode(z, torch.empty(z.shape, dtype=torch.float32, device="cuda"))
+    direct = kern.resident_generate(x, torch.empty(z.shape, dtype=torch.float32, device="cuda"))
+    assert torch.equal(direct[:, 1:], enc[:, 1:])              # column 0 is the intercept, substituted by the consumer
+    assert torch.equal((direct.double() * kern.feature_scale())[:, 1:], z[:, 1:])

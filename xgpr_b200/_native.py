@@ -67,6 +67,9 @@ EXPORTED.append("xgpr_b200_atb_tc_workspace_bytes")
 lib.xgpr_b200_ztzq_tc_workspace_bytes.argtypes = [_i64, _i64, _i64, _int]
 lib.xgpr_b200_ztzq_tc_workspace_bytes.restype = _i64
 EXPORTED.append("xgpr_b200_ztzq_tc_workspace_bytes")
+lib.xgpr_b200_rbf_feature_gen_c32.argtypes = [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr]
+lib.xgpr_b200_rbf_feature_gen_c32.restype = _int
+EXPORTED.append("xgpr_b200_rbf_feature_gen_c32")
 lib.xgpr_b200_unscale_to_f32.argtypes = [_ptr, _i64, ctypes.c_double, _ptr, _ptr]
 lib.xgpr_b200_unscale_to_f32.restype = _int
 EXPORTED.append("xgpr_b200_unscale_to_f32")

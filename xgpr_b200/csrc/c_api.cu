@@ -60,6 +60,8 @@ double tc_last_gemm_ms();
 int64_t atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int num_slices);
 int atb_accum_tc(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc, int num_slices,
                  int digit_bits, void* workspace, int64_t workspace_bytes, cudaStream_t st);
+int rbf_c32_dispatch(const float* x, int64_t n, int64_t d, float* c, int64_t num_rffs, const int8_t* radem, int64_t R,
+                     const float* chi, int64_t F, cudaStream_t st);
 int unscale_to_f32(const double* z, int64_t count, double scale, float* c, cudaStream_t st);
 int cres_zzv_supported(int64_t m);
 int cres_zzv(const float* c, int64_t n, int64_t m, const double* vs, double* w, double scale, int fit_intercept,
@@ -186,6 +188,10 @@ int64_t xgpr_b200_atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int nu
 int xgpr_b200_atb_accum_tc_f64(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc,
                                int num_slices, int digit_bits, void* workspace, int64_t workspace_bytes, void* s) {
     return atb_accum_tc(a, z, n, r, m, acc, num_slices, digit_bits, workspace, workspace_bytes, ST(s));
+}
+int xgpr_b200_rbf_feature_gen_c32(const float* x, int64_t n, int64_t d, float* c, int64_t num_rffs, const int8_t* radem,
+                                  int64_t rl, const float* chi, int64_t nf, void* s) {
+    return rbf_c32_dispatch(x, n, d, c, num_rffs, radem, rl, chi, nf, ST(s));
 }
 int xgpr_b200_unscale_to_f32(const double* z, int64_t count, double scale, float* c, void* s) {
     return unscale_to_f32(z, count, scale, c, ST(s));

@@ -22,7 +22,9 @@ namespace xb {
 //   in registers and walks the CTA's rows; rows arrive through a double-buffered cp.async tile in shared
 //   memory (zero-padded, permuted), ITB row-iterations per batch, so no global-load latency sits on the
 //   per-row critical path.  The K sub-lanes of a slot write K*16 contiguous bytes per register index.
-template <typename T, int P, int E, bool GRAD, int WARPS>
+// C32 (float32 kernels only): write the UNSCALED float32 cos / sin values instead of the fp64 features -- the lossless
+// resident encoding Z = double(c) * scale consumed by resident_matvec_kernels.cu; `out` then points at float storage.
+template <typename T, int P, int E, bool GRAD, int WARPS, bool C32 = false>
 __global__ void __launch_bounds__(WARPS * 32)
 rbf_core_kernel(const T* __restrict__ x, double* __restrict__ out, double* __restrict__ grad,
                 const int8_t* __restrict__ radem, const T* __restrict__ chi,
@@ -110,6 +112,16 @@ rbf_core_kernel(const T* __restrict__ x, double* __restrict__ out, double* __res
                     a[i] = GRAD ? (T)((double)gv[i] * sigma) : gv[i];
                 }
                 sincos_group<CH>(a, sn, cs);
+                if constexpr (C32) {
+                    float2* frow = reinterpret_cast<float2*>(out) + (size_t)row * F + base + sub;
+                    if (ok) {
+#pragma unroll
+                        for (int i = 0; i < CH; ++i)
+                            if (full || base + sub + K * (r0 + i) < F)
+                                frow[K * (r0 + i)] = make_float2((float)cs[i], (float)sn[i]);
+                    }
+                    continue;
+                }
                 double2 o[CH], og[GRAD ? CH : 1];
 #pragma unroll
                 for (int i = 0; i < CH; ++i) {
@@ -216,7 +228,7 @@ __host__ __device__ constexpr int rbf_k(int p) {
     return cmin(32, (p / 16 > cmin(4, p / 2)) ? p / 16 : cmin(4, p / 2));
 }
 
-template <typename T, int P, bool GRAD>
+template <typename T, int P, bool GRAD, bool C32 = false>
 static int launch_core(const T* x, int64_t n, int64_t d, double* out, double* grad, const int8_t* radem,
                        int64_t R, const T* chi, int64_t F, double scale, double sigma, cudaStream_t st) {
     constexpr int K = rbf_k(P);
@@ -240,7 +252,7 @@ static int launch_core(const T* x, int64_t n, int64_t d, double* out, double* gr
     if (ITB < 1) ITB = 1;
     if (ITB > 8) ITB = 8;
     const size_t smem = 2 * ITB * row_bytes + (size_t)RC * K * CPITCH * sizeof(T);
-    auto kern = rbf_core_kernel<T, P, E, GRAD, WARPS>;
+    auto kern = rbf_core_kernel<T, P, E, GRAD, WARPS, C32>;
     if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     const T c = norm_constant<T>(P);
     const T fold = is_pow4(P) ? (T)(c * c * c) : T(1);
@@ -298,6 +310,30 @@ int rbf_dispatch(const T* x, int64_t n, int64_t d, double* out, double* grad, in
     }
 #undef XB_CASE
     return launch_cta<T, GRAD>(x, n, d, P, out, grad, radem, R, chi, F, scale, sigma, st);
+}
+
+// Resident encoding straight from the feature kernel: c (n, 2F) float32 = the cos / sin values rbf_dispatch would scale.
+int rbf_c32_dispatch(const float* x, int64_t n, int64_t d, float* c, int64_t num_rffs, const int8_t* radem, int64_t R,
+                     const float* chi, int64_t F, cudaStream_t st) {
+    XB_REQUIRE(n > 0 && d > 0, "no datapoints");
+    XB_REQUIRE(num_rffs >= 2 && (num_rffs & 1) == 0, "last dim of output must be even number");
+    XB_REQUIRE(2 * F == num_rffs && F <= R, "incorrect number of rffs and or freqs.");
+    const int64_t P = padded_width(d);
+    XB_REQUIRE(R % P == 0, "incorrect number of rffs and or freqs.");
+    XB_REQUIRE(P <= 1024, "resident encoding supports at most 1024 input features");
+    XB_REQUIRE(n < (1ll << 31) && F < (1ll << 30), "array too large");
+    XB_REQUIRE(x && c && radem && chi, "null pointer");
+    double* out = reinterpret_cast<double*>(c);
+#define XB_CASE(PP) \
+    case PP: return launch_core<float, PP, false, true>(x, n, d, out, nullptr, radem, R, chi, F, 1.0, 0.0, st);
+    switch (P) {
+        XB_CASE(2) XB_CASE(4) XB_CASE(8) XB_CASE(16) XB_CASE(32) XB_CASE(64)
+        XB_CASE(128) XB_CASE(256) XB_CASE(512) XB_CASE(1024)
+        default: break;
+    }
+#undef XB_CASE
+    set_error("resident encoding: unsupported padded width");
+    return XGPR_B200_EINVAL;
 }
 
 template int rbf_dispatch<float, false>(const float*, int64_t, int64_t, double*, double*, int64_t, const int8_t*,

@@ -149,6 +149,19 @@ def rbf_zzv(inputArr, radem, chiArr, fitIntercept, v, w):
         int(bool(fitIntercept)), v.data_ptr(), w.data_ptr(), _stream()))
 
 
+def cudaRBFFeatureGenC32(inputArr, outputArr, radem, chiArr):
+    """outputArr (float32, n x 2F) <- the unscaled cos / sin values of cudaRBFFeatureGen: the lossless resident encoding."""
+    x = _dev(inputArr, "inputArr", (torch.float32,), 2)
+    o = _dev(outputArr, "outputArr", (torch.float32,), 2)
+    r = _radem3(radem)
+    c = _dev(chiArr, "chiArr", (torch.float32,), 1)
+    if o.shape[0] != x.shape[0]:
+        raise RuntimeError("no datapoints")
+    check(lib.xgpr_b200_rbf_feature_gen_c32(x.data_ptr(), x.shape[0], x.shape[1], o.data_ptr(), o.shape[1],
+                                            r.data_ptr(), r.shape[2], c.data_ptr(), c.shape[0], _stream()))
+    return 0
+
+
 def unscale_to_f32(z, scale, out):
     """out (float32, same shape) = float(z / scale): the lossless 4-byte encoding of sine-cosine features."""
     z = _dev(z, "z", (torch.float64,), 2)

@@ -364,7 +364,12 @@ class ConjugateGrad:
             return None
         c = torch.empty((rows, m), dtype=torch.float32, device=dev)
         lo = 0
+        direct = getattr(kernel, "resident_generate", None) if kernel.get_xdim()[-1] <= 1024 else None
         for xdata, ldata in dataset.get_chunked_x_data():
+            if direct is not None:               # the feature kernel writes the float32 values itself
+                direct(xdata, c[lo:lo + xdata.shape[0]])
+                lo += xdata.shape[0]
+                continue
             for p0 in range(0, xdata.shape[0], piece):
                 z = kernel.transform_x(xdata[p0:p0 + piece], None if ldata is None else ldata[p0:p0 + piece])
                 kernel.resident_encode(z, c[lo:lo + z.shape[0]])

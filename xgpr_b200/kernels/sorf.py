@@ -91,6 +91,14 @@ class SORFKernelBaseclass(KernelBaseclass):
         """out (float32) <- the unscaled cos / sin values of the feature chunk z: lossless, since z = double(c) * scale."""
         return ext.unscale_to_f32(z, self.feature_scale(), out)
 
+    def resident_generate(self, input_x, out):
+        """out (float32, rows x num_rffs) <- the encoding of transform_x(input_x), straight from the feature kernel (no
+        fp64 round trip).  Same staging and sigma scaling as transform_x."""
+        xin = self._stage_input(input_x)
+        ext.scale_input_(xin, float(self.hyperparams[1]))
+        ext.cudaRBFFeatureGenC32(xin, out, self.radem_diag, self.chi_arr)
+        return out
+
     def resident_zzv(self, c, v, w):
         """w += Z^T (Z v) from the resident encoding c, one pass."""
         scale = self.feature_scale()
