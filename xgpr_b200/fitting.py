@@ -362,7 +362,11 @@ class ConjugateGrad:
         if rows * m * 4 + min(piece, rows) * m * 8 > fraction * free:
             self._resident_c = (key, None)
             return None
-        c = torch.empty((rows, m), dtype=torch.float32, device=dev)
+        try:
+            c = torch.empty((rows, m), dtype=torch.float32, device=dev)
+        except torch.cuda.OutOfMemoryError:      # fragmented pool: keep the fused regenerate-per-iteration path
+            self._resident_c = (key, None)
+            return None
         lo = 0
         direct = getattr(kernel, "resident_generate", None) if kernel.get_xdim()[-1] <= 1024 else None
         for xdata, ldata in dataset.get_chunked_x_data():
