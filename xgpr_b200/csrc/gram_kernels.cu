@@ -792,7 +792,11 @@ int cg_matvec_accum(const double* z, int64_t n, int64_t m, const double* v, int6
         // default: fp64 tensor-core kernels (4 CTAs per SM); XGPR_B200_MATVEC_DFMA selects the v2 DFMA kernels
         static const bool dfma = getenv("XGPR_B200_MATVEC_DFMA") != nullptr;
         constexpr int ZV16 = 2 * m2_zv_stage(16) * 8, ZT16 = 2 * m2_zt_stage(16) * 8;
-        static bool attr_done = false;
+        // function attributes are per device: one flag per device ordinal (one process may drive several GPUs)
+        static bool attr_done_dev[64] = {};
+        int dev_id = 0;
+        cudaGetDevice(&dev_id);
+        bool& attr_done = attr_done_dev[dev_id & 63];
         if (!attr_done) {
             cudaFuncSetAttribute(zv_tile2_kernel<16, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ZV16);
             cudaFuncSetAttribute(ztt_tile2_kernel<16, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ZT16);

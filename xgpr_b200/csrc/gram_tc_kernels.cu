@@ -585,7 +585,10 @@ static int tc_prepare_operand(TcOperand& op, uint8_t* ws, const double* z, int64
 }
 
 static int tc_setup(int& sms) {
-    static int smem_set = 0;
+    static int smem_set_dev[64] = {};                    // function attributes are per device
+    int dev_id = 0;
+    cudaGetDevice(&dev_id);
+    int& smem_set = smem_set_dev[dev_id & 63];
     if (!smem_set) {
         if (cudaFuncSetAttribute(tc_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES) != cudaSuccess)
             return check_launch("tc_gram_kernel smem attribute");

@@ -203,7 +203,10 @@ static int launch_cres(const float* c, int64_t n, const double* vs, double* w, d
     constexpr int RB = cr_batch_rows(EPT);
     constexpr int SMEM = CR_STAGES * (RB / 2) * HC * 4 + (2 * RB * (CR_THREADS / 32) + 4 * RB) * 8;
     auto kern = cres_zzv_kernel<EPT>;
-    static int clusters = 0;
+    static int clusters_dev[64] = {};                    // attribute + occupancy are per device
+    int dev_id = 0;
+    cudaGetDevice(&dev_id);
+    int& clusters = clusters_dev[dev_id & 63];
     if (clusters == 0) {
         if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess)
             return check_launch("cres_zzv_kernel smem attribute");
