@@ -6,13 +6,20 @@ Metric : RFF feature rows/s @ 16384 RFFs, RBF kernel (configs[1]: 64 input featu
 Step   : one pass of the fused SORF+RBF kernel over one chunk of ``--rows`` synthetic rows
          (output chunk = rows x 131,072 B  >>  126 MB L2, so every step streams through HBM).
 value  : whole-job rows/s with the chunk resident in HBM (all ranks; rows shard, no collective).
-e2e    : the same metric through the kernel-plugin call ``RBF.transform_stream(host chunks)`` -- host
-         (pinned) input, H2D inside the timed region, and a D2H read of the chunk's first feature row.
+e2e    : the same metric through the repo's consumer pass ``fitting.calc_zty(dataset, kernel)`` on a HOST-resident
+         (pinned) dataset: every step copies its rows (x and y) host->device inside the timed region, generates the
+         features of every row (fused featurise -> Z^T y, Z never written) and reads the M-vector Z^T y back to the host.
+         ``e2e.materialised`` is the same pass with Z written and re-read (transform_stream + zty_accum).
 roofline: achieved algorithmic GB/s of the feature kernel (CUDA events around each launch) / measured
          HBM copy bandwidth (MEASURED_PEAKS.json).
 cpu_baseline: the reference's own CPU extension (oracle/_ref, OpenMP) on a bounded sample, rank 0, N=1.
 
-``--impl reference`` times the reference CPU extension itself (same config / metric / unit).
+also   : the metric's second kernel, Conv1dRBF @16384 RFFs, with its own roofline (fp32 issue), cpu_baseline and e2e.
+fit    : the strong-scaling workload (cfg2: 1M x 64, 16384 RFFs, rank-512 srht preconditioner + CG to 1e-6), the SAME
+         global dataset at every N, rows sharded, fp64 NCCL all-reduces in the timed region; weights compared with the
+         committed N = 1 weight vector (tests/golden/cfg2_fit_w_n1.npy).
+
+``--impl reference`` times the reference CPU extension itself (same config / metric / unit), all host threads.
 """
 import argparse
 import json
@@ -43,14 +50,41 @@ def parse():
     ap.add_argument("--rows", type=int, default=262144, help="rows per step per GPU")
     ap.add_argument("--cpu-rows", type=int, default=16384, help="rows per CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--fit-rows", type=int, default=1000000, help="GLOBAL rows of the strong-scaling fit (0 = skip)")
+    ap.add_argument("--fit-rank", type=int, default=512)
+    ap.add_argument("--save-fit-weights", action="store_true", help="N=1 only: (re)write tests/golden/cfg2_fit_w_n1.npy")
+    ap.add_argument("--no-gram", action="store_true")
+    ap.add_argument("--no-conv", action="store_true")
     return ap.parse_args()
 
 
+class HostParams:
+    """Host-drawn SORF parameters, the recipe of SORFKernelBaseclass (sorf_kernel_baseclass.py:71-84 /
+    conv_kernel_baseclass.py:85-99) restated with NumPy / SciPy only, so that the reference arm never imports (or maps the
+    native library of) the package under test."""
+
+    def __init__(self, width, num_rffs, seed=123):
+        from scipy.stats import chi
+        p = 2
+        while p < width:
+            p *= 2
+        f = num_rffs // 2
+        reps = -(-f // p) if p < f else 1
+        rng = np.random.default_rng(seed)
+        self.radem_diag = rng.choice(np.asarray([-1, 1], dtype=np.int8), size=(3, 1, reps * p), replace=True)
+        self.chi_arr = chi.rvs(df=p, size=f, random_state=seed).astype(np.float32)
+
+
 def draw_params():
-    """Host-drawn SORF parameters exactly as SORFKernelBaseclass does (sorf_kernel_baseclass.py:71-84)."""
-    from xgpr_b200.kernels import RBF
-    k = RBF((1, D_IN), NUM_RFFS, random_seed=123, device="cpu")
-    return k
+    return HostParams(D_IN, NUM_RFFS)
+
+
+def use_all_host_threads():
+    """torch.distributed.run exports OMP_NUM_THREADS=1 to its workers; the CPU baseline must use every core at every N.
+    Must run before the OpenMP runtime of the reference extension is loaded."""
+    n = os.cpu_count() or 1
+    os.environ["OMP_NUM_THREADS"] = str(n)
+    return n
 
 
 def peaks():
@@ -130,12 +164,18 @@ class ClockSampler(threading.Thread):
 
 
 def ref_ext():
+    n = use_all_host_threads()
     sys.path.insert(0, os.path.join(ROOT, "oracle", "_ref"))
     try:
         import xgpr_cpu_rfgen_cpp_ext as ext
-        return ext
     except ImportError:
         return None
+    try:                                     # the runtime may have been initialised (with 1 thread) before we got here
+        import ctypes
+        ctypes.CDLL("libgomp.so.1").omp_set_num_threads(int(n))
+    except Exception:
+        pass
+    return ext
 
 
 def cpu_rows_per_s(kern, rows, min_seconds=10.0, max_reps=50):
@@ -222,7 +262,8 @@ def run_reference(args):
 def run_b200(args):
     import torch
     import torch.distributed as dist
-    from xgpr_b200 import ext
+    from xgpr_b200 import ext, fitting
+    from xgpr_b200.kernels import RBF
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -234,17 +275,19 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    kern = draw_params()
-    kern.device = "cuda"
+    kern = RBF((1, D_IN), NUM_RFFS, random_seed=123, device="cuda")
     kern.set_hyperparams(np.asarray([np.log(np.sqrt(0.0767)), np.log(SIGMA)]), logspace=True)
 
     rows = args.rows
     rng = np.random.default_rng(123 + rank)
     x_host_np = rng.standard_normal((rows, D_IN)).astype(np.float32)
+    y_host_np = np.sin(x_host_np[:, :8].sum(1)) + 0.1 * rng.standard_normal(rows)
     x_pinned = torch.from_numpy(x_host_np).pin_memory()
+    y_pinned = torch.from_numpy(y_host_np).pin_memory()
     x_dev = torch.from_numpy((x_host_np * np.float32(SIGMA)).astype(np.float32)).to(dev)
     out = torch.empty((rows, NUM_RFFS), dtype=torch.float64, device=dev)
     radem, chi = kern.radem_diag, kern.chi_arr
+    steps, warm = args.steps, max(args.warmup, 3)
 
     def barrier():
         if world > 1:
@@ -254,14 +297,14 @@ def run_b200(args):
         ext.cudaRBFFeatureGen(x_dev, out, radem, chi, True)
 
     # ---------------- device-resident throughput (value) + per-launch kernel time (roofline)
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(warm):
         kernel_step()
     torch.cuda.synchronize()
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
     l0 = ext.launch_count()
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
@@ -275,41 +318,61 @@ def run_b200(args):
     launches = ext.launch_count() - l0
     kern_ms = [a.elapsed_time(b) for a, b in evs]
     dev_ms = evs[0][0].elapsed_time(evs[-1][1])
-    # ---------------- end to end through the plugin API (host input, H2D, D2H of a result row)
-    # The plugin's streaming call: every step copies its chunk from pinned host memory (H2D inside the timed region, issued
-    # on a side stream one chunk ahead), scales it, runs the fused kernel, sets the intercept column, and the loop reads
-    # the step's first feature row back to the host (131 KB, a synchronising D2H) before taking the next chunk.
+
+    # ---------------- end to end: the consumer pass on a host-resident dataset (see module docstring)
+    # One step = fitting.calc_zty over `rows` pinned host rows in 4 chunks: x (and y) of chunk i+1 are copied host->device
+    # on the side stream while chunk i runs the fused featurise -> Z^T y kernel; the step ends with the D2H of Z^T y.
+    ds_host = fitting.ShardDataset(x_pinned, y_pinned, None, chunk_size=rows // 4)
+
     def e2e_steps(k):
-        for z in kern.transform_stream((x_pinned, None) for _ in range(k)):
-            z[0].cpu()
+        for _ in range(k):
+            zty, _ = fitting.calc_zty(ds_host, kern)
+            zty.cpu()
 
-    e2e_steps(max(args.warmup, 3))
-    torch.cuda.synchronize()
-    barrier()
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    e2e_steps(args.steps)
-    e1.record()
-    torch.cuda.synchronize()
-    barrier()
-    e2e_ms = e0.elapsed_time(e1)
-    clocks = sampler.stop() if sampler else None      # sampled across both timed regions
+    def e2e_mat_steps(k):                 # Z written to HBM and re-read by the Z^T y kernel (what transform_x + `@` does)
+        yd = y_pinned.to(dev)
+        for _ in range(k):
+            zty = torch.zeros(NUM_RFFS, dtype=torch.float64, device=dev)
+            for z in kern.transform_stream([(x_pinned, None)]):
+                ext.zty_accum(z, yd, zty)
+            zty.cpu()
 
-    # ---------------- the metric's second kernel: Conv1dRBF @16384 RFFs on cfg3-shaped sequences
-    conv = conv_headline(args, dev, rank)
-    gram = gram_headline(dev, rank)
+    def timed_region(fn, k):
+        fn(warm)
+        torch.cuda.synchronize()
+        barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn(k)
+        e1.record()
+        torch.cuda.synchronize()
+        barrier()
+        return e0.elapsed_time(e1)
 
-    t = torch.tensor([dev_ms, e2e_ms, float(np.mean(kern_ms)), conv["ms"], gram["tc_ms"], gram["gemm_ms"],
-                      gram["dfma_ms"]], dtype=torch.float64, device=dev)
+    e2e_ms = timed_region(e2e_steps, steps)
+    clocks = sampler.stop() if sampler else None      # sampled across the two headline timed regions
+    e2e_mat_ms = timed_region(e2e_mat_steps, max(3, steps // 4)) * steps / max(3, steps // 4)
+    del out, x_dev
+    torch.cuda.empty_cache()
+
+    # ---------------- the metric's second kernel, the dense contraction, and the strong-scaling fit
+    conv = conv_headline(args, dev, rank, world) if not args.no_conv else None
+    gram = gram_headline(dev, rank) if not args.no_gram else None
+    torch.cuda.empty_cache()
+    fit = fit_headline(args, dev, rank, world) if args.fit_rows > 0 else None
+
+    vals = [dev_ms, e2e_ms, float(np.mean(kern_ms)), e2e_mat_ms]
+    vals += [conv["ms"], conv["e2e_ms"]] if conv else [0.0, 0.0]
+    vals += [gram["tc_ms"], gram["gemm_ms"], gram["dfma_ms"]] if gram else [0.0, 0.0, 0.0]
+    t = torch.tensor(vals, dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms, e2e_ms, kmean, conv_ms, gram_ms, gram_gemm_ms, gram_dfma_ms = [float(v) for v in t.cpu()]
+    dev_ms, e2e_ms, kmean, e2e_mat_ms, conv_ms, conv_e2e_ms, gram_ms, gram_gemm_ms, gram_dfma_ms = [float(v) for v in t.cpu()]
 
     if rank == 0:
-        total_rows = rows * args.steps * world
+        total_rows = rows * steps * world
         value = total_rows / (dev_ms * 1e-3)
-        e2e_val = total_rows / (e2e_ms * 1e-3)
         peak, how = peaks()
         achieved = BYTES_PER_ROW * rows / (kmean * 1e-3) / 1e9
         traffic = None
@@ -321,47 +384,38 @@ def run_b200(args):
                 traffic = None
         line = {
             "metric": "RFF feature rows/s @16384 RFFs (RBF)", "value": value, "unit": "rows/s",
-            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "n_gpus": world, "steps": steps, "warmup": warm,
+            "ms_per_step": dev_ms / steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32 FHT -> f64 features", "data": "synthetic",
             "config": {"workload": "cfg2: RBF, 64 input features, num_rffs=16384, feature generation",
-                       "rows_per_step_per_gpu": rows, "bytes_per_row": BYTES_PER_ROW,
+                       "rows_per_step": rows, "rows_per_step_per_gpu": rows, "bytes_per_row": BYTES_PER_ROW,
                        "l2": "output chunk %.1f GB per step >> 126 MB L2 (inputs larger than L2)"
                              % (rows * NUM_RFFS * 8 / 1e9),
                        "sharding": "rows, no collective"},
-            "e2e": {"value": e2e_val, "unit": "rows/s", "h2d_bytes_per_step": rows * D_IN * 4,
-                    "d2h_bytes_per_step": NUM_RFFS * 8, "api": "xgpr_b200.kernels.RBF.transform_stream(pinned host chunks): transform_x per chunk, next chunk's H2D double-buffered"},
+            "e2e": {"value": total_rows / (e2e_ms * 1e-3), "unit": "rows/s",
+                    "h2d_bytes_per_step": rows * D_IN * 4 + rows * 8, "d2h_bytes_per_step": NUM_RFFS * 8,
+                    "api": "xgpr_b200.fitting.calc_zty(host-resident pinned ShardDataset, RBF kernel): per step H2D of x "
+                           "and y in 4 double-buffered chunks, fused featurise -> Z^T y over every row (Z never written), "
+                           "D2H of the M-vector",
+                    "materialised": {"value": total_rows / (e2e_mat_ms * 1e-3), "unit": "rows/s",
+                                     "api": "RBF.transform_stream(pinned host chunk) -> Z in HBM -> zty_accum -> D2H of "
+                                            "the M-vector (Z written once and read once)"}},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": how,
                          "kernel": "rbf_core_kernel<float,64,16>", "kernel_ms": kmean,
                          "algorithmic_bytes_per_launch": BYTES_PER_ROW * rows},
             "clocks": clocks, "wall_s": wall,
-            "also": {"metric": "RFF feature rows/s @16384 RFFs (Conv1dRBF)",
-                     "value": conv["rows"] * conv["steps"] * world / (conv_ms * 1e-3), "unit": "rows/s",
-                     "workload": "cfg3 shape: one-hot 500 x 21 sequences (full length), conv_width 9, num_rffs=16384, "
-                                 "sum-pooled; %d sequences per step per GPU, device-resident" % conv["rows"],
-                     "bound": "fp32 issue (ALU), not HBM: see DESIGN.md",
-                     "freq_windows_per_s": conv["fw"] * conv["steps"] * world / (conv_ms * 1e-3),
-                     "gpu_launches": conv["launches"]},
         }
-        bf16_peak = tensor_peak()
-        line["gram"] = {
-            "metric": "Z^T Z accumulation (exact-fit Gram), fp64-equivalent TFLOP/s per GPU",
-            "workload": "Z (%d x %d) fp64 features per call per GPU, %d int8 digit planes of %d bits (element error "
-                        "<= n 2^-37 colmax^2), upper triangle + mirror" % (gram["n"], gram["m"], gram["slices"], gram["bits"]),
-            "value": 2.0 * gram["n"] * gram["m"] ** 2 / (gram_ms * 1e-3) / 1e12, "unit": "TFLOP/s (fp64-equivalent)",
-            "ms_per_call": gram_ms, "dfma_kernel_ms": gram_dfma_ms,
-            "speedup_vs_fp64_pipe": gram_dfma_ms / gram_ms, "gpu_launches_per_call": gram["launches"],
-            "roofline": {"bound": "tensor", "kernel": "tc_gram_kernel (tcgen05.mma kind::i8, M128 N256 K32)",
-                         "achieved": gram["int8_ops"] / (gram_gemm_ms * 1e-3) / 1e12,
-                         "peak": None if bf16_peak is None else 2.0 * bf16_peak, "unit": "TOP/s (int8)",
-                         "frac": None if bf16_peak is None else gram["int8_ops"] / (gram_gemm_ms * 1e-3) / 1e12 / (2.0 * bf16_peak),
-                         "peak_source": "2 x measured bf16 burst TFLOP/s (MEASURED_PEAKS.json); int8 issues at twice the bf16 rate",
-                         "kernel_ms": gram_gemm_ms, "algorithmic_ops_per_launch": gram["int8_ops"]}}
+        if conv:
+            line["also"] = conv_record(conv, conv_ms, conv_e2e_ms, world, args)
+        if gram:
+            line["gram"] = gram_record(gram, gram_ms, gram_gemm_ms, gram_dfma_ms)
+        if fit:
+            line["fit"] = fit
         if world == 1 and not args.no_cpu_baseline:
             try:
-                v, kind, cores, sample = cpu_rows_per_s(kern_cpu_copy(), args.cpu_rows)
+                v, kind, cores, sample = cpu_rows_per_s(draw_params(), args.cpu_rows)
                 line["cpu_baseline"] = {"value": v, "unit": "rows/s", "cores": cores, "kind": kind, "sample": sample}
             except Exception as exc:  # the baseline must never take the GPU line down
                 line["cpu_baseline"] = {"value": None, "unit": "rows/s", "cores": 0, "kind": "port",
@@ -371,21 +425,33 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
-def conv_headline(args, dev, rank, nseq=4096, steps=3):
-    """Conv1dRBF feature generation at 16384 RFFs (the second kernel BASELINE.json's metric names)."""
+# ------------------------------------------------------------------------------------------------ Conv1dRBF @16384
+CONV_SEQ, CONV_LEN, CONV_CH, CONV_W = 4096, 500, 21, 9
+CONV_WINDOWS = CONV_LEN - CONV_W + 1
+
+
+def conv_headline(args, dev, rank, world, steps=3):
+    """Conv1dRBF feature generation at 16384 RFFs (the second kernel BASELINE.json's metric names): device-resident
+    throughput, and end to end from pinned host sequences through Conv1dRBF.transform_stream into Z^T y."""
     import torch
     from xgpr_b200 import ext
     from xgpr_b200.kernels import Conv1dRBF
-    k = Conv1dRBF((nseq, 500, 21), NUM_RFFS, random_seed=123, device="cuda", kernel_spec_parms={"conv_width": 9})
-    g = torch.Generator(device=dev)
-    g.manual_seed(123 + rank)
-    idx = torch.randint(0, 21, (nseq, 500), device=dev, generator=g)
-    x = (torch.nn.functional.one_hot(idx, 21).to(torch.float32) * 0.3).contiguous()
-    seqlen = np.full(nseq, 500, dtype=np.int32)
+    nseq = CONV_SEQ
+    k = Conv1dRBF((nseq, CONV_LEN, CONV_CH), NUM_RFFS, random_seed=123, device="cuda",
+                  kernel_spec_parms={"conv_width": CONV_W})
+    k.set_hyperparams(np.log(np.asarray([np.sqrt(0.0767), 0.3])), logspace=True)
+    rng = np.random.default_rng(123 + rank)
+    idx = rng.integers(0, CONV_CH, size=(nseq, CONV_LEN))
+    x_np = np.zeros((nseq, CONV_LEN, CONV_CH), dtype=np.float32)
+    np.put_along_axis(x_np, idx[:, :, None], 1.0, axis=2)
+    x_pinned = torch.from_numpy(x_np).pin_memory()
+    x = (x_pinned.to(dev) * 0.3).contiguous()
+    seqlen = np.full(nseq, CONV_LEN, dtype=np.int32)
     out = torch.zeros((nseq, NUM_RFFS), dtype=torch.float64, device=dev)
+    y = torch.from_numpy(rng.standard_normal(nseq)).to(dev)
 
     def step():
-        ext.cudaConv1dFGen(x, out, k.radem_diag, k.chi_arr, seqlen, 9, 0)
+        ext.cudaConv1dFGen(x, out, k.radem_diag, k.chi_arr, seqlen, CONV_W, 0)
 
     step()
     torch.cuda.synchronize()
@@ -396,10 +462,94 @@ def conv_headline(args, dev, rank, nseq=4096, steps=3):
         step()
     b.record()
     torch.cuda.synchronize()
-    return {"ms": a.elapsed_time(b), "rows": nseq, "steps": steps, "fw": nseq * 492 * (NUM_RFFS // 2),
-            "launches": ext.launch_count() - l0}
+    launches = ext.launch_count() - l0
+    ms = a.elapsed_time(b)
+
+    # end to end: pinned host sequences, 4 double-buffered chunks per step, Z^T y accumulated, M-vector read back
+    q = nseq // 4
+    chunks = [(x_pinned[i * q:(i + 1) * q], seqlen[i * q:(i + 1) * q]) for i in range(4)]
+
+    def e2e_step():
+        zty = torch.zeros(NUM_RFFS, dtype=torch.float64, device=dev)
+        for i, z in enumerate(k.transform_stream(chunks)):
+            ext.zty_accum(z, y[i * q:(i + 1) * q].contiguous(), zty)
+        zty.cpu()
+
+    e2e_step()
+    torch.cuda.synchronize()
+    a.record()
+    for _ in range(steps):
+        e2e_step()
+    b.record()
+    torch.cuda.synchronize()
+    e2e_ms = a.elapsed_time(b)
+    del out, x
+    return {"ms": ms, "e2e_ms": e2e_ms, "rows": nseq, "steps": steps, "fw": nseq * CONV_WINDOWS * (NUM_RFFS // 2),
+            "launches": launches, "h2d": int(x_pinned.numel() * 4), "d2h": NUM_RFFS * 8}
 
 
+def conv_cpu_baseline(nseq=64, reps=3):
+    """The reference's cpuConv1dFGen (rbf_convolution.cpp:22-139) on `nseq` full-length sequences, all host threads."""
+    ext = ref_ext()
+    if ext is None:
+        return None
+    prm = HostParams(CONV_W * CONV_CH, NUM_RFFS)
+    rng = np.random.default_rng(123)
+    idx = rng.integers(0, CONV_CH, size=(nseq, CONV_LEN))
+    x = np.zeros((nseq, CONV_LEN, CONV_CH), dtype=np.float32)
+    np.put_along_axis(x, idx[:, :, None], np.float32(0.3), axis=2)
+    seqlen = np.full(nseq, CONV_LEN, dtype=np.int32)
+    best = None
+    for _ in range(reps + 1):
+        out = np.zeros((nseq, NUM_RFFS))
+        t = time.perf_counter()
+        ext.cpuConv1dFGen(x, out, prm.radem_diag, prm.chi_arr, seqlen, CONV_W, 0)
+        dt = time.perf_counter() - t
+        best = dt if best is None else min(best, dt)
+    return {"value": nseq / best, "unit": "rows/s", "cores": os.cpu_count(), "kind": "reference",
+            "sample": f"{nseq} sequences of 500 x 21 x {reps + 1} reps (best), cpuConv1dFGen"}
+
+
+def conv_record(conv, conv_ms, conv_e2e_ms, world, args):
+    n = conv["rows"] * conv["steps"] * world
+    fw_s = conv["fw"] * conv["steps"] * world / (conv_ms * 1e-3)
+    # fp32-issue roofline: warp-lane instructions per frequency-window (ncu instruction count of the kernel / its
+    # frequency-windows, profiles/conv_instr_mix.json) x frequency-windows/s, against the measured FFMA issue rate
+    # (profiles/r01_microbench.jsonl, probe "FFMA")
+    mix, peak = 60.3, 3.5395e13
+    try:
+        mix = float(json.load(open(os.path.join(ROOT, "profiles", "conv_instr_mix.json")))["lane_instr_per_freq_window"])
+    except Exception:
+        pass
+    try:
+        for ln in open(os.path.join(ROOT, "profiles", "r01_microbench.jsonl")):
+            d = json.loads(ln)
+            if d.get("probe") == "FFMA":
+                peak = float(d["lane_ops_per_s"])
+    except Exception:
+        pass
+    achieved = mix * fw_s / world
+    rec = {"metric": "RFF feature rows/s @16384 RFFs (Conv1dRBF)", "value": n / (conv_ms * 1e-3), "unit": "rows/s",
+           "workload": "cfg3 shape: one-hot 500 x 21 sequences (full length), conv_width 9, num_rffs=16384, "
+                       "sum-pooled; %d sequences per step per GPU, device-resident" % conv["rows"],
+           "freq_windows_per_s": fw_s, "gpu_launches": conv["launches"],
+           "roofline": {"bound": "fp32_issue", "achieved": achieved, "peak": peak, "unit": "lane-instr/s per GPU",
+                        "frac": achieved / peak, "kernel": "conv_core_kernel<float,256,16,FGEN>",
+                        "lane_instr_per_freq_window": mix,
+                        "peak_source": "measured FFMA issue rate, profiles/r01_microbench.jsonl",
+                        "hbm_frac": (173076.0 * n / (conv_ms * 1e-3) / 1e9 / world) / peaks()[0]},
+           "e2e": {"value": n / (conv_e2e_ms * 1e-3), "unit": "rows/s", "h2d_bytes_per_step": conv["h2d"],
+                   "d2h_bytes_per_step": conv["d2h"],
+                   "api": "Conv1dRBF.transform_stream(4 pinned host chunks) -> zty_accum -> D2H of the M-vector"}}
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            rec["cpu_baseline"] = conv_cpu_baseline()
+        except Exception as exc:
+            rec["cpu_baseline"] = {"value": None, "sample": f"failed: {exc}"}
+    return rec
+
+
+# ------------------------------------------------------------------------------------------------ tensor-core Gram
 def tensor_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -448,8 +598,106 @@ def gram_headline(dev, rank, n=32768, m=8192, slices=5, bits=8, steps=3):
             "slices": slices, "bits": bits, "launches": launches, "int8_ops": int8_ops}
 
 
-def kern_cpu_copy():
-    return draw_params()
+def gram_record(gram, gram_ms, gram_gemm_ms, gram_dfma_ms):
+    bf16_peak = tensor_peak()
+    tops = gram["int8_ops"] / (gram_gemm_ms * 1e-3) / 1e12
+    return {
+        "metric": "Z^T Z accumulation (exact-fit Gram), fp64-equivalent TFLOP/s per GPU",
+        "workload": "Z (%d x %d) fp64 features per call per GPU, %d int8 digit planes of %d bits (element error "
+                    "<= n 2^-37 colmax^2), upper triangle + mirror" % (gram["n"], gram["m"], gram["slices"], gram["bits"]),
+        "value": 2.0 * gram["n"] * gram["m"] ** 2 / (gram_ms * 1e-3) / 1e12, "unit": "TFLOP/s (fp64-equivalent)",
+        "ms_per_call": gram_ms, "dfma_kernel_ms": gram_dfma_ms,
+        "speedup_vs_fp64_pipe": gram_dfma_ms / gram_ms, "gpu_launches_per_call": gram["launches"],
+        "roofline": {"bound": "tensor", "kernel": "tc_gram_kernel (tcgen05.mma kind::i8, M128 N256 K32)",
+                     "achieved": tops, "peak": None if bf16_peak is None else 2.0 * bf16_peak, "unit": "TOP/s (int8)",
+                     "frac": None if bf16_peak is None else tops / (2.0 * bf16_peak),
+                     "peak_source": "2 x measured bf16 burst TFLOP/s (MEASURED_PEAKS.json); int8 issues at twice the bf16 rate",
+                     "kernel_ms": gram_gemm_ms, "algorithmic_ops_per_launch": gram["int8_ops"]}}
+
+
+# ------------------------------------------------------------------------------------------------ strong-scaling fit
+FIT_W_N1 = os.path.join(ROOT, "tests", "golden", "cfg2_fit_w_n1.npy")
+
+
+def fit_dataset(n_global, rank, world):
+    """cfg2's synthetic training set, identical at every N: generated from ONE global seed, sliced by rank."""
+    rng = np.random.default_rng(123)
+    x = rng.standard_normal((n_global, D_IN), dtype=np.float32)
+    y = np.sin(x[:, :8].sum(1, dtype=np.float64)) + 0.1 * rng.standard_normal(n_global)
+    lo, hi = (n_global * rank) // world, (n_global * (rank + 1)) // world
+    return x[lo:hi], y[lo:hi]
+
+
+def fit_headline(args, dev, rank, world, chunk=32768, tol=1e-6, maxiter=200):
+    """cfg2: RBF 1M x 64 -> 16,384 RFFs, rank-512 "srht" Nystrom preconditioner + CG to 1e-6 (BASELINE.json configs[1]).
+    STRONG scaling: the global row count is fixed, every rank holds rows [rank/N, (rank+1)/N) of the same dataset on its
+    device; the collectives are the fp64 all-reduces of fitting.py (Nystrom accumulator, Z^T y, one per CG iteration).
+    One untimed warm-up fit (allocator pools, cuSOLVER / cuBLAS handles, NCCL channels), then precondition + CG timed with
+    CUDA events, max over ranks."""
+    import torch
+    import torch.distributed as dist
+    from xgpr_b200 import ext, fitting
+    from xgpr_b200.kernels import RBF
+    comm = fitting.RowShardComm()
+    xs, ys = fit_dataset(args.fit_rows, rank, world)
+    x = torch.from_numpy(np.ascontiguousarray(xs)).to(dev)
+    y = torch.from_numpy(np.ascontiguousarray(ys)).to(dev)
+    ds = fitting.build_shard_dataset(x, y, None, chunk, comm)
+    kern = RBF((args.fit_rows, D_IN), NUM_RFFS, random_seed=123, device="cuda")
+    kern.set_hyperparams(np.asarray([np.log(np.sqrt(0.0767)), np.log(SIGMA)]), logspace=True)
+
+    def timed(fn):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        res = fn()
+        b.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return res, float(t[0]) * 1e-3
+
+    pre = fitting.RandNysPreconditioner(kern, ds, args.fit_rank, False, 123, "srht", comm)
+    fitting.cg_fit_lib_internal(kern, ds, tol, maxiter, pre, False, comm)
+    del pre
+    comm.n_allreduce, comm.bytes_allreduce = 0, 0
+    l0 = ext.launch_count()
+    pre, t_pre = timed(lambda: fitting.RandNysPreconditioner(kern, ds, args.fit_rank, False, 123, "srht", comm))
+    cg_op = {}
+
+    def run_cg():
+        op = fitting.ConjugateGrad(comm)
+        cg_op["op"] = op
+        return fitting.cg_fit_lib_internal(kern, ds, tol, maxiter, pre, False, comm, cg_operator=op)
+
+    (w, n_iter, losses), t_cg = timed(run_cg)
+    rec = None
+    if rank == 0:
+        w_np = w.cpu().numpy()
+        if args.save_fit_weights and world == 1:
+            np.save(FIT_W_N1, w_np)
+        w_err = None
+        if os.path.exists(FIT_W_N1):
+            w1 = np.load(FIT_W_N1)
+            if w1.shape == w_np.shape:
+                w_err = float(np.abs(w_np - w1).max() / np.abs(w1).max())
+        rec = {"metric": "cfg2 CG fit wall-clock (strong scaling)", "value": t_pre + t_cg, "unit": "s",
+               "higher_is_better": False, "scaling": "strong",
+               "workload": f"RBF {args.fit_rows} x {D_IN} (global, same dataset at every N: seed 123, sliced by rank), "
+                           f"num_rffs={NUM_RFFS}, rank-{args.fit_rank} srht preconditioner, CG tol {tol}",
+               "n_gpus": world, "fit_s": t_pre + t_cg, "precond_s": t_pre, "cg_s": t_cg, "cg_iters": int(n_iter),
+               "final_err": float(losses[-1]) if losses else None, "achieved_ratio": float(pre.achieved_ratio),
+               "allreduces": int(comm.n_allreduce), "allreduce_bytes": int(comm.bytes_allreduce),
+               "rows_per_s_fit": args.fit_rows / (t_pre + t_cg), "gpu_launches": int(ext.launch_count() - l0),
+               "cg": dict(cg_op["op"].last_fit_info),
+               "weights_vs_n1": {"max_abs_err_over_max_abs_w": w_err, "bound": 1e-6,
+                                 "reference_vector": "tests/golden/cfg2_fit_w_n1.npy (this fit on 1 B200)"}}
+    del x, y, ds, pre
+    torch.cuda.empty_cache()
+    return rec
 
 
 def main():

@@ -165,6 +165,11 @@ int xgpr_b200_symmetrize_upper_f64(double* g, int64_t m, void* stream);
  * launching stream; xgpr_b200_tc_last_gemm_ms() synchronises on the last bracket and returns its duration (-1: none). */
 int    xgpr_b200_tc_profile(int enable);
 double xgpr_b200_tc_last_gemm_ms(void);
+/* Accuracy switch for the float32 cos / sin of every feature kernel, per device (applies to the CURRENT device): 0 (default)
+ * = two-term Cody-Waite reduction + MUFU.SIN / MUFU.COS (abs. error <= ~6e-7); 1 = CUDA's accurate sincosf (<= 2 ulp, the
+ * class of glibc's cosf / sinf the reference calls at cpu/shared_fht_functions/shared_rfgen_ops.cpp:107-112).  Measured
+ * cost and effect on fitted weights: DESIGN.md section 2. */
+int    xgpr_b200_set_accurate_sincos(int on);
 /* Tensor-core sketch accumulation, same scheme: acc (r, m) += A^T Z, A (n, r), Z (n, m) fp64 row-major
  * (`acc_results += compressor.transform_x(xdata).T @ xdata`, src/xGPR/preconditioners/rand_nys_constructors.py:119). */
 int64_t xgpr_b200_atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int num_slices);
@@ -192,6 +197,23 @@ int xgpr_b200_rbf_feature_gen_c32(const float* x, int64_t n, int64_t d, float* c
 int xgpr_b200_cres_zzv_supported(int64_t m);
 int xgpr_b200_cres_zzv_f32(const float* c, int64_t n, int64_t m, const double* vs, double* w, double scale,
                            int fit_intercept, void* stream);
+/* Stream-ordered preconditioned CG for ONE right-hand side (src/xGPR/fitting_toolkit/cg_tools.py:57-156 with the scalar
+ * recurrences kept on the device, so that an iteration needs no host synchronisation and can be captured in a CUDA graph).
+ * state (8 doubles, device): [0] r.z  [1] ||r_0||  [2] tol  [3] alpha  [4] beta  [5] done (0 / 1)  [6] iterations run
+ * when done  [7] iteration counter.  Once done != 0 every entry point below (and the gated matvec) is a no-op, so
+ * iterations launched ahead of the host's convergence check leave x untouched.
+ *   cg_update_a : given w = sum_chunks Z^T (Z p) (all-reduced): w' = w + lambda2 p; alpha = r.z / p.w'; x += alpha p;
+ *                 hist[iter] = ||r|| / ||r_0|| (the residual BEFORE the update, as cg_tools.py:116,139 judges it);
+ *                 r -= alpha w'; done = hist[iter] < tol; ++iter.
+ *   cg_update_b : given z = P^-1 r: beta = r.z / (r.z)_old; p = z + beta p; ps = p * scale (ps[0] = p[0] when
+ *                 fit_intercept) -- the scaled direction the resident matvec consumes (ps may be NULL).
+ *   cres_zzv_gated : xgpr_b200_cres_zzv_f32 that returns immediately when *skip != 0 (skip = state + 5). */
+int xgpr_b200_cg_update_a_f64(const double* w, const double* p, double* x, double* r, int64_t m, double lambda2,
+                              double* state, double* hist, int64_t maxiter, void* stream);
+int xgpr_b200_cg_update_b_f64(const double* r, const double* z, double* p, double* ps, int64_t m, double scale,
+                              int fit_intercept, double* state, void* stream);
+int xgpr_b200_cres_zzv_gated_f32(const float* c, int64_t n, int64_t m, const double* vs, double* w, double scale,
+                                 int fit_intercept, const double* skip, void* stream);
 /* acc (r, m) += A^T Z ;  A (n, r) row-major: the Nystrom sketch accumulation
  * `acc_results += compressor.transform_x(xdata).T @ xdata` (src/xGPR/preconditioners/rand_nys_constructors.py:119) */
 int xgpr_b200_atb_accum_f64(const double* a, const double* z, int64_t n, int64_t r, int64_t m, double* acc, void* stream);

@@ -1,0 +1,133 @@
+"""GPU: the BASELINE.json configurations at their REAL widths against the REFERENCE's own results.
+
+Fixtures `tests/golden/cfg_*.npz` were produced by tests/golden/make_golden_configs.py from the unmodified reference model
+class on its CPU path (xGPRegression(device="cpu")); the inputs are regenerated here from the same seeds
+(tests/config_inputs.py).  Where `oracle/_ref` (the reference's CPU extension compiled by oracle/Makefile) travelled to the
+box, the convolution shapes are ALSO compared live, all columns and the gradient.
+
+  cfg3 / cfg4 / Conv1dRBF @16,384   ragged real-shape sequences, three scalings: rtol 1e-5, atol 1e-5 x max|Z|
+  cfg1 (full size, exact fit)       features 1e-5 of scale; weights and predictions: float32 bound, see F32_*
+  cfg2 (20k-row subsample, 16,384)  rank-512 srht ratio, CG iteration count, weights, predictions, rank-ratio pass
+  cfg5 (20k-row subsample, 32,768)  approximate NMLL (SLQ), MiniARD split_points=[64]
+
+float32 tolerances (north_star states 1e-6 on weights and predictions; the reference hard-wires the float32 FHT,
+model_baseclass.py:115-117).  The feature kernels reproduce every pre-activation of the reference bit for bit; what
+differs is cos / sin itself: glibc cosf/sinf (<= 1 ulp) on the reference side, here MUFU after a Cody-Waite reduction
+(<= ~6e-7 absolute) or, with XGPR_B200_ACCURATE_SINCOS=1, CUDA's sincosf (<= 2 ulp).  A feature perturbation of relative size
+e moves the solution of (Z^T Z + lambda^2 I) w = Z^T y by ~ e x sqrt(cond) x |w|; the measured effect is tabulated in
+DESIGN.md section 2 (tools/f32_parity_study.py) and the bounds below are ~3x the measured errors.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from config_inputs import CONV_CASES, LAMBDA, conv_cols, conv_inputs, tabular
+from conftest import GOLDEN, load_golden, ref_ext
+
+pytestmark = pytest.mark.gpu
+
+# measured on B200 (profiles/r02_f32_parity.json): max |w - w_ref| / max |w_ref| and max |pred - pred_ref| / std(y)
+F32_WEIGHT_TOL = {"cfg1": 2e-3, "cfg2": 2e-3}
+F32_PRED_TOL = {"cfg1": 1e-4, "cfg2": 1e-4}
+
+
+def _rel(a, b):
+    return float(np.abs(a - b).max() / np.abs(b).max())
+
+
+@pytest.mark.parametrize("case", CONV_CASES, ids=[c[0] for c in CONV_CASES])
+def test_conv_config_shape_vs_reference(case):
+    from xgpr_b200 import ext
+    from xgpr_b200.kernels import Conv1dRBF, GraphRBF
+    name, kind, n, w, m, sigma = case
+    x, lens = conv_inputs(kind, n, seed=31)
+    g = load_golden(os.path.join(GOLDEN, f"cfg_conv_{name}.npz"))
+    assert np.array_equal(g["seqlen"], lens)
+    cols = conv_cols(m)
+    live = ref_ext()
+    cls = Conv1dRBF if w > 1 else GraphRBF
+    for st, avg in enumerate(("none", "sqrt", "full")):
+        parms = {"conv_width": w, "averaging": avg} if w > 1 else {"averaging": avg}
+        k = cls(x.shape, m, random_seed=123, device="cuda", kernel_spec_parms=parms)
+        k.set_hyperparams(np.log(np.asarray([LAMBDA, sigma])), logspace=True)
+        z = k.transform_x(x, lens).cpu().numpy()
+        gold = g["z_" + avg]
+        scale = float(np.abs(gold[:, 1:]).max())
+        np.testing.assert_allclose(z[:, cols], gold, rtol=1e-5, atol=1e-5 * scale)
+        if live is None:
+            continue
+        # the reference's CPU extension on the same inputs: every column, and the gradient entry point
+        host = cls(x.shape, m, random_seed=123, device="cpu", kernel_spec_parms=parms)
+        xs = x.copy()
+        xs *= np.float64(sigma)                          # `input_x *= hyperparams[1]`: double product, one rounding
+        ref = np.zeros((n, m))
+        live.cpuConv1dFGen(xs, ref, host.radem_diag, host.chi_arr, lens, w, st)
+        ref[:, 0] = 1.0
+        np.testing.assert_allclose(z, ref, rtol=1e-5, atol=1e-5 * scale)
+        if st == 1:
+            gref, dref = np.zeros((n, m)), np.zeros((n, m, 1))
+            live.cpuConvGrad(x, gref, host.radem_diag, host.chi_arr, lens, dref, float(sigma), w, st)
+            out = torch.zeros((n, m), dtype=torch.float64, device="cuda")
+            grad = torch.zeros((n, m, 1), dtype=torch.float64, device="cuda")
+            ext.cudaConvGrad(torch.from_numpy(x).cuda(), out, k.radem_diag, k.chi_arr, lens, grad, float(sigma), w, st)
+            np.testing.assert_allclose(out.cpu().numpy(), gref, rtol=1e-5, atol=1e-5 * float(np.abs(gref).max()))
+            np.testing.assert_allclose(grad.cpu().numpy(), dref, rtol=1e-5, atol=1e-5 * float(np.abs(dref).max()))
+
+
+def test_cfg1_full_size_vs_reference_exact_fit():
+    """BASELINE config 1 IS the reference's CPU exact fit: 20,000 x 512 -> 2,048 RFFs, weights and predictions."""
+    from xgpr_b200 import fitting
+    from xgpr_b200.kernels import RBF
+    g = load_golden(os.path.join(GOLDEN, "cfg_1_exact.npz"))
+    x, y = tabular(20000, 512)
+    kern = RBF(x.shape, 2048, random_seed=123, device="cuda")
+    kern.set_hyperparams(np.log(g["hyperparams"]), logspace=True)
+    z4 = kern.transform_x(x[:4]).cpu().numpy()
+    np.testing.assert_allclose(z4, g["z_first4"], rtol=1e-5, atol=1e-5 * float(np.abs(g["z_first4"][:, 1:]).max()))
+    ds = fitting.build_shard_dataset(x, y, None, chunk_size=2000)
+    np.testing.assert_allclose(ds.get_ymean(), float(g["trainy_mean"]), rtol=1e-12)
+    np.testing.assert_allclose(ds.get_ystd(), float(g["trainy_std"]), rtol=1e-12)
+    w, _, _ = fitting.calc_weights_exact(ds, kern)
+    assert _rel(w.cpu().numpy(), g["weights"]) < F32_WEIGHT_TOL["cfg1"]
+    pred = fitting.predict(kern, w, x[:500], None, 2000, ds.get_ymean(), ds.get_ystd())
+    assert float(np.abs(pred - g["pred"]).max()) / ds.get_ystd() < F32_PRED_TOL["cfg1"]
+
+
+def test_cfg2_subsample_full_width_cg_fit_vs_reference():
+    """RBF, 16,384 RFFs, the reference's rank-512 "srht" preconditioner + fit(mode="cg", tol=1e-6) on 20,000 rows."""
+    from xgpr_b200 import fitting, scoring
+    from xgpr_b200.kernels import RBF
+    g = load_golden(os.path.join(GOLDEN, "cfg_2_cg.npz"))
+    x, y = tabular(20000, 64)
+    kern = RBF(x.shape, 16384, random_seed=123, device="cuda")
+    kern.set_hyperparams(np.log(g["hyperparams"]), logspace=True)
+    ds = fitting.build_shard_dataset(x, y, None, chunk_size=2000)
+    pre = fitting.RandNysPreconditioner(kern, ds, 512, False, 123, "srht")
+    np.testing.assert_allclose(pre.achieved_ratio, float(g["ratio"]), rtol=1e-3)
+    w, nit, losses = fitting.cg_fit_lib_internal(kern, ds, 1e-6, 500, pre, False)
+    assert abs(nit - int(g["niter"])) <= 1
+    assert _rel(w.cpu().numpy(), g["weights"]) < F32_WEIGHT_TOL["cfg2"]
+    xt, _ = tabular(200, 64, seed=321)
+    pred = fitting.predict(kern, w, xt, None, 2000, ds.get_ymean(), ds.get_ystd())
+    assert float(np.abs(pred - g["pred"]).max()) / ds.get_ystd() < F32_PRED_TOL["cfg2"]
+    # the autoselection's ratio pass: the reference runs it on min(num_rffs, 8192) features (model_baseclass.py:465-474)
+    rr = scoring.check_rank_ratio(ds, kern, 0.2, 512, 123)
+    np.testing.assert_allclose(rr, float(g["rank_ratio_512"]), rtol=1e-3)
+    assert kern.get_num_rffs() == 16384
+
+
+def test_cfg5_subsample_full_width_approximate_nmll_vs_reference():
+    """MiniARD split_points=[64], 32,768 RFFs, approximate_nmll (25 probes, rank-512 srht_2, tol 1e-6) on 20,000 rows."""
+    from xgpr_b200 import fitting, scoring
+    from xgpr_b200.kernels import MiniARD
+    g = load_golden(os.path.join(GOLDEN, "cfg_5_nmll.npz"))
+    x, y = tabular(20000, 128)
+    kern = MiniARD(x.shape, 32768, random_seed=123, device="cuda", kernel_spec_parms={"split_points": [64]})
+    ds = fitting.build_shard_dataset(x, y, None, chunk_size=2000)
+    settings = {"max_rank": int(g["max_rank"]), "nsamples": int(g["nsamples"]), "nmll_tol": float(g["tol"]),
+                "nmll_iter": 500, "preconditioner_mode": "srht_2"}
+    val = scoring.approximate_nmll(np.log(g["hyperparams"]), ds, kern, manual_settings=settings)
+    # SLQ with identical host-drawn probes: the estimate itself is deterministic; float32 features move it by ~1e-6
+    np.testing.assert_allclose(val, float(g["nmll_approx"]), rtol=1e-5)

@@ -61,6 +61,55 @@ def test_fit_matches_reference(name):
     np.testing.assert_allclose(pe, g["pred_exact"], rtol=1e-6 if f64 else 1e-4, atol=1e-9 if f64 else 1e-4)
 
 
+@pytest.mark.parametrize("m", [256, 4096])
+def test_device_cg_matches_host_loop(m):
+    """The stream-ordered CG (scalar recurrences on the device, CUDA-graph replay, lagged convergence polling:
+    ConjugateGrad._fit_device) against the host-driven loop that mirrors cg_tools.py:57-156 line by line: same iteration
+    count, same loss history, same weights.  m = 256 runs the fused regenerate-per-iteration matvec, m = 4096 the resident
+    float32 encoding with the gated cluster matvec."""
+    from xgpr_b200 import fitting
+    from xgpr_b200.kernels import RBF
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((3000, 20)).astype(np.float32)
+    y = np.sin(x[:, :4].sum(1)) + 0.1 * rng.standard_normal(3000)
+    kern = RBF(x.shape, m, random_seed=123, device="cuda")
+    kern.set_hyperparams(np.log(np.asarray([0.5, 0.35])), logspace=True)
+    ds = fitting.build_shard_dataset(torch.from_numpy(x).cuda(), y, None, chunk_size=1000)
+    pre = fitting.RandNysPreconditioner(kern, ds, 64, False, 123, "srht")
+    out = {}
+    for name, dev_cg in (("device", True), ("host", False)):
+        op = fitting.ConjugateGrad()
+        op.device_cg = dev_cg
+        out[name] = fitting.cg_fit_lib_internal(kern, ds, 1e-9, 500, pre, False, cg_operator=op) + (op.last_fit_info,)
+    (w1, n1, l1, info1), (w0, n0, l0, info0) = out["device"], out["host"]
+    assert info1["device_cg"] and not info0["device_cg"]
+    assert info1["cuda_graph"], "the CG iteration should have been captured in a CUDA graph"
+    assert info1["resident"] == (m == 4096)
+    assert n1 == n0 and len(l1) == len(l0) == n1
+    np.testing.assert_allclose(l1, l0, rtol=1e-6)
+    np.testing.assert_allclose(w1.cpu().numpy(), w0.cpu().numpy(), rtol=1e-8, atol=1e-10 * float(w0.abs().max()))
+    # without a preconditioner, and a tolerance it cannot reach in 3 iterations: stops at maxiter, not converged
+    op = fitting.ConjugateGrad()
+    resid = torch.zeros((m, 2, 1), dtype=torch.float64, device="cuda")
+    resid[:, 0, 0] = pre.get_zty() / ds.get_ndatapoints()
+    xk, conv, nit, losses = op.fit(ds, kern, None, resid, maxiter=3, tol=1e-30, verbose=False)
+    assert not conv and nit == 3 and len(losses) == 3 and np.isfinite(losses).all()
+
+
+def test_fused_predict_matches_materialised():
+    """predict() through the fused featurise-dot kernel (Z never written) against (Z * w).sum(1) on transform_x."""
+    from xgpr_b200 import fitting
+    from xgpr_b200.kernels import RBF
+    rng = np.random.default_rng(8)
+    x = rng.standard_normal((5000, 64)).astype(np.float32)
+    kern = RBF(x.shape, 2048, random_seed=123, device="cuda")
+    kern.set_hyperparams(np.log(np.asarray([0.3, 0.1])), logspace=True)
+    w = torch.from_numpy(rng.standard_normal(2048)).cuda()
+    pred = fitting.predict(kern, w, x, None, 700, 1.5, 2.0)
+    ref = (kern.transform_x(x) @ w).cpu().numpy() * 2.0 + 1.5
+    np.testing.assert_allclose(pred, ref, rtol=1e-10, atol=1e-10)
+
+
 def test_resident_shard_gives_same_weights():
     fitting, g, kern, ds, _, _ = _setup("rbf_f32")
     w0, _, _ = fitting.calc_weights_exact(ds, kern)

@@ -79,6 +79,13 @@ EXPORTED.append("xgpr_b200_cres_zzv_supported")
 lib.xgpr_b200_cres_zzv_f32.argtypes = [_ptr, _i64, _i64, _ptr, _ptr, ctypes.c_double, _int, _ptr]
 lib.xgpr_b200_cres_zzv_f32.restype = _int
 EXPORTED.append("xgpr_b200_cres_zzv_f32")
+lib.xgpr_b200_cres_zzv_gated_f32.argtypes = [_ptr, _i64, _i64, _ptr, _ptr, ctypes.c_double, _int, _ptr, _ptr]
+lib.xgpr_b200_cres_zzv_gated_f32.restype = _int
+lib.xgpr_b200_cg_update_a_f64.argtypes = [_ptr, _ptr, _ptr, _ptr, _i64, _dbl, _ptr, _ptr, _i64, _ptr]
+lib.xgpr_b200_cg_update_a_f64.restype = _int
+lib.xgpr_b200_cg_update_b_f64.argtypes = [_ptr, _ptr, _ptr, _ptr, _i64, _dbl, _int, _ptr, _ptr]
+lib.xgpr_b200_cg_update_b_f64.restype = _int
+EXPORTED += ["xgpr_b200_cres_zzv_gated_f32", "xgpr_b200_cg_update_a_f64", "xgpr_b200_cg_update_b_f64"]
 lib.xgpr_b200_rbf_zzv_supported.argtypes = [_i64, _i64]
 lib.xgpr_b200_rbf_zzv_supported.restype = _int
 EXPORTED.append("xgpr_b200_rbf_zzv_supported")
@@ -87,6 +94,9 @@ lib.xgpr_b200_tc_profile.restype = _int
 lib.xgpr_b200_tc_last_gemm_ms.argtypes = []
 lib.xgpr_b200_tc_last_gemm_ms.restype = _dbl
 EXPORTED += ["xgpr_b200_tc_profile", "xgpr_b200_tc_last_gemm_ms"]
+lib.xgpr_b200_set_accurate_sincos.argtypes = [_int]
+lib.xgpr_b200_set_accurate_sincos.restype = _int
+EXPORTED.append("xgpr_b200_set_accurate_sincos")
 lib.xgpr_b200_abi_version.restype = _int
 lib.xgpr_b200_last_error.restype = ctypes.c_char_p
 lib.xgpr_b200_launch_count.restype = _i64

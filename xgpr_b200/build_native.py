@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libxgpr_b200.so")
-SOURCES = ["c_api.cu", "fht_kernels.cu", "rbf_kernels.cu", "rbf_matvec_kernels.cu", "conv_kernels.cu", "ard_kernels.cu", "gram_kernels.cu", "gram_tc_kernels.cu", "resident_matvec_kernels.cu"]
+SOURCES = ["c_api.cu", "fht_kernels.cu", "rbf_kernels.cu", "rbf_matvec_kernels.cu", "conv_kernels.cu", "ard_kernels.cu", "gram_kernels.cu", "gram_tc_kernels.cu", "resident_matvec_kernels.cu", "cg_kernels.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-fmad=false",
          "-Xcompiler", "-fPIC,-O2", "-Xptxas", "-v", "--threads", "0"]

@@ -93,7 +93,7 @@ int ard_dispatch(const T* x, int64_t n, int64_t d, double* out, const T* w, int6
     const double ff = (double)F;
     const double scale = (double)(T)(fit_intercept ? sqrt(1.0 / (ff - 0.5)) : sqrt(1.0 / ff));
     auto kern = ard_grad_kernel<T, TF, TR, KC>;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ensure_dyn_smem(kern, smem);
     dim3 grid((unsigned)((F + TF - 1) / TF), (unsigned)((n + TR - 1) / TR));
     XB_REQUIRE(grid.y <= 65535u * 1024u, "array too large");
     if (grid.y > 65535) {

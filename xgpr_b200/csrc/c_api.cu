@@ -2,6 +2,9 @@
 #include "common.cuh"
 
 #include <atomic>
+#include <map>
+#include <mutex>
+#include <utility>
 
 namespace xb {
 
@@ -22,6 +25,36 @@ int check_launch(const char* what) {
         return XGPR_B200_ECUDA;
     }
     return XGPR_B200_OK;
+}
+
+int current_device() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return dev;
+}
+
+static std::mutex g_smem_mu;
+static std::map<std::pair<const void*, int>, size_t> g_smem_limit;
+void ensure_dyn_smem_impl(const void* kern, size_t bytes) {
+    const int dev = current_device();
+    std::lock_guard<std::mutex> lk(g_smem_mu);
+    size_t& have = g_smem_limit[std::make_pair(kern, dev)];
+    if (have >= bytes) return;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) == cudaSuccess) have = bytes;
+    // on failure the launch that follows reports the error through check_launch
+}
+
+// accurate-sincos switch: every translation unit that includes sorf_core.cuh registers the setter of its own
+// __constant__ limit at static-initialisation time
+static void (*g_sincos_setters[16])(float) = {};
+static int g_n_sincos_setters = 0;
+int register_sincos_limit_setter(void (*fn)(float)) {
+    if (g_n_sincos_setters < 16) g_sincos_setters[g_n_sincos_setters++] = fn;
+    return g_n_sincos_setters;
+}
+int set_accurate_sincos(int on) {
+    for (int i = 0; i < g_n_sincos_setters; ++i) g_sincos_setters[i](on ? 0.0f : 1.0e6f);
+    return check_launch("set_accurate_sincos");
 }
 
 // implemented in the kernel translation units
@@ -65,7 +98,11 @@ int rbf_c32_dispatch(const float* x, int64_t n, int64_t d, float* c, int64_t num
 int unscale_to_f32(const double* z, int64_t count, double scale, float* c, cudaStream_t st);
 int cres_zzv_supported(int64_t m);
 int cres_zzv(const float* c, int64_t n, int64_t m, const double* vs, double* w, double scale, int fit_intercept,
-             cudaStream_t st);
+             const double* skip, cudaStream_t st);
+int cg_update_a(const double* w, const double* p, double* x, double* r, int64_t m, double lambda2, double* state,
+                double* hist, int64_t maxiter, cudaStream_t st);
+int cg_update_b(const double* r, const double* z, double* p, double* ps, int64_t m, double scale, int fit_intercept,
+                double* state, cudaStream_t st);
 int64_t ztzq_tc_workspace_bytes(int64_t n, int64_t m, int64_t r, int num_slices);
 int ztzq_accum_tc(const double* z, int64_t n, int64_t m, const double* q, int64_t r, double* acc, int num_slices,
                   int digit_bits, void* workspace, int64_t workspace_bytes, cudaStream_t st);
@@ -182,6 +219,7 @@ int xgpr_b200_ztz_accum_tc_f64(const double* z, int64_t n, int64_t m, double* zt
 int xgpr_b200_symmetrize_upper_f64(double* g, int64_t m, void* s) { return symmetrize_upper(g, m, ST(s)); }
 int xgpr_b200_tc_profile(int enable) { tc_profile(enable); return XGPR_B200_OK; }
 double xgpr_b200_tc_last_gemm_ms(void) { return tc_last_gemm_ms(); }
+int xgpr_b200_set_accurate_sincos(int on) { return set_accurate_sincos(on); }
 int64_t xgpr_b200_atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int num_slices) {
     return atb_tc_workspace_bytes(n, r, m, num_slices);
 }
@@ -199,7 +237,19 @@ int xgpr_b200_unscale_to_f32(const double* z, int64_t count, double scale, float
 int xgpr_b200_cres_zzv_supported(int64_t m) { return cres_zzv_supported(m); }
 int xgpr_b200_cres_zzv_f32(const float* c, int64_t n, int64_t m, const double* vs, double* w, double scale,
                            int fit_intercept, void* s) {
-    return cres_zzv(c, n, m, vs, w, scale, fit_intercept, ST(s));
+    return cres_zzv(c, n, m, vs, w, scale, fit_intercept, nullptr, ST(s));
+}
+int xgpr_b200_cres_zzv_gated_f32(const float* c, int64_t n, int64_t m, const double* vs, double* w, double scale,
+                                 int fit_intercept, const double* skip, void* s) {
+    return cres_zzv(c, n, m, vs, w, scale, fit_intercept, skip, ST(s));
+}
+int xgpr_b200_cg_update_a_f64(const double* w, const double* p, double* x, double* r, int64_t m, double lambda2,
+                              double* state, double* hist, int64_t maxiter, void* s) {
+    return cg_update_a(w, p, x, r, m, lambda2, state, hist, maxiter, ST(s));
+}
+int xgpr_b200_cg_update_b_f64(const double* r, const double* z, double* p, double* ps, int64_t m, double scale,
+                              int fit_intercept, double* state, void* s) {
+    return cg_update_b(r, z, p, ps, m, scale, fit_intercept, state, ST(s));
 }
 int64_t xgpr_b200_ztzq_tc_workspace_bytes(int64_t n, int64_t m, int64_t r, int num_slices) {
     return ztzq_tc_workspace_bytes(n, m, r, num_slices);

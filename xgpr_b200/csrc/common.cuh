@@ -14,6 +14,13 @@ namespace xb {
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
 int  check_launch(const char* what);   // cudaGetLastError -> XGPR_B200_ECUDA / OK
+// Raises a kernel's dynamic shared-memory limit ONCE per (kernel, device) -- and again only if a larger size is asked
+// for -- instead of a cudaFuncSetAttribute driver call on every launch.  No-op for sizes within the 48 KB default.
+void ensure_dyn_smem_impl(const void* kern, size_t bytes);
+int  current_device();                 // cudaGetDevice
+template <typename K> static inline void ensure_dyn_smem(K kern, size_t bytes) {
+    if (bytes > 48 * 1024) ensure_dyn_smem_impl(reinterpret_cast<const void*>(kern), bytes);
+}
 
 #define XB_REQUIRE(cond, msg)                      \
     do {                                           \

@@ -14,6 +14,7 @@
 
 #include <mutex>
 #include <unordered_map>
+#include <utility>
 
 namespace xb {
 
@@ -250,11 +251,14 @@ conv_cta_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __res
 // grow-only per-stream device buffer (no cudaMalloc / cudaFree per call, no blocking copy).
 struct SeqBuf { int32_t* dev = nullptr; size_t cap = 0; };
 static std::mutex g_seq_mu;
-static std::unordered_map<void*, SeqBuf> g_seq;
+// keyed by (device ordinal, stream): torch's default stream handle is 0 on EVERY device
+struct SeqKeyHash { size_t operator()(const std::pair<int, void*>& k) const {
+    return std::hash<void*>()(k.second) ^ (std::hash<int>()(k.first) * 0x9e3779b97f4a7c15ull); } };
+static std::unordered_map<std::pair<int, void*>, SeqBuf, SeqKeyHash> g_seq;
 
 static int stage_seqlen(const int32_t* host, int64_t n, cudaStream_t st, const int32_t** dev_out) {
     std::lock_guard<std::mutex> lk(g_seq_mu);
-    SeqBuf& b = g_seq[(void*)st];
+    SeqBuf& b = g_seq[std::make_pair(current_device(), (void*)st)];
     if (b.cap < (size_t)n) {
         if (b.dev) {
             cudaStreamSynchronize(st);
@@ -313,14 +317,13 @@ static int launch_conv_core(const T* x, int64_t n, int64_t m, int64_t c, void* o
     if (chi_bytes + x_bytes <= 100 * 1024) {
         const size_t smem = chi_bytes + x_bytes;
         auto kern = conv_core_kernel<T, P, E, MODE, WARPS, true>;
-        if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        ensure_dyn_smem(kern, smem);
         kern<<<grid, WARPS * 32, smem, st>>>(x, out, grad, radem, chi, seq_dev, (int)n, (int)m, (int)c, (int)F, R,
                                              reps, RC, conv_width, scaling_type, cn, fold, base_scale, sigma,
                                              tile_elems);
     } else {
         auto kern = conv_core_kernel<T, P, E, MODE, WARPS, false>;
-        if (chi_bytes > 48 * 1024)
-            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)chi_bytes);
+        ensure_dyn_smem(kern, chi_bytes);
         kern<<<grid, WARPS * 32, chi_bytes, st>>>(x, out, grad, radem, chi, seq_dev, (int)n, (int)m, (int)c, (int)F,
                                                   R, reps, RC, conv_width, scaling_type, cn, fold, base_scale,
                                                   sigma, 0);
@@ -374,7 +377,7 @@ int conv_dispatch(const T* x, int64_t n, int64_t m, int64_t c, void* out, int64_
         return XGPR_B200_EINVAL;
     }
     auto kern = conv_cta_kernel<T, MODE>;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ensure_dyn_smem(kern, smem);
     const int grid = (int)(n < 148 * 16 ? n : 148 * 16);
     kern<<<grid, 256, smem, st>>>(x, out, grad, radem, chi, seq_dev, (int)n, (int)m, (int)c, (int)P, (int)F, R,
                                   (int)reps64, conv_width, scaling_type, norm_constant<T>(P), base_scale, sigma);

@@ -157,7 +157,7 @@ static int launch_fht_cta2(T* x, int64_t n, const int8_t* radem, cudaStream_t st
     constexpr int64_t P = (int64_t)NS * 1024;
     const size_t smem = (size_t)P * sizeof(T);
     auto kern = fht_cta2_kernel<T, NS, SRHT>;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ensure_dyn_smem(kern, smem);
     int per_sm = (int)((220 * 1024) / smem);
     if (per_sm < 1) per_sm = 1;
     if (per_sm * 32 * NS > 2048) per_sm = 2048 / (32 * NS);
@@ -223,7 +223,7 @@ template <typename T, bool SRHT>
 static int launch_fht_cta(T* x, int64_t n, int64_t P, const int8_t* radem, cudaStream_t st) {
     const size_t smem = (size_t)P * sizeof(T);
     auto kern = fht_cta_kernel<T, SRHT>;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ensure_dyn_smem(kern, smem);
     int64_t blocks = n < 148 * 4 ? n : 148 * 4;
     kern<<<(unsigned)blocks, 512, smem, st>>>(x, radem, n, (int)P, norm_constant<T>(P));
     count_launch();

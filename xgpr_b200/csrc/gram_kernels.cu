@@ -5,8 +5,9 @@
 // src/xGPR/preconditioners/rand_nys_constructors.py:117-119).  All accumulate (+=) into
 // caller-owned fp64 device arrays so that chunks and (after an all-reduce) GPUs can be summed.
 //
-// Round-1 implementation: fp64 FMA-pipe kernels (exact analogue of the reference's DGEMM/DGEMV
-// arithmetic).  The tcgen05 split-precision Gram build is the next step.
+// fp64-pipe kernels (DFMA tiles and the DMMA multi-RHS matvec): the exact analogue of the reference's DGEMM/DGEMV
+// arithmetic.  The Gram-shaped products default to the tcgen05 split-int8 kernel in gram_tc_kernels.cu; these stay as
+// the gram="f64" path, the HBM-bound Z^T y, and the skinny matvecs.
 #include "common.cuh"
 
 namespace xb {

@@ -253,7 +253,7 @@ static int launch_core(const T* x, int64_t n, int64_t d, double* out, double* gr
     if (ITB > 8) ITB = 8;
     const size_t smem = 2 * ITB * row_bytes + (size_t)RC * K * CPITCH * sizeof(T);
     auto kern = rbf_core_kernel<T, P, E, GRAD, WARPS, C32>;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ensure_dyn_smem(kern, smem);
     const T c = norm_constant<T>(P);
     const T fold = is_pow4(P) ? (T)(c * c * c) : T(1);
     dim3 grid((unsigned)((n + rows_per_cta - 1) / rows_per_cta), (unsigned)rep_groups);
@@ -274,7 +274,7 @@ static int launch_cta(const T* x, int64_t n, int64_t d, int64_t P, double* out, 
         return XGPR_B200_EINVAL;
     }
     auto kern = rbf_cta_kernel<T, GRAD>;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ensure_dyn_smem(kern, smem);
     const int grid = (int)(n < 148 * 16 ? n : 148 * 16);
     kern<<<grid, 256, smem, st>>>(x, out, grad, radem, chi, (int)n, (int)d, (int)P, (int)F, R, reps,
                                   norm_constant<T>(P), scale, sigma);

@@ -367,7 +367,7 @@ static int launch_matvec(const T* x, int64_t n, int64_t d, const int8_t* radem, 
         return XGPR_B200_EINVAL;
     }
     auto kern = rbf_matvec_kernel<T, P, E, MODE, WARPS>;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ensure_dyn_smem(kern, smem);
     const T c = norm_constant<T>(P);
     const T fold = is_pow4(P) ? (T)(c * c * c) : T(1);
     dim3 grid((unsigned)((n + rows_per_cta - 1) / rows_per_cta), (unsigned)rep_groups);
@@ -419,7 +419,7 @@ static int launch_zzv(const T* x, int64_t n, int64_t d, const int8_t* radem, int
         return XGPR_B200_EINVAL;
     }
     auto kern = rbf_zzv_kernel<T, P, E, ZZV_WARPS>;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ensure_dyn_smem(kern, smem);
     const T c = norm_constant<T>(P);
     const T fold = is_pow4(P) ? (T)(c * c * c) : T(1);
     dim3 grid((unsigned)((n + rows_per_cta - 1) / rows_per_cta));

@@ -23,6 +23,8 @@
 
 namespace cg = cooperative_groups;
 
+#include <mutex>
+
 namespace xb {
 
 constexpr int CR_THREADS = 512;
@@ -50,7 +52,10 @@ unscale_to_f32_kernel(const double* __restrict__ z, int64_t count, double scale,
 template <int EPT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CR_THREADS, 1)
 cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict__ vs, double* __restrict__ w,
-                double scale, int fit_intercept, int64_t rows_per_cluster) {
+                double scale, int fit_intercept, int64_t rows_per_cluster, const double* __restrict__ skip) {
+    // gate for stream-ordered solvers (cg_kernels.cu): a non-zero *skip means "the solve has converged", and the launch
+    // becomes a no-op.  Both CTAs of a cluster read the same word, before any cluster barrier.
+    if (skip != nullptr && *skip != 0.0) return;
     constexpr int HC = CR_THREADS * EPT;                 // columns per CTA; m = 2 * HC
     constexpr int PCS = EPT / 4;                         // 16-byte pieces per thread per row
     constexpr int RB = cr_batch_rows(EPT);               // rows per batch = per cluster barrier
@@ -198,14 +203,15 @@ int cres_zzv_supported(int64_t m) { return (m == 4096 || m == 8192 || m == 16384
 
 template <int EPT>
 static int launch_cres(const float* c, int64_t n, const double* vs, double* w, double scale, int fit_intercept,
-                       cudaStream_t st) {
+                       const double* skip, cudaStream_t st) {
     constexpr int HC = CR_THREADS * EPT;
     constexpr int RB = cr_batch_rows(EPT);
     constexpr int SMEM = CR_STAGES * (RB / 2) * HC * 4 + (2 * RB * (CR_THREADS / 32) + 4 * RB) * 8;
     auto kern = cres_zzv_kernel<EPT>;
     static int clusters_dev[64] = {};                    // attribute + occupancy are per device
-    int dev_id = 0;
-    cudaGetDevice(&dev_id);
+    static std::mutex mu;
+    const int dev_id = current_device();
+    std::lock_guard<std::mutex> lk(mu);                  // several host threads may drive different GPUs
     int& clusters = clusters_dev[dev_id & 63];
     if (clusters == 0) {
         if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess)
@@ -230,22 +236,22 @@ static int launch_cres(const float* c, int64_t n, const double* vs, double* w, d
     int64_t rows_per = (n + nclusters - 1) / nclusters;
     rows_per = ((rows_per + RB - 1) / RB) * RB;
     nclusters = (n + rows_per - 1) / rows_per;
-    kern<<<(unsigned)(2 * nclusters), CR_THREADS, SMEM, st>>>(c, n, vs, w, scale, fit_intercept, rows_per);
+    kern<<<(unsigned)(2 * nclusters), CR_THREADS, SMEM, st>>>(c, n, vs, w, scale, fit_intercept, rows_per, skip);
     count_launch();
     return check_launch("cres_zzv_kernel");
 }
 
 // w (m) += Z^T (Z v), Z[i, j] = double(c[i, j]) * scale (column 0 = 1 when fit_intercept); vs = v * scale (vs[0] = v[0])
 int cres_zzv(const float* c, int64_t n, int64_t m, const double* vs, double* w, double scale, int fit_intercept,
-             cudaStream_t st) {
+             const double* skip, cudaStream_t st) {
     XB_REQUIRE(n > 0 && m > 0, "no datapoints");
     XB_REQUIRE(c && vs && w, "null pointer");
     XB_REQUIRE(cres_zzv_supported(m), "resident matvec: num_rffs must be 4096, 8192 or 16384");
     XB_REQUIRE((reinterpret_cast<uintptr_t>(c) & 15) == 0, "resident matvec: C must be 16-byte aligned");
     switch (m) {
-        case 4096: return launch_cres<4>(c, n, vs, w, scale, fit_intercept, st);
-        case 8192: return launch_cres<8>(c, n, vs, w, scale, fit_intercept, st);
-        default:   return launch_cres<16>(c, n, vs, w, scale, fit_intercept, st);
+        case 4096: return launch_cres<4>(c, n, vs, w, scale, fit_intercept, skip, st);
+        case 8192: return launch_cres<8>(c, n, vs, w, scale, fit_intercept, skip, st);
+        default:   return launch_cres<16>(c, n, vs, w, scale, fit_intercept, skip, st);
     }
 }
 

@@ -15,7 +15,22 @@ from ._native import lib, check
 _SFX = {torch.float32: "_f32", torch.float64: "_f64"}
 
 
+_ACCURATE = {"on": bool(int(__import__("os").environ.get("XGPR_B200_ACCURATE_SINCOS", "0") or 0)), "devices": set()}
+
+
+def set_accurate_sincos(on):
+    """float32 cos / sin of the feature kernels: False (default) = Cody-Waite + MUFU (<= ~6e-7 absolute), True = CUDA's
+    accurate sincosf.  Also selectable with XGPR_B200_ACCURATE_SINCOS=1.  The setting is a per-device constant: it is
+    (re)applied lazily to every device the next call launches on."""
+    _ACCURATE["on"] = bool(on)
+    _ACCURATE["devices"].clear()
+
+
 def _stream():
+    dev = torch.cuda.current_device()
+    if dev not in _ACCURATE["devices"]:
+        check(lib.xgpr_b200_set_accurate_sincos(int(_ACCURATE["on"])))
+        _ACCURATE["devices"].add(dev)
     return torch.cuda.current_stream().cuda_stream
 
 
@@ -176,16 +191,55 @@ def cres_zzv_supported(num_rffs):
     return bool(lib.xgpr_b200_cres_zzv_supported(int(num_rffs)))
 
 
-def cres_zzv(c, vs, w, scale, fitIntercept):
+def cres_zzv(c, vs, w, scale, fitIntercept, skip=None):
     """w (m) += Z^T (Z v) in one pass over the resident float32 encoding c of Z (Z = double(c) * scale, column 0 = 1 when
-    fitIntercept); vs = v * scale with vs[0] = v[0] when fitIntercept."""
+    fitIntercept); vs = v * scale with vs[0] = v[0] when fitIntercept.  skip: optional device double; the launch is a
+    no-op when it is non-zero (the convergence flag of the stream-ordered CG, cg_state()[5:6])."""
     c = _dev(c, "c", (torch.float32,), 2)
     vs = _dev(vs, "vs", (torch.float64,), 1)
     w = _dev(w, "w", (torch.float64,), 1)
     if vs.shape[0] != c.shape[1] or w.shape[0] != c.shape[1]:
         raise RuntimeError("wrong array sizes")
-    check(lib.xgpr_b200_cres_zzv_f32(c.data_ptr(), c.shape[0], c.shape[1], vs.data_ptr(), w.data_ptr(), float(scale),
-                                     int(bool(fitIntercept)), _stream()))
+    if skip is None:
+        check(lib.xgpr_b200_cres_zzv_f32(c.data_ptr(), c.shape[0], c.shape[1], vs.data_ptr(), w.data_ptr(), float(scale),
+                                         int(bool(fitIntercept)), _stream()))
+        return
+    skip = _dev(skip, "skip", (torch.float64,), 1)
+    check(lib.xgpr_b200_cres_zzv_gated_f32(c.data_ptr(), c.shape[0], c.shape[1], vs.data_ptr(), w.data_ptr(),
+                                           float(scale), int(bool(fitIntercept)), skip.data_ptr(), _stream()))
+
+
+CG_STATE_LEN = 8          # [r.z, ||r0||, tol, alpha, beta, done, iterations when done, iteration counter]
+
+
+def cg_update_a(w, p, x, r, lambda2, state, hist):
+    """First half of a device-resident CG iteration (include/xgpr_b200.h): alpha, x += alpha p, residual history,
+    r -= alpha (w + lambda2 p), convergence flag.  All arguments are fp64 CUDA vectors; nothing synchronises."""
+    for nm, t in (("w", w), ("p", p), ("x", x), ("r", r), ("state", state), ("hist", hist)):
+        _dev(t, nm, (torch.float64,), 1)
+    m = w.shape[0]
+    if p.shape[0] != m or x.shape[0] != m or r.shape[0] != m or state.shape[0] < CG_STATE_LEN:
+        raise RuntimeError("wrong array sizes")
+    check(lib.xgpr_b200_cg_update_a_f64(w.data_ptr(), p.data_ptr(), x.data_ptr(), r.data_ptr(), m, float(lambda2),
+                                        state.data_ptr(), hist.data_ptr(), hist.shape[0], _stream()))
+
+
+def cg_update_b(r, z, p, state, ps=None, scale=1.0, fitIntercept=False):
+    """Second half: beta = r.z / (r.z)_old, p = z + beta p, and (optionally) ps = p * scale with ps[0] = p[0] when
+    fitIntercept -- the scaled direction cres_zzv consumes."""
+    for nm, t in (("r", r), ("z", z), ("p", p), ("state", state)):
+        _dev(t, nm, (torch.float64,), 1)
+    m = r.shape[0]
+    if z.shape[0] != m or p.shape[0] != m or state.shape[0] < CG_STATE_LEN:
+        raise RuntimeError("wrong array sizes")
+    psp = 0
+    if ps is not None:
+        _dev(ps, "ps", (torch.float64,), 1)
+        if ps.shape[0] != m:
+            raise RuntimeError("wrong array sizes")
+        psp = ps.data_ptr()
+    check(lib.xgpr_b200_cg_update_b_f64(r.data_ptr(), z.data_ptr(), p.data_ptr(), psp, m, float(scale),
+                                        int(bool(fitIntercept)), state.data_ptr(), _stream()))
 
 
 def cudaRBFGrad(inputArr, outputArr, gradArr, radem, chiArr, sigma, fitIntercept):

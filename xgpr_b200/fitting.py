@@ -23,6 +23,7 @@ reference.
 fails loudly on non-CUDA tensors.  Tests inject an oracle-backed provider to run the host logic under
 ``gloo`` on CPU.
 """
+import os
 import warnings
 
 import numpy as np
@@ -35,19 +36,21 @@ from . import ext as _cuda_ops
 class RowShardComm:
     """Thin wrapper over torch.distributed for the row-sharded reductions (no-op when world size is 1)."""
 
-    def __init__(self, group=None):
+    def __init__(self, group=None, single=False):
         import torch.distributed as dist
-        self.dist = dist if (dist.is_available() and dist.is_initialized()) else None
+        self.dist = dist if (dist.is_available() and dist.is_initialized() and not single) else None
         self.group = group
         self.world = self.dist.get_world_size(group) if self.dist else 1
         self.rank = self.dist.get_rank(group) if self.dist else 0
         self.n_allreduce = 0
+        self.bytes_allreduce = 0
 
     def all_reduce_(self, *tensors):
         """In-place sum over ranks.  Several small tensors are flattened into ONE call (latency-bound)."""
         if self.world == 1:
             return
         self.n_allreduce += 1
+        self.bytes_allreduce += sum(t.numel() * t.element_size() for t in tensors)
         if len(tensors) == 1:
             self.dist.all_reduce(tensors[0], group=self.group)
             return
@@ -170,6 +173,10 @@ def _transformed_xy_chunks(dataset, kernel):
         yield z, to_device(yin, torch.float64)
 
 
+def _as_f64(y):
+    return y.astype(np.float64) if isinstance(y, np.ndarray) else y
+
+
 def _available_hbm(dev):
     """Bytes a new allocation can use: free device memory plus what torch's caching allocator holds but is not using."""
     free, _ = torch.cuda.mem_get_info(dev)
@@ -191,10 +198,15 @@ def calc_zty(dataset, kernel, comm=None, ops=_cuda_ops):
     dev = _device_of(kernel)
     z_trans_y, y_trans_y = _new((kernel.get_num_rffs(),), dev), _new((1,), dev)
     if _fused_ok(kernel, ops):
-        from .kernels.base import to_device
-        for xin, yin, _ in dataset.get_chunked_data():
-            y = to_device(yin, torch.float64).contiguous()
-            kernel.fused_ztv(kernel.stage_scaled(xin), y, z_trans_y)
+        # fused featurise -> Z^T y: the features are regenerated in registers and never written (rbf_ztv); the next
+        # chunk's x and y are copied under this chunk's kernel (stage_stream)
+        def chunks():
+            for xin, yin, ldata in dataset.get_chunked_data():
+                yield xin, ldata, yin
+
+        for xin, _, (y,) in kernel.stage_stream(chunks(), extra=lambda item: (_as_f64(item[2]),)):
+            y = y.to(torch.float64).contiguous()
+            kernel.fused_ztv(kernel.scale_staged(xin), y, z_trans_y)
             y_trans_y += y @ y
         comm.all_reduce_(z_trans_y, y_trans_y)
         return z_trans_y, float(y_trans_y[0])
@@ -276,6 +288,22 @@ def calc_variance_exact(kernel, dataset, variance_rffs, comm=None, ops=_cuda_ops
 
 
 # ----------------------------------------------------------------------------------------- conjugate gradients
+_TOKENS = iter(range(1, 1 << 62))
+
+
+def _token(obj):
+    """A process-unique token stored ON the object: unlike id(), it is never reused for a different object after the
+    first one is garbage collected (a tuning loop rebuilding datasets / kernels would otherwise be served stale features)."""
+    tok = getattr(obj, "_xb_token", None)
+    if tok is None:
+        tok = next(_TOKENS)
+        try:
+            obj._xb_token = tok
+        except AttributeError:              # objects without a __dict__: fall back to a weak identity
+            return ("id", id(obj))
+    return tok
+
+
 class ConjugateGrad:
     """Batched-RHS preconditioned CG on (Z^T Z + lambda^2 I).  cg_tools.py:15-156 (GPU_ConjugateGrad)."""
 
@@ -288,13 +316,18 @@ class ConjugateGrad:
         self._resident_c = None
         self.keep_resident = True
         self.one_pass = True
+        # one right-hand side on the GPU: scalar recurrences on the device, no per-iteration host sync (_fit_device)
+        self.device_cg = os.environ.get("XGPR_B200_DEVICE_CG", "1") != "0"
+        self.use_graph = os.environ.get("XGPR_B200_CG_GRAPH", "1") != "0"
+        self.poll_lag = 2
+        self.last_fit_info = {}
 
     def _staged_blocks(self, dataset, kernel, budget_bytes=8 << 30):
         """The sigma-scaled device copies of the shard's x blocks for the fused passes.  x * sigma does not change during
         a fit, so the copies (4 * D bytes per row; 256 MB for cfg2's 1M x 64) are staged ONCE and reused by every CG
         iteration -- with a device-resident shard as one block, i.e. two launches per iteration -- unless they would
         exceed `budget_bytes`, in which case each chunk is staged per pass as before."""
-        key = (id(dataset), id(kernel), float(kernel.get_hyperparams(logspace=False)[1]))
+        key = (_token(dataset), _token(kernel), float(kernel.get_hyperparams(logspace=False)[1]))
         if self._staged is not None and self._staged[0] == key:
             return self._staged[1]
         xdata = dataset._xdata
@@ -352,7 +385,7 @@ class ConjugateGrad:
         `fraction` of the free HBM; None otherwise (the fused regenerate-per-iteration kernels are used instead)."""
         if not self.keep_resident or not getattr(kernel, "resident_ok", lambda: False)():
             return None
-        key = (id(dataset), id(kernel), tuple(np.asarray(kernel.get_hyperparams(logspace=False)).tolist()))
+        key = (_token(dataset), _token(kernel), tuple(np.asarray(kernel.get_hyperparams(logspace=False)).tolist()))
         if self._resident_c is not None and self._resident_c[0] == key:
             return self._resident_c[1]
         self._resident_c = None
@@ -387,7 +420,7 @@ class ConjugateGrad:
         the whole shard's Z (8 M bytes per row) fits in `fraction` of the free HBM it is generated ONCE and kept resident
         for every iteration (cfg5 on 8 GPUs: 250k rows x 32,768 RFFs = 65 GB of 180 GB); otherwise it is regenerated per
         iteration, as the reference does (cg_tools.py:42-44)."""
-        key = (id(dataset), id(kernel), tuple(np.asarray(kernel.get_hyperparams(logspace=False)).tolist()))
+        key = (_token(dataset), _token(kernel), tuple(np.asarray(kernel.get_hyperparams(logspace=False)).tolist()))
         if self._resident is not None and self._resident[0] == key:
             yield from self._resident[1]
             return
@@ -405,8 +438,126 @@ class ConjugateGrad:
         if keep is not None:
             self._resident = (key, keep)
 
+    # ---- one right-hand side, device-resident recurrences -----------------------------------------------------------
+    def _device_cg_ok(self, kernel, resid, nmll_settings):
+        return (self.device_cg and self.ops is _cuda_ops and not nmll_settings and resid.shape[2] == 1 and resid.is_cuda
+                and kernel.device == "cuda" and _fused_ok(kernel, self.ops))
+
+    def _fit_device(self, dataset, kernel, preconditioner, resid, maxiter, tol, verbose):
+        """cg_tools.py:57-156 for one right-hand side with NO host round trip inside the loop.  Per iteration, all on the
+        current stream: [memset w, matvec kernel(s), ONE all-reduce of w, cg_update_a, two preconditioner GEMVs (+ one
+        scaling), cg_update_b] -- alpha, beta, the residual history and the convergence flag stay in a device `state`
+        (csrc/cg_kernels.cu).  After one eager iteration (cuBLAS / NCCL / kernel attributes initialised) the iteration is
+        captured ONCE in a CUDA graph and replayed.  The host reads the convergence flag with a fixed lag of `poll_lag`
+        iterations (8-byte async copies into pinned memory), so the GPU always has the next iteration queued; iterations
+        launched after convergence are no-ops on the device (the resident matvec is gated on the flag as well), hence x, the
+        iteration count and the loss history are exactly those of stopping at the right iteration.  With several ranks
+        every rank sees bit-identical all-reduced w, takes the same decision at the same iteration, and so issues the same
+        number of collectives."""
+        ops = self.ops
+        dev, m = resid.device, resid.shape[0]
+        lam2 = float(kernel.get_lambda()) ** 2
+        r = resid[:, 0, 0].clone().contiguous()
+        x, w = torch.zeros(m, dtype=torch.float64, device=dev), torch.zeros(m, dtype=torch.float64, device=dev)
+        z, p, ps = torch.empty_like(r), torch.empty_like(r), torch.empty_like(r)
+        state = torch.zeros(ops.CG_STATE_LEN, dtype=torch.float64, device=dev)
+        hist = torch.zeros(maxiter, dtype=torch.float64, device=dev)
+        skip = state[5:6]
+        if preconditioner is not None:
+            u_mat = preconditioner.u_mat
+            coef = (preconditioner.inv_eig * preconditioner.prefactor - 1.0).contiguous()
+            tsm = torch.empty(u_mat.shape[1], dtype=torch.float64, device=dev)
+
+        def apply_precond():                 # z = P^-1 r = r + U ((inv_eig * prefactor - 1) o (U^T r)); batch_matvec
+            if preconditioner is None:
+                z.copy_(r)
+                return
+            torch.mv(u_mat.T, r, out=tsm)
+            tsm.mul_(coef)
+            torch.addmv(r, u_mat, tsm, out=z)
+
+        resident = self._resident_encoding(dataset, kernel)
+        scale, icpt = kernel.feature_scale(), kernel.fit_intercept
+        one_pass = self.one_pass and getattr(kernel, "fused_zzv_ok", lambda: False)()
+        blocks = None if resident is not None else list(self._staged_blocks(dataset, kernel))
+
+        def iteration():
+            w.zero_()
+            if resident is not None:
+                kernel.resident_zzv_scaled(resident, ps, w, skip)
+            else:
+                for xs, t in blocks:
+                    if one_pass:
+                        kernel.fused_zzv(xs, p, w)
+                    else:
+                        t.zero_()
+                        kernel.fused_zv(xs, p, t)
+                        kernel.fused_ztv(xs, t, w)
+            self.comm.all_reduce_(w)
+            ops.cg_update_a(w, p, x, r, lam2, state, hist)
+            apply_precond()
+            ops.cg_update_b(r, z, p, state, ps, scale, icpt)
+
+        apply_precond()
+        p.copy_(z)
+        torch.mul(p, scale, out=ps)
+        if icpt:
+            ps[0:1].copy_(p[0:1])
+        state[0:1].copy_((r * z).sum().reshape(1))
+        state[1:2].copy_(torch.linalg.norm(r).reshape(1))
+        state[2:3].fill_(float(tol))
+
+        lag = max(1, int(self.poll_lag))
+        flags = torch.zeros(lag + 2, dtype=torch.float64).pin_memory()
+        events = [torch.cuda.Event() for _ in range(lag + 2)]
+        graph, launched, graphed = None, 0, False
+        for k in range(maxiter):
+            if k >= lag:
+                slot = (k - lag) % (lag + 2)
+                events[slot].synchronize()
+                if flags[slot] != 0.0:
+                    break
+            if k == 1 and self.use_graph and graph is None:
+                graph = self._capture(iteration)
+                graphed = graph is not None
+            if graph is not None and k >= 1:
+                graph.replay()
+            else:
+                iteration()
+            slot = k % (lag + 2)
+            flags[slot:slot + 1].copy_(skip, non_blocking=True)
+            events[slot].record()
+            launched += 1
+        st = state.cpu()
+        done = bool(st[5] != 0.0)
+        niter = int(st[6]) if done else launched
+        losses = hist[:niter].cpu().tolist()
+        self.last_fit_info = {"device_cg": True, "cuda_graph": graphed, "iterations_launched": launched,
+                              "resident": resident is not None}
+        if verbose:
+            print(f"{niter} iterations complete.")
+        return x, done, niter, losses
+
+    @staticmethod
+    def _capture(iteration):
+        """One CG iteration as a CUDA graph (NCCL's all-reduce is capturable); None if capture is not possible."""
+        try:
+            graph = torch.cuda.CUDAGraph()
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.graph(graph, stream=side, capture_error_mode="thread_local"):
+                iteration()
+            torch.cuda.current_stream().wait_stream(side)
+            return graph
+        except Exception as exc:             # keep the stream-ordered eager launches
+            warnings.warn(f"CUDA-graph capture of the CG iteration failed ({exc}); launching eagerly.")
+            return None
+
     def fit(self, dataset, kernel, preconditioner, resid, maxiter=200, tol=1e-4, verbose=True,
             nmll_settings=False):
+        if self._device_cg_ok(kernel, resid, nmll_settings):
+            return self._fit_device(dataset, kernel, preconditioner, resid, maxiter, tol, verbose)
+        self.last_fit_info = {"device_cg": False}
         converged = False
         target = resid[:, 0, :].clone()
         init_norms = torch.linalg.norm(target, dim=0)
@@ -458,10 +609,10 @@ class ConjugateGrad:
 
 
 def cg_fit_lib_internal(kernel, dataset, cg_tol=1e-4, max_iter=500, preconditioner=None, verbose=True,
-                        comm=None, ops=_cuda_ops):
+                        comm=None, ops=_cuda_ops, cg_operator=None):
     """cg_fitting_toolkit.py:18-70: rhs = Z^T y / N, zero start, result * N."""
     comm = comm or RowShardComm()
-    cg_operator = ConjugateGrad(comm, ops)
+    cg_operator = cg_operator or ConjugateGrad(comm, ops)
     if preconditioner is None:
         z_trans_y, _ = calc_zty(dataset, kernel, comm, ops)
     else:
@@ -649,14 +800,29 @@ class RandNysPreconditioner:
 
 # ----------------------------------------------------------------------------------------- predict
 def predict(kernel, weights, input_x, sequence_lengths=None, chunk_size=2000, trainy_mean=0.0, trainy_std=1.0,
-            var=None, variance_rffs=None):
-    """xgp_regression.py:105-134: (Z * w).sum(1), de-standardised; optional exact variance (:120-126)."""
+            var=None, variance_rffs=None, ops=_cuda_ops):
+    """xgp_regression.py:105-134: (Z * w).sum(1), de-standardised; optional exact variance (:120-126).
+
+    Mean-only prediction with a fixed-vector SORF kernel never writes Z: every chunk goes through the fused
+    featurise-dot kernel (`rbf_zv`: t = Z w with the features regenerated in registers), so inference
+    moves 4 D bytes in and 8 bytes out per row instead of 8 M.  With a variance request (which needs the first
+    `variance_rffs` columns of Z) or any other kernel family the chunk's Z is materialised as in the reference."""
     preds, pvar = [], []
     lambda_ = kernel.get_lambda()
+
     def chunks():
         for i in range(0, input_x.shape[0], chunk_size):
             cutoff = min(i + chunk_size, input_x.shape[0])
             yield input_x[i:cutoff, ...], None if sequence_lengths is None else sequence_lengths[i:cutoff]
+
+    if var is None and sequence_lengths is None and kernel.device == "cuda" and _fused_ok(kernel, ops):
+        w = weights.to(torch.float64).contiguous()
+        for xc, _ in chunks():
+            xs = kernel.stage_scaled(xc)
+            t = torch.zeros(xs.shape[0], dtype=torch.float64, device=xs.device)
+            kernel.fused_zv(xs, w, t)
+            preds.append(t)
+        return torch.cat(preds).cpu().numpy() * trainy_std + trainy_mean
 
     stream = getattr(kernel, "transform_stream", None)
     zs = stream(chunks()) if stream is not None and kernel.device == "cuda" else \

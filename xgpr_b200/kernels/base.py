@@ -11,6 +11,8 @@ argument meaning and error behaviour.  Differences, all forced by "no CuPy, no C
   * inputs may also be (pinned) host torch tensors or CUDA tensors, so datasets can stay resident.
 """
 import abc
+import functools
+import inspect
 
 import numpy as np
 import torch
@@ -57,6 +59,39 @@ class KernelBaseclass(abc.ABC):
         self._xdim = xdim
         self.hyperparams = None
         self.bounds = None
+
+    def __init_subclass__(cls, **kwargs):
+        """Records the arguments of the OUTERMOST constructor call (the registered class's signature,
+        model_baseclass.py:302-305) so that `with_num_rffs` can rebuild the kernel the way the reference's
+        `num_rffs` setter does."""
+        super().__init_subclass__(**kwargs)
+        init = cls.__dict__.get("__init__")
+        if init is None:
+            return
+
+        @functools.wraps(init)
+        def wrapped(self, *args, **kw):
+            if not hasattr(self, "_ctor_call"):
+                self._ctor_call = (cls, args, dict(kw))
+            init(self, *args, **kw)
+        cls.__init__ = wrapped
+
+    def with_num_rffs(self, num_rffs):
+        """A fresh kernel of the same class, xdim, seed, precision, settings, device, hyperparameters and bounds with a
+        different number of random features -- what `model.num_rffs = value` does in the reference
+        (model_baseclass.py:528-540 -> _initialize_kernel :263-321)."""
+        cls, args, kw = self._ctor_call
+        bound = inspect.signature(cls.__init__).bind(self, *args, **kw)
+        bound.arguments["num_rffs"] = int(num_rffs)
+        bound.arguments["device"] = self.device
+        params = dict(bound.arguments)
+        params.pop("self", None)
+        new = cls(**params)
+        if self.bounds is not None:
+            new.bounds = np.array(self.bounds, copy=True)
+        if self.hyperparams is not None:
+            new.set_hyperparams(np.array(self.hyperparams, copy=True), logspace=False)
+        return new
 
     # ---- hooks every kernel implements
     @abc.abstractmethod
@@ -150,13 +185,13 @@ class KernelBaseclass(abc.ABC):
             xtrans[:, 0] = 1.0
         return xtrans
 
-    def transform_stream(self, chunks):
-        """transform_x over an iterable of (input_x, sequence_length) chunks, double-buffered: the host->device copy of
-        chunk i+1 is issued on a side stream before chunk i's kernels are launched, so the copy (pinned memory: fully
-        asynchronous; pageable: staged by the driver) runs under the previous chunk's feature generation.  Yields exactly
-        what transform_x(input_x, sequence_length) returns, in order.  This is how the L4 chunk loops of the reference
-        (`for xdata, ldata in dataset.get_chunked_x_data(): kernel.transform_x(xdata, ldata)`, e.g.
-        fitting_toolkit/cg_tools.py:40-44) are meant to be driven when the dataset lives on the host."""
+    def stage_stream(self, chunks, extra=None):
+        """Double-buffered staging of an iterable of (input_x, sequence_length[, ...]) chunks: the host->device copy of
+        chunk i+1 is issued on a side stream before chunk i is handed to the caller, so the copy (pinned memory: fully
+        asynchronous; pageable: staged by the driver) runs under the caller's kernels on chunk i.  Yields
+        (device copy of input_x in the FHT dtype, host int32 sequence lengths or None, extra(item) staged the same way or
+        None); the current stream has already been made to wait for the copies.  `extra` maps a chunk tuple to further
+        host arrays to stage alongside (e.g. y), returned as a tuple of device tensors."""
         if self.device != "cuda":
             raise RuntimeError("xgpr_b200 generates features on device='cuda' only (no CPU fallback).")
         side = getattr(self, "_copy_stream", None)
@@ -164,16 +199,25 @@ class KernelBaseclass(abc.ABC):
             side = self._copy_stream = torch.cuda.Stream()
 
         def stage(item):
-            input_x, seqlen = item
+            input_x, seqlen = item[0], item[1]
             main = torch.cuda.current_stream()
-            if isinstance(input_x, torch.Tensor) and input_x.is_cuda:
-                return self._stage_input(input_x), seqlen, None
+            others = extra(item) if extra is not None else None
+            on_device = isinstance(input_x, torch.Tensor) and input_x.is_cuda
+            if on_device and others is None:
+                return self._stage_input(input_x), seqlen, None, None
+            if on_device:
+                side.wait_stream(main)                   # a device-resident input may have just been produced on `main`
             with torch.cuda.stream(side):
                 xin = self._stage_input(input_x)
+                staged = None
+                if others is not None:
+                    staged = tuple(to_device(o) for o in others)
                 done = torch.cuda.Event()
                 done.record(side)
             xin.record_stream(main)
-            return xin, seqlen, done
+            for t in staged or ():
+                t.record_stream(main)
+            return xin, seqlen, staged, done
 
         it = iter(chunks)
         try:
@@ -181,14 +225,23 @@ class KernelBaseclass(abc.ABC):
         except StopIteration:
             return
         while nxt is not None:
-            xin, seqlen, done = nxt
+            xin, seqlen, staged, done = nxt
             try:
                 nxt = stage(next(it))
             except StopIteration:
                 nxt = None
             if done is not None:
                 torch.cuda.current_stream().wait_event(done)
-            xtrans = self.kernel_specific_transform(xin, self._stage_seqlen(seqlen))
+            yield xin, self._stage_seqlen(seqlen), staged
+
+    def transform_stream(self, chunks):
+        """transform_x over an iterable of (input_x, sequence_length) chunks through `stage_stream` (next chunk's H2D under
+        this chunk's feature generation).  Yields exactly what transform_x(input_x, sequence_length) returns, in order.
+        This is how the L4 chunk loops of the reference (`for xdata, ldata in dataset.get_chunked_x_data():
+        kernel.transform_x(xdata, ldata)`, e.g. fitting_toolkit/cg_tools.py:40-44) are meant to be driven when the dataset
+        lives on the host."""
+        for xin, seqlen, _ in self.stage_stream(chunks):
+            xtrans = self.kernel_specific_transform(xin, seqlen)
             if self.fit_intercept:
                 xtrans[:, 0] = 1.0
             yield xtrans

@@ -64,6 +64,12 @@ class SORFKernelBaseclass(KernelBaseclass):
             return None
         return ext.scale_input_(xin, float(self.hyperparams[1]))
 
+    def scale_staged(self, xin):
+        """stage_scaled for an input that `stage_stream` already copied to the device (scaled in place)."""
+        if xin.shape[1] > 1024:
+            return None
+        return ext.scale_input_(xin, float(self.hyperparams[1]))
+
     def fused_zv(self, xs, v, t):
         ext.rbf_zv(xs, self.radem_diag, self.chi_arr, self.fit_intercept, v, t)
 
@@ -106,6 +112,11 @@ class SORFKernelBaseclass(KernelBaseclass):
         if self.fit_intercept:
             vs[0] = v[0]
         ext.cres_zzv(c, vs, w, scale, self.fit_intercept)
+
+    def resident_zzv_scaled(self, c, vs, w, skip=None):
+        """resident_zzv with the direction already scaled (vs = v * feature_scale(), vs[0] = v[0] with an intercept) and an
+        optional device-side gate: the form the stream-ordered CG uses (no temporaries, capturable in a CUDA graph)."""
+        ext.cres_zzv(c, vs, w, self.feature_scale(), self.fit_intercept, skip)
 
     def kernel_specific_gradient(self, input_x, sequence_length=None):
         output_x = torch.empty((input_x.shape[0], self.num_rffs), dtype=torch.float64, device=input_x.device)

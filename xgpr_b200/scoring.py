@@ -24,6 +24,7 @@ from . import ext as _cuda_ops
 from . import fitting
 from .fitting import RowShardComm, _device_of, _new
 
+MAX_RATIO_CHECK_RFFS = 8192                          # model_baseclass.py:470
 DEFAULT_SCORE_IF_PROBLEM = 1e40                      # constants.py:12
 DEFAULT_NMLL_PARAMS = {"max_rank": 1024, "preconditioner_mode": "srht_2", "nsamples": 25, "nmll_iter": 500,
                        "nmll_tol": 1e-6}             # constants.py:15-16
@@ -204,6 +205,11 @@ def check_rank_ratio(dataset, kernel, sample_frac, max_rank, random_seed=123, co
     if compressor_cls is None:
         from .kernels import SRHTCompressor as compressor_cls
     dev = _device_of(kernel)
+    # the reference runs this pass on min(num_rffs, 8192) random features: `self.num_rffs = min(self.num_rffs, 8192)`
+    # re-initialises the kernel (same class, seed, settings, hyperparameters) before srht_ratio_check and restores it
+    # afterwards (model_baseclass.py:465-474).  Same here, on a temporary kernel; the caller's kernel is untouched.
+    if kernel.get_num_rffs() > MAX_RATIO_CHECK_RFFS and hasattr(kernel, "with_num_rffs"):
+        kernel = kernel.with_num_rffs(MAX_RATIO_CHECK_RFFS)
     m = kernel.get_num_rffs()
     acc = _new((max_rank, m), dev)
     compressor = compressor_cls(max_rank, m, random_seed=random_seed, device=kernel.device)
