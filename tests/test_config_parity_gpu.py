@@ -28,9 +28,12 @@ from conftest import GOLDEN, load_golden, ref_ext
 
 pytestmark = pytest.mark.gpu
 
-# measured on B200 (profiles/r02_f32_parity.json): max |w - w_ref| / max |w_ref| and max |pred - pred_ref| / std(y)
-F32_WEIGHT_TOL = {"cfg1": 2e-3, "cfg2": 2e-3}
-F32_PRED_TOL = {"cfg1": 1e-4, "cfg2": 1e-4}
+# measured on B200 (profiles/r02a_f32_parity.json, tools/f32_parity_study.py): max |w - w_ref| / max |w_ref| is 2.7e-7
+# (cfg1) / 3.8e-7 (cfg2) with the default cos/sin and 4.6e-8 / 7.9e-8 with sincosf; max |pred - pred_ref| / std(y) is
+# 2.1e-7 / 1.2e-6 and 4.3e-8 / 2.0e-7.  The weight bound IS north_star's 1e-6; the prediction bound is 1e-6 where the
+# measurement allows it and 3e-6 for cfg2 in the default mode (1e-6 with accurate cos/sin, tested below).
+F32_WEIGHT_TOL = {"cfg1": 1e-6, "cfg2": 1e-6}
+F32_PRED_TOL = {"cfg1": 1e-6, "cfg2": 3e-6}
 
 
 def _rel(a, b):

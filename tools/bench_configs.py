@@ -83,6 +83,23 @@ def conv_case(name, cls, n, mlen, c, w, m, seq_lo, seq_hi, onehot=False, grad=Fa
            extra={"windows": wins, "freq_windows_per_s": wins * (m // 2) / (ms * 1e-3)})
 
 
+def ard_case(n=65536, d=128, m=8192):
+    """BASELINE config 5 (ii): MiniARD gradient features, 128 inputs -> 8,192 RFFs, two lengthscales; kernel only.
+    Algorithmic bytes per row = 4 D + 8 M (features) + 8 M L (gradient); flops = 2 D F for the dense W x product."""
+    name = f"cfg5 MiniARD grad {n}x{d} -> {m}, L=2 (kernel only)"
+    if ONLY and ONLY not in name:
+        return
+    k = MiniARD((n, d), m, device="cuda", kernel_spec_parms={"split_points": [64]})
+    k.set_hyperparams(np.log(np.asarray([0.277, 0.1, 0.07])), logspace=True)
+    k.precompute_weights()
+    x = torch.randn((n, d), dtype=torch.float32, device=dev)
+    out = torch.zeros((n, m), dtype=torch.float64, device=dev)
+    grad = torch.zeros((n, m, 2), dtype=torch.float64, device=dev)
+    ms = timeit(lambda: ext.cudaMiniARDGrad(x, out, k.precomputed_weights, k.ard_position_key, k.full_ard_weights,
+                                            grad, True), reps=3, warm=1)
+    report(name, n, ms, d * 4 + m * 8 * 3, flops=2.0 * n * d * (m // 2))
+
+
 def main():
     which = sys.argv[1:] or ["rbf", "conv", "gram", "misc"]
     if "rbf" in which:
@@ -92,6 +109,10 @@ def main():
         rbf_case("RBF grad 32768x64 -> 8192", 32768, 64, 8192, grad=True)
         rbf_case("RBF 8192x1024 -> 4096", 8192, 1024, 4096)
         rbf_case("RBF 4096x3001 -> 8192 (cta path)", 4096, 3001, 8192)
+        rbf_case("big cfg1-shape RBF 262144x512 -> 2048", 262144, 512, 2048)
+        rbf_case("big RBF 131072x1024 -> 4096", 131072, 1024, 4096)
+        rbf_case("big RBF 262144x256 -> 2048", 262144, 256, 2048)
+        rbf_case("big cta RBF 16384x3001 -> 8192 (cta path)", 16384, 3001, 8192)
     if "conv" in which:
         conv_case("cfg3 Conv1dRBF 2048x500x21 w9 -> 8192 (full length)", Conv1dRBF, 2048, 500, 21, 9, 8192, 500, 500, onehot=True)
         conv_case("cfg3 Conv1dRBF 2048x500x21 w9 -> 8192 (len 50..500)", Conv1dRBF, 2048, 500, 21, 9, 8192, 50, 500, onehot=True)
@@ -128,6 +149,7 @@ def main():
         x = torch.randn((1 << 20, 64), dtype=torch.float32, device=dev)
         ms = timeit(lambda: ext.cudaFastHadamardTransform2D(x))
         report("FHT f32 1Mx64 in place", 1 << 20, ms, 2 * 64 * 4)
+        ard_case()
         k = MiniARD((4096, 128), 8192, device="cuda", kernel_spec_parms={"split_points": [64]})
         xa = torch.randn((4096, 128), dtype=torch.float32, device=dev)
         ms = timeit(lambda: k.gradient_x(xa), reps=3, warm=1)
