@@ -165,11 +165,13 @@ int xgpr_b200_symmetrize_upper_f64(double* g, int64_t m, void* stream);
  * launching stream; xgpr_b200_tc_last_gemm_ms() synchronises on the last bracket and returns its duration (-1: none). */
 int    xgpr_b200_tc_profile(int enable);
 double xgpr_b200_tc_last_gemm_ms(void);
-/* Accuracy switch for the float32 cos / sin of every feature kernel, per device (applies to the CURRENT device): 0 (default)
- * = two-term Cody-Waite reduction + MUFU.SIN / MUFU.COS (abs. error <= ~6e-7); 1 = CUDA's accurate sincosf (<= 2 ulp, the
- * class of glibc's cosf / sinf the reference calls at cpu/shared_fht_functions/shared_rfgen_ops.cpp:107-112).  Measured
- * cost and effect on fitted weights: DESIGN.md section 2. */
-int    xgpr_b200_set_accurate_sincos(int on);
+/* Accuracy level of the float32 cos / sin of every feature kernel, per device (applies to the CURRENT device):
+ *   0 = two-term Cody-Waite reduction + MUFU.SIN / MUFU.COS (abs. error <= ~4e-7);
+ *   1 = pi/2 reduction + minimax polynomials on the FMA pipe (abs. error <= 7e-8: the class of glibc's cosf / sinf, which
+ *       the reference calls at cpu/shared_fht_functions/shared_rfgen_ops.cpp:107-112);
+ *   2 = CUDA's sincosf;   -1 = per-kernel-family defaults (fixed-vector RBF-family kernels: 1, convolution kernels: 0).
+ * Measured cost and effect on fitted weights: DESIGN.md section 2. */
+int    xgpr_b200_set_accurate_sincos(int level);
 /* Tensor-core sketch accumulation, same scheme: acc (r, m) += A^T Z, A (n, r), Z (n, m) fp64 row-major
  * (`acc_results += compressor.transform_x(xdata).T @ xdata`, src/xGPR/preconditioners/rand_nys_constructors.py:119). */
 int64_t xgpr_b200_atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int num_slices);

@@ -4,8 +4,8 @@ predictions from the REFERENCE's, and how much of that distance is the MUFU cos/
 glibc-vs-CUDA libm differences amplified by the conditioning of the solve?
 
 Runs cfg1 (full size, exact fit), cfg2 (20k-row subsample, 16,384 RFFs, preconditioned CG) and the small l3 float32
-fixture against the reference-generated fixtures, once with the default cos/sin (Cody-Waite + MUFU) and once with
-XGPR_B200_ACCURATE_SINCOS (CUDA sincosf), and times cfg2-shaped feature generation in both modes.
+fixture against the reference-generated fixtures at the three cos/sin levels of include/xgpr_b200.h (0 = Cody-Waite + MUFU,
+1 = polynomial on the FMA pipe, 2 = CUDA sincosf), and times cfg2-shaped feature generation at each level.
 
     python tools/f32_parity_study.py > profiles/r02_f32_parity.json
 """
@@ -116,10 +116,10 @@ def speed(rows=262144, reps=5):
 
 def main():
     res = {}
-    for mode, on in (("mufu", False), ("sincosf", True)):
+    for mode, on in (("mufu", 0), ("poly", 1), ("sincosf", 2)):
         ext.set_accurate_sincos(on)
         res[mode] = {"cfg1": cfg1(), "cfg2": cfg2(), "l3_rbf_f32": l3_small(), "cfg2_feature_gen": speed()}
-    ext.set_accurate_sincos(False)
+    ext.set_accurate_sincos(None)
     print(json.dumps(res, indent=1))
 
 

@@ -9,6 +9,7 @@
 // through shared memory in k-chunks (coalesced global reads, conflict-free smem reads); each thread
 // owns one (row, frequency) pair, keeps rf in a register and its L bucket sums in shared memory.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace xb {
 
@@ -76,6 +77,231 @@ ard_grad_kernel(const T* __restrict__ x, double* __restrict__ out, const T* __re
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Tensor-core version (fp64 DMMA, mma.sync.m8n8k4.f64 -- tcgen05 has no fp64 kind), L <= 3 lengthscales.
+//
+// The gradient features are a GEMM in disguise: with the input columns grouped by lengthscale,
+//   G_l[row, f] = sum_{k in group l} x[row, k] W[f, k]        (L skinny GEMMs over disjoint k ranges)
+//   rf[row, f]  = sum_k sigma_k x[row, k] W[f, k]             (= sum_l sigma_l G_l when sigma is constant on a group,
+//                                                               which is how MiniARD builds it, mini_ard.py:172-177)
+// A CTA owns 64 frequencies and walks row tiles of 64; x and W tiles are widened to fp64 ONCE when staged into shared
+// memory (the first kernel paid one F2F.F64.F32 per (row, f, k) triple on the 16-lane XU pipe), columns are permuted so
+// that each group is contiguous and padded to a multiple of 4 (the MMA's K), and every 4-column step feeds its group's
+// accumulator fragments.  8 warps x (2 x 4 fragments) = 64 x 64; accumulators stay in registers; the epilogue does the
+// double sincos and writes [cos, sin] and the 2 L gradient values of each (row, f) as 32- / 32 L-byte contiguous pieces.
+// Arithmetic vs the oracle (ard_ops.cpp:98-121): T = double -- the same products and sums up to fp64 summation order and
+// FMA contraction; T = float -- the oracle rounds each product x W to float before widening, here the product is exact
+// (<= 6e-8 relative per term closer to the true sum; measured feature deviation ~1e-7 of scale, inside the 1e-5 contract).
+constexpr int AM_ROWS = 64, AM_F = 64, AM_KC = 32, AM_LD = AM_KC + 4;      // row stride == 8 words (mod 32): LDS.64 clean
+
+__device__ __forceinline__ void ard_dmma(double (&c)[2], double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
+
+template <typename T, int NG>
+__global__ void __launch_bounds__(256, NG <= 2 ? 2 : 1)
+ard_mma_kernel(const T* __restrict__ x, double* __restrict__ out, const T* __restrict__ w,
+               const int32_t* __restrict__ sigma_map, const double* __restrict__ sigma_vals,
+               double* __restrict__ grad, int N, int D, int F, double scale, int npos_max) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double* xs = reinterpret_cast<double*>(smem_raw);            // [64][AM_LD]   x tile, fp64
+    double* xg = xs + AM_ROWS * AM_LD;                           // [64][AM_LD]   x * sigma (general-sigma path)
+    double* ws = xg + AM_ROWS * AM_LD;                           // [64][AM_LD]   W tile, fp64
+    double* sigp = ws + AM_F * AM_LD;                            // [npos_max]    sigma at each permuted position
+    int* perm = reinterpret_cast<int*>(sigp + npos_max);         // [npos_max]    permuted position -> column (-1 = padding)
+    int* kgrp = perm + npos_max;                                 // [npos_max/4]  group of each 4-column step
+    __shared__ int s_cnt[32][NG];                                // per 32-column chunk, per group: member count
+    __shared__ int s_start[NG + 1];
+    __shared__ double s_gsig[NG];
+    __shared__ int s_uniform;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g4 = lane >> 2, t4 = lane & 3;
+    const int wr = warp >> 1, wf = warp & 1;                     // warp tile: rows wr*16.., freqs wf*32..
+    const int f0 = blockIdx.x * AM_F;
+
+    // ---- column permutation: groups contiguous (ascending k inside a group), each padded to a multiple of 4
+    const int nchunk = (D + 31) / 32;                            // host guarantees D <= 1024
+    if (tid == 0) s_uniform = 1;
+    for (int c = warp; c < nchunk; c += 8) {
+        const int k = c * 32 + lane;
+        int mv = (k < D) ? sigma_map[k] : -1;
+        if (k < D) mv = mv < 0 ? 0 : (mv >= NG ? NG - 1 : mv);
+#pragma unroll
+        for (int g = 0; g < NG; ++g) {
+            const unsigned b = __ballot_sync(0xffffffffu, mv == g);
+            if (lane == 0) s_cnt[c][g] = __popc(b);
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int pos = 0;
+        for (int g = 0; g < NG; ++g) {
+            s_start[g] = pos;
+            for (int c = 0; c < nchunk; ++c) { const int n = s_cnt[c][g]; s_cnt[c][g] = pos; pos += n; }
+            pos = (pos + 3) & ~3;
+        }
+        s_start[NG] = pos;
+    }
+    for (int i = tid; i < npos_max; i += 256) { perm[i] = -1; sigp[i] = 0.0; }
+    __syncthreads();
+    for (int c = warp; c < nchunk; c += 8) {
+        const int k = c * 32 + lane;
+        int mv = (k < D) ? sigma_map[k] : -1;
+        if (k < D) mv = mv < 0 ? 0 : (mv >= NG ? NG - 1 : mv);
+#pragma unroll
+        for (int g = 0; g < NG; ++g) {
+            const unsigned b = __ballot_sync(0xffffffffu, mv == g);
+            if (mv == g) {
+                const int pos = s_cnt[c][g] + __popc(b & ((1u << lane) - 1u));
+                perm[pos] = k;
+                sigp[pos] = sigma_vals[k];
+            }
+        }
+    }
+    __syncthreads();
+    const int npos = s_start[NG];
+    for (int i = tid; i < npos / 4; i += 256) {
+        int g = 0;
+#pragma unroll
+        for (int q = 1; q < NG; ++q) g += (4 * i >= s_start[q]) ? 1 : 0;
+        kgrp[i] = g;
+    }
+    if (tid < NG) {                                              // sigma constant on the group?  (MiniARD: always)
+        const int beg = s_start[tid], end = s_start[tid + 1];
+        double sv = 0.0;
+        bool have = false, uni = true;
+        for (int i = beg; i < end; ++i)
+            if (perm[i] >= 0) {
+                if (!have) { sv = sigp[i]; have = true; }
+                else if (sigp[i] != sv) uni = false;
+            }
+        s_gsig[tid] = sv;
+        if (!uni) s_uniform = 0;
+    }
+    __syncthreads();
+    const bool uniform = s_uniform != 0;
+    const int nsteps_total = npos / 4;
+
+    for (int rt = blockIdx.y; rt * AM_ROWS < N; rt += gridDim.y) {
+        const int r0 = rt * AM_ROWS;
+        double acc[NG][2][4][2], accr[2][4][2];
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    accr[i][j][e] = 0.0;
+#pragma unroll
+                    for (int g = 0; g < NG; ++g) acc[g][i][j][e] = 0.0;
+                }
+        for (int p0 = 0; p0 < npos; p0 += AM_KC) {
+            __syncthreads();                                     // previous chunk's fragments are consumed
+            for (int t = tid; t < AM_ROWS * AM_KC; t += 256) {
+                const int rr = t / AM_KC, kk = t % AM_KC;
+                const int col = (p0 + kk < npos) ? perm[p0 + kk] : -1;
+                const int gr = r0 + rr, gf = f0 + rr;
+                const double xv = (col >= 0 && gr < N) ? (double)x[(size_t)gr * D + col] : 0.0;
+                xs[rr * AM_LD + kk] = xv;
+                if (!uniform) xg[rr * AM_LD + kk] = xv * sigp[min(p0 + kk, npos_max - 1)];
+                ws[rr * AM_LD + kk] = (col >= 0 && gf < F) ? (double)w[(size_t)gf * D + col] : 0.0;
+            }
+            __syncthreads();
+            const int nsteps = min(AM_KC / 4, nsteps_total - p0 / 4);
+            for (int ks = 0; ks < nsteps; ++ks) {
+                const int grp = kgrp[p0 / 4 + ks];               // warp-uniform
+                double a[2], b[4];
+#pragma unroll
+                for (int i = 0; i < 2; ++i) a[i] = xs[(wr * 16 + i * 8 + g4) * AM_LD + ks * 4 + t4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) b[j] = ws[(wf * 32 + j * 8 + g4) * AM_LD + ks * 4 + t4];
+#pragma unroll
+                for (int g = 0; g < NG; ++g)
+                    if (grp == g) {
+#pragma unroll
+                        for (int i = 0; i < 2; ++i)
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) ard_dmma(acc[g][i][j], a[i], b[j]);
+                    }
+                if (!uniform) {
+#pragma unroll
+                    for (int i = 0; i < 2; ++i) {
+                        const double as = xg[(wr * 16 + i * 8 + g4) * AM_LD + ks * 4 + t4];
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) ard_dmma(accr[i][j], as, b[j]);
+                    }
+                }
+            }
+        }
+        // ---- epilogue: fragment element (g4, 2 t4 + e) of fragment (i, j)
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int row = r0 + wr * 16 + i * 8 + g4;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int f = f0 + wf * 32 + j * 8 + 2 * t4;     // f and f + 1
+                if (row >= N || f >= F) continue;
+                double cv[2], sv[2];
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    double rf = accr[i][j][e];
+                    if (uniform) {
+                        rf = 0.0;
+#pragma unroll
+                        for (int g = 0; g < NG; ++g) rf = fma(s_gsig[g], acc[g][i][j][e], rf);
+                    }
+                    double sn, cs;
+                    sincos(rf, &sn, &cs);
+                    cv[e] = scale * cs;
+                    sv[e] = scale * sn;
+                }
+                const bool two = (f + 1 < F);
+                double* o = out + (size_t)row * 2 * F + 2 * f;
+                if (two) {
+                    reinterpret_cast<double2*>(o)[0] = make_double2(cv[0], sv[0]);
+                    reinterpret_cast<double2*>(o)[1] = make_double2(cv[1], sv[1]);
+                } else {
+                    o[0] = cv[0];
+                    o[1] = sv[0];
+                }
+                double* gp = grad + ((size_t)row * 2 * F + 2 * f) * NG;
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    if (e == 1 && !two) break;
+#pragma unroll
+                    for (int g = 0; g < NG; ++g) {
+                        // grad += on a caller-zeroed array, then rescaled (ard_ops.cpp:100,117-121)
+                        const double gv = __dadd_rn(gp[e * 2 * NG + g], acc[g][i][j][e]);
+                        gp[e * 2 * NG + g] = -gv * sv[e];
+                        gp[e * 2 * NG + NG + g] = gv * cv[e];
+                    }
+                }
+            }
+        }
+    }
+}
+
+template <typename T, int NG>
+static int launch_ard_mma(const T* x, int64_t n, int64_t d, double* out, const T* w, int64_t F, const int32_t* sigma_map,
+                          const double* sigma_vals, double* grad, double scale, cudaStream_t st) {
+    const int npos_max = (int)((d + 3) / 4 * 4 + 4 * NG);
+    const size_t smem = (size_t)(3 * AM_ROWS * AM_LD) * 8 + (size_t)npos_max * 8 + (size_t)npos_max * 4 +
+                        (size_t)(npos_max / 4 + 1) * 4;
+    auto kern = ard_mma_kernel<T, NG>;
+    ensure_dyn_smem(kern, smem);
+    const int64_t ftiles = (F + AM_F - 1) / AM_F, rtiles = (n + AM_ROWS - 1) / AM_ROWS;
+    // each CTA keeps its column permutation and walks row tiles: ~8 CTAs per SM slot in flight over the whole grid
+    int64_t gy = (148 * 2 * 8 + ftiles - 1) / ftiles;
+    if (gy > rtiles) gy = rtiles;
+    if (gy < 1) gy = 1;
+    if (gy > 65535) gy = 65535;
+    dim3 grid((unsigned)ftiles, (unsigned)gy);
+    kern<<<grid, 256, smem, st>>>(x, out, w, sigma_map, sigma_vals, grad, (int)n, (int)d, (int)F, scale, npos_max);
+    count_launch();
+    return check_launch("ard_mma_kernel");
+}
+
 template <typename T>
 int ard_dispatch(const T* x, int64_t n, int64_t d, double* out, const T* w, int64_t F,
                  const int32_t* sigma_map, const double* sigma_vals, double* grad, int64_t L,
@@ -85,6 +311,15 @@ int ard_dispatch(const T* x, int64_t n, int64_t d, double* out, const T* w, int6
     XB_REQUIRE(d > 0 && F > 0 && L > 0, "Wrong array sizes.");
     XB_REQUIRE(x && out && w && sigma_map && sigma_vals && grad, "null pointer");
     XB_REQUIRE(n < (1ll << 31) && F < (1ll << 30), "array too large");
+    // the constant is declared T (ard_ops.cpp:87-92)
+    const double ff0 = (double)F;
+    const double scale0 = (double)(T)(fit_intercept ? sqrt(1.0 / (ff0 - 0.5)) : sqrt(1.0 / ff0));
+    static const bool simt_only = getenv("XGPR_B200_ARD_SIMT") != nullptr;
+    if (L <= 3 && d <= 1024 && F < (1ll << 26) && !simt_only) {      // fp64 tensor-core path
+        if (L == 1) return launch_ard_mma<T, 1>(x, n, d, out, w, F, sigma_map, sigma_vals, grad, scale0, st);
+        if (L == 2) return launch_ard_mma<T, 2>(x, n, d, out, w, F, sigma_map, sigma_vals, grad, scale0, st);
+        return launch_ard_mma<T, 3>(x, n, d, out, w, F, sigma_map, sigma_vals, grad, scale0, st);
+    }
     constexpr int TF = 32, TR = 8, KC = 32;
     const size_t smem = (size_t)L * TF * TR * 8 + KC * 8 + (size_t)KC * (TF + 1) * sizeof(T) +
                         (size_t)TR * KC * sizeof(T) + KC * 4;

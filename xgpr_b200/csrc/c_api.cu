@@ -44,16 +44,17 @@ void ensure_dyn_smem_impl(const void* kern, size_t bytes) {
     // on failure the launch that follows reports the error through check_launch
 }
 
-// accurate-sincos switch: every translation unit that includes sorf_core.cuh registers the setter of its own
-// __constant__ limit at static-initialisation time
-static void (*g_sincos_setters[16])(float) = {};
+// cos / sin accuracy switch: every translation unit that includes sorf_core.cuh registers the setter of its own
+// __constant__ limits at static-initialisation time
+static void (*g_sincos_setters[16])(int) = {};
 static int g_n_sincos_setters = 0;
-int register_sincos_limit_setter(void (*fn)(float)) {
+int register_sincos_limit_setter(void (*fn)(int)) {
     if (g_n_sincos_setters < 16) g_sincos_setters[g_n_sincos_setters++] = fn;
     return g_n_sincos_setters;
 }
-int set_accurate_sincos(int on) {
-    for (int i = 0; i < g_n_sincos_setters; ++i) g_sincos_setters[i](on ? 0.0f : 1.0e6f);
+int set_accurate_sincos(int level) {
+    if (level > 2) level = 2;
+    for (int i = 0; i < g_n_sincos_setters; ++i) g_sincos_setters[i](level);
     return check_launch("set_accurate_sincos");
 }
 

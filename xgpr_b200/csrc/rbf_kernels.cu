@@ -9,8 +9,10 @@
 // three sign-flip/FWHT rounds, the chi scale and cos/sin happen in registers (sorf_core.cuh), and the
 // interleaved fp64 [cos, sin] pairs leave through a padded per-warp shared-memory tile so that every
 // 128-bit global store of a warp covers whole 128-byte lines.  No scratch buffer, no per-call allocation.
+#define XB_SINCOS_DEFAULT_LEVEL 1   // HBM-bound fixed-vector kernels: polynomial cos / sin by default (sorf_core.cuh)
 #include "sorf_core.cuh"
 #include "sorf_warp.cuh"   // cta_sorf for P > 1024
+#include <stdlib.h>
 
 namespace xb {
 
@@ -29,8 +31,10 @@ __global__ void __launch_bounds__(WARPS * 32)
 rbf_core_kernel(const T* __restrict__ x, double* __restrict__ out, double* __restrict__ grad,
                 const int8_t* __restrict__ radem, const T* __restrict__ chi,
                 int N, int D, int F, int64_t R, int reps, int RC, int rows_per_cta, int ITB,
-                T cnorm, T fold, double scale, double sigma) {
+                T cnorm, T fold, double scale, double sigma, int vec16) {
     constexpr int K = P / E;
+    constexpr bool LINEAR = (K >= 16);                // natural-order input tile, 16-byte copies (sorf_core.cuh)
+    constexpr int XROW = LINEAR ? LinTile<T, P, E>::PITCH : K * ChiTile<T, E>::PITCH;   // tile elements per row
     constexpr int V = 32 / K;
     constexpr int S = WARPS * V;
     constexpr bool FOLD = is_pow4(P);
@@ -42,8 +46,8 @@ rbf_core_kernel(const T* __restrict__ x, double* __restrict__ out, double* __res
     const int nrl = S / RC;
     const int tile_rows = nrl * ITB;
     T* xt0 = reinterpret_cast<T*>(smem_raw);
-    T* xt1 = xt0 + (size_t)tile_rows * K * CPITCH;
-    T* chi_tile = xt1 + (size_t)tile_rows * K * CPITCH;
+    T* xt1 = xt0 + (size_t)tile_rows * XROW;
+    T* chi_tile = xt1 + (size_t)tile_rows * XROW;
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int sub = lane % K, q = lane / K;
@@ -60,7 +64,8 @@ rbf_core_kernel(const T* __restrict__ x, double* __restrict__ out, double* __res
     const int iters = (rows_per_cta + nrl - 1) / nrl;
     const int nbatch = (iters + ITB - 1) / ITB;
 
-    issue_x_tile<T, P, E>(xt0, x, row0, tile_rows, min(N, row0 + rows_per_cta), D);
+    if constexpr (LINEAR) issue_x_tile_linear<T, P, E>(xt0, x, row0, tile_rows, min(N, row0 + rows_per_cta), D, vec16 != 0);
+    else issue_x_tile<T, P, E>(xt0, x, row0, tile_rows, min(N, row0 + rows_per_cta), D);
     cp_async_commit();
     load_chi_tile<T, P, E>(chi_tile, chi, rep0, RC, reps, F, fold);
     SignBits<E> sg;
@@ -76,8 +81,12 @@ rbf_core_kernel(const T* __restrict__ x, double* __restrict__ out, double* __res
     for (int b = 0; b < nbatch; ++b) {
         T* cur = (b & 1) ? xt1 : xt0;
         if (b + 1 < nbatch) {
-            issue_x_tile<T, P, E>((b & 1) ? xt0 : xt1, x, row0 + (b + 1) * tile_rows, tile_rows,
-                                  min(N, row0 + rows_per_cta), D);
+            if constexpr (LINEAR)
+                issue_x_tile_linear<T, P, E>((b & 1) ? xt0 : xt1, x, row0 + (b + 1) * tile_rows, tile_rows,
+                                             min(N, row0 + rows_per_cta), D, vec16 != 0);
+            else
+                issue_x_tile<T, P, E>((b & 1) ? xt0 : xt1, x, row0 + (b + 1) * tile_rows, tile_rows,
+                                      min(N, row0 + rows_per_cta), D);
             cp_async_commit();
             cp_async_wait<1>();
         } else {
@@ -91,7 +100,8 @@ rbf_core_kernel(const T* __restrict__ x, double* __restrict__ out, double* __res
             const bool ok = rep_ok && (rl < rows_per_cta) && (row < N);
             if (it >= iters) break;                       // warp-uniform
             T v[E];
-            lds_chunk<E>(cur + ((ib * nrl + rowlane) * K + sub) * CPITCH, v);
+            if constexpr (LINEAR) lds_strided<T, E, K>(cur + (ib * nrl + rowlane) * XROW + sub, v);
+            else lds_chunk<E>(cur + ((ib * nrl + rowlane) * K + sub) * CPITCH, v);
             core_sorf<T, E, K, FOLD>(v, sg, sub, cnorm);
 
             double2* orow = reinterpret_cast<double2*>(out) + (size_t)row * F + base + sub;
@@ -220,6 +230,106 @@ rbf_cta_kernel(const T* __restrict__ x, double* __restrict__ out, double* __rest
 }
 
 // ---------------------------------------------------------------------------------------------
+// 2048 <= P <= 16384 (more than 1024 input features), v2: the scheme of fht_cta2_kernel applied to all three rounds.
+// One warp per 1024-element segment: strides 1..512 in registers + shuffles, ONE pass through shared memory, then every
+// thread finishes the NS = P / 1024 cross-segment strides in registers on {o + s * 1024}.  Two block barriers per round
+// instead of log2 P (cta_sorf above runs 11-14 per round and measured 0.19 of HBM, profiles/r02a_rbfcta_full.md); after
+// the third round the values are already spread thread-consecutively, so chi, cos / sin and the 16-byte [cos, sin] stores
+// follow directly, coalesced.  The zero-padded row is staged once per row and reused by every repeat.
+// Same butterflies in the same ascending-stride order, same one-rounding sign multiply as cta_sorf: bit-identical
+// pre-activations.
+template <typename T, int NS, bool GRAD>
+__global__ void __launch_bounds__(32 * NS)
+rbf_cta2_kernel(const T* __restrict__ x, double* __restrict__ out, double* __restrict__ grad,
+                const int8_t* __restrict__ radem, const T* __restrict__ chi,
+                int N, int D, int F, int64_t R, int reps, T cnorm, double scale, double sigma) {
+    constexpr int E = 32, K = 32, SEG = 1024, P = NS * SEG, THREADS = 32 * NS, GROUPS = SEG / THREADS;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T* xin = reinterpret_cast<T*>(smem_raw);
+    T* buf = xin + P;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int off = warp * SEG;
+    for (int row = blockIdx.x; row < N; row += gridDim.x) {
+        const T* xr = x + (size_t)row * D;
+        for (int j = threadIdx.x; j < P; j += THREADS) xin[j] = (j < D) ? xr[j] : T(0);
+        __syncthreads();
+        double2* orow = reinterpret_cast<double2*>(out + (size_t)row * 2 * F);
+        double2* grow = GRAD ? reinterpret_cast<double2*>(grad + (size_t)row * 2 * F) : nullptr;
+        for (int rep = 0; rep < reps; ++rep) {
+            const int64_t base = (int64_t)rep * P;
+            T v[E];
+#pragma unroll
+            for (int r = 0; r < E; ++r) v[r] = xin[off + lane + K * r];
+#pragma unroll 1
+            for (int s = 0; s < 3; ++s) {
+                const int8_t* rd = radem + (int64_t)s * R + base + off + lane;
+#pragma unroll
+                for (int r = 0; r < E; ++r) v[r] = mul_rn(v[r], (T)rd[K * r] * cnorm);     // one rounding, as cta_sorf
+                warp_fwht<T, E, K>(v, lane);
+#pragma unroll
+                for (int r = 0; r < E; ++r) buf[off + lane + K * r] = v[r];
+                __syncthreads();
+#pragma unroll
+                for (int q = 0; q < GROUPS; ++q) {
+                    const int o = threadIdx.x + q * THREADS;
+                    T w[NS];
+#pragma unroll
+                    for (int sidx = 0; sidx < NS; ++sidx) w[sidx] = buf[o + sidx * SEG];
+#pragma unroll
+                    for (int h = 1; h < NS; h <<= 1)
+#pragma unroll
+                        for (int i = 0; i < NS; ++i)
+                            if ((i & h) == 0) {
+                                const T a = w[i], b = w[i + h];
+                                w[i]     = add_rn(a, b);
+                                w[i + h] = sub_rn(a, b);
+                            }
+                    if (s < 2) {
+#pragma unroll
+                        for (int sidx = 0; sidx < NS; ++sidx) buf[o + sidx * SEG] = w[sidx];
+                    } else {
+#pragma unroll
+                        for (int sidx = 0; sidx < NS; ++sidx) {
+                            const int64_t idx = base + o + sidx * SEG;
+                            if (idx < F) {
+                                if (GRAD) rbf_post_grad<T>(w[sidx], chi[idx], scale, sigma, orow + idx, grow + idx);
+                                else      rbf_post<T>(w[sidx], chi[idx], scale, orow + idx);
+                            }
+                        }
+                    }
+                }
+                __syncthreads();                         // cross-segment reads / writes of buf are complete
+                if (s < 2) {
+#pragma unroll
+                    for (int r = 0; r < E; ++r) v[r] = buf[off + lane + K * r];
+                }
+            }
+        }
+        __syncthreads();                                 // xin is rewritten by the next row
+    }
+}
+
+template <typename T, int NS, bool GRAD>
+static int launch_cta2(const T* x, int64_t n, int64_t d, double* out, double* grad, const int8_t* radem, int64_t R,
+                       const T* chi, int64_t F, double scale, double sigma, cudaStream_t st) {
+    constexpr int64_t P = (int64_t)NS * 1024;
+    const int reps = (int)((F + P - 1) / P);
+    const size_t smem = 2 * (size_t)P * sizeof(T);
+    auto kern = rbf_cta2_kernel<T, NS, GRAD>;
+    ensure_dyn_smem(kern, smem);
+    int per_sm = (int)((220 * 1024) / smem);
+    if (per_sm * 32 * NS > 2048) per_sm = 2048 / (32 * NS);
+    if (per_sm > 16) per_sm = 16;
+    if (per_sm < 1) per_sm = 1;
+    int64_t blocks = (int64_t)148 * per_sm;
+    if (blocks > n) blocks = n;
+    kern<<<(unsigned)blocks, 32 * NS, smem, st>>>(x, out, grad, radem, chi, (int)n, (int)d, (int)F, R, reps,
+                                                 norm_constant<T>(P), scale, sigma);
+    count_launch();
+    return check_launch("rbf_cta2_kernel");
+}
+
+// ---------------------------------------------------------------------------------------------
 static inline int pow2_ceil(int v) { int p = 1; while (p < v) p *= 2; return p; }
 
 // elements per lane: K = P/E sub-lanes; K >= 4 where possible (>= 64 contiguous bytes per store group),
@@ -246,9 +356,11 @@ static int launch_core(const T* x, int64_t n, int64_t d, double* out, double* gr
     const int64_t rep_groups = (reps + RC - 1) / RC;
     while (rows_per_cta > nrl && ((n + rows_per_cta - 1) / rows_per_cta) * rep_groups < 148 * 6)
         rows_per_cta /= 2;
-    // row iterations per cp.async batch: <= 16 KB per buffer
-    const size_t row_bytes = (size_t)nrl * K * CPITCH * sizeof(T);
-    int ITB = (int)((16 * 1024) / row_bytes);
+    // row iterations per cp.async batch: <= 16 KB per buffer (24 KB for the linear tile of the wide vectors)
+    constexpr bool LINEAR = (K >= 16);
+    constexpr int XROW = LINEAR ? LinTile<T, P, E>::PITCH : K * CPITCH;
+    const size_t row_bytes = (size_t)nrl * XROW * sizeof(T);
+    int ITB = (int)(((LINEAR ? 24 : 16) * 1024) / row_bytes);
     if (ITB < 1) ITB = 1;
     if (ITB > 8) ITB = 8;
     const size_t smem = 2 * ITB * row_bytes + (size_t)RC * K * CPITCH * sizeof(T);
@@ -257,8 +369,9 @@ static int launch_core(const T* x, int64_t n, int64_t d, double* out, double* gr
     const T c = norm_constant<T>(P);
     const T fold = is_pow4(P) ? (T)(c * c * c) : T(1);
     dim3 grid((unsigned)((n + rows_per_cta - 1) / rows_per_cta), (unsigned)rep_groups);
+    const int vec16 = ((d * sizeof(T)) % 16 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
     kern<<<grid, WARPS * 32, smem, st>>>(x, out, grad, radem, chi, (int)n, (int)d, (int)F, R, reps, RC,
-                                         rows_per_cta, ITB, c, fold, scale, sigma);
+                                         rows_per_cta, ITB, c, fold, scale, sigma, vec16);
     count_launch();
     return check_launch("rbf_core_kernel");
 }
@@ -309,6 +422,16 @@ int rbf_dispatch(const T* x, int64_t n, int64_t d, double* out, double* grad, in
         default: break;
     }
 #undef XB_CASE
+    static const bool cta_v1 = getenv("XGPR_B200_RBF_CTA_V1") != nullptr;
+    if (!cta_v1 && 2 * (size_t)P * sizeof(T) <= 200 * 1024) {
+        switch (P) {
+            case 2048:  return launch_cta2<T, 2, GRAD>(x, n, d, out, grad, radem, R, chi, F, scale, sigma, st);
+            case 4096:  return launch_cta2<T, 4, GRAD>(x, n, d, out, grad, radem, R, chi, F, scale, sigma, st);
+            case 8192:  return launch_cta2<T, 8, GRAD>(x, n, d, out, grad, radem, R, chi, F, scale, sigma, st);
+            case 16384: return launch_cta2<T, 16, GRAD>(x, n, d, out, grad, radem, R, chi, F, scale, sigma, st);
+            default: break;
+        }
+    }
     return launch_cta<T, GRAD>(x, n, d, P, out, grad, radem, R, chi, F, scale, sigma, st);
 }
 

@@ -15,21 +15,30 @@ from ._native import lib, check
 _SFX = {torch.float32: "_f32", torch.float64: "_f64"}
 
 
-_ACCURATE = {"on": bool(int(__import__("os").environ.get("XGPR_B200_ACCURATE_SINCOS", "0") or 0)), "devices": set()}
+def _env_level():
+    v = __import__("os").environ.get("XGPR_B200_ACCURATE_SINCOS", "")
+    try:
+        return int(v) if v != "" else -1
+    except ValueError:
+        return -1
 
 
-def set_accurate_sincos(on):
-    """float32 cos / sin of the feature kernels: False (default) = Cody-Waite + MUFU (<= ~6e-7 absolute), True = CUDA's
-    accurate sincosf.  Also selectable with XGPR_B200_ACCURATE_SINCOS=1.  The setting is a per-device constant: it is
-    (re)applied lazily to every device the next call launches on."""
-    _ACCURATE["on"] = bool(on)
+_ACCURATE = {"level": _env_level(), "devices": set()}
+
+
+def set_accurate_sincos(level):
+    """float32 cos / sin of the feature kernels (include/xgpr_b200.h): 0 / False = Cody-Waite + MUFU (<= ~4e-7 absolute),
+    1 / True = polynomial on the FMA pipe (<= 7e-8), 2 = CUDA's sincosf, -1 / None = the per-kernel-family defaults
+    (fixed-vector kernels 1, convolution kernels 0).  Also selectable with XGPR_B200_ACCURATE_SINCOS=<level>.  The setting
+    is a per-device constant: it is (re)applied lazily to every device the next call launches on."""
+    _ACCURATE["level"] = -1 if level is None else int(level)
     _ACCURATE["devices"].clear()
 
 
 def _stream():
     dev = torch.cuda.current_device()
     if dev not in _ACCURATE["devices"]:
-        check(lib.xgpr_b200_set_accurate_sincos(int(_ACCURATE["on"])))
+        check(lib.xgpr_b200_set_accurate_sincos(int(_ACCURATE["level"])))
         _ACCURATE["devices"].add(dev)
     return torch.cuda.current_stream().cuda_stream
 
