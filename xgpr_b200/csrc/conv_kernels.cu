@@ -13,6 +13,7 @@
 #include "sorf_warp.cuh"   // cta_sorf for P > 1024
 
 #include <mutex>
+#include <stdlib.h>
 #include <unordered_map>
 #include <utility>
 
@@ -27,22 +28,48 @@ __device__ __forceinline__ double conv_row_scale(double base, int nk, int scalin
     return base;
 }
 
+// ---- 1-D bulk copies (TMA, cp.async.bulk) of whole sequences into shared memory
+__device__ __forceinline__ void cv_mbar_init(unsigned bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void cv_mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cv_bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void cv_mbar_wait(unsigned bar, unsigned parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}"
+        ::"r"(bar), "r"(parity) : "memory");
+}
+
 // Register kernel, P <= 1024 (sorf_core.cuh).  Slot g = warp*V + q owns (sequence rowlane = g / RC,
-// repeat = blockIdx.y*RC + g % RC).  SMEMX: the CTA's sequences are first copied (cp.async) into shared
-// memory, so every overlapping window is served on-chip and global memory sees each input element once
-// per repeat group.
+// repeat = blockIdx.y*RC + g % RC).  SMEMX: the CTA's sequences are first copied into shared memory, so every
+// overlapping window is served on-chip and global memory sees each input element once per repeat group.  The copy is ONE
+// 1-D bulk copy (TMA, cp.async.bulk + mbarrier) per sequence -- a sequence's seqlen * C leading elements are contiguous --
+// issued by one thread, whenever the rows are 16-byte aligned (`bulk`); otherwise element-wise cp.async.
 template <typename T, int P, int E, int MODE, int WARPS, bool SMEMX>
 __global__ void __launch_bounds__(WARPS * 32, (E <= 16 && sizeof(T) == 4 && MODE != CONV_GRAD) ? 2 : 1)
 conv_core_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __restrict__ grad,
                  const int8_t* __restrict__ radem, const T* __restrict__ chi,
                  const int32_t* __restrict__ seqlen, int N, int M, int C, int F, int64_t R,
                  int reps, int RC, int conv_width, int scaling_type, T cnorm, T fold, double base_scale,
-                 double sigma, int tile_elems) {
+                 double sigma, int tile_elems, int bulk) {
     constexpr int K = P / E;
     constexpr int V = 32 / K;
     constexpr int S = WARPS * V;
     constexpr bool FOLD = is_pow4(P);
-    constexpr int CH = cmin(8, E);
+    // cos / sin group size: 4 for the float sum-pool instance at E = 16, whose 32 fp64 accumulators + 16 chi values leave
+    // no room for 3 x 8 temporaries under the 128-register cap of 2 CTAs / SM (it spilled 44-52 bytes with groups of 8)
+    constexpr int CH = (MODE == CONV_FGEN && sizeof(T) == 4 && E == 16) ? 4 : cmin(8, E);
     constexpr int CPITCH = ChiTile<T, E>::PITCH;
     constexpr int NACC = (MODE == CONV_GRAD) ? 4 : ((MODE == CONV_FGEN) ? 2 : 0);
 
@@ -63,23 +90,46 @@ conv_core_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __re
     const int64_t base = (int64_t)rep * P;
     const int wlen = conv_width * C;
 
+    __shared__ __align__(8) unsigned long long seq_bar;
     if (SMEMX) {
         // sequences of this CTA -> shared memory (only the seqlen[row] * C leading elements are needed)
-        for (int rl = 0; rl < nrl; ++rl) {
-            const int rw = blockIdx.x * nrl + rl;
-            if (rw >= N) break;
-            const int cnt = min(seqlen[rw] * C, tile_elems);
-            const T* src = x + (size_t)rw * M * C;
-            T* dst = xtile + (size_t)rl * tile_elems;
-            for (int t = threadIdx.x; t < cnt; t += blockDim.x) cp_async_elem<T>(dst + t, src + t, true);
+        if (bulk) {
+            if (threadIdx.x == 0) {
+                const unsigned bar = (unsigned)__cvta_generic_to_shared(&seq_bar);
+                cv_mbar_init(bar, 1);
+                unsigned total = 0;
+                for (int rl = 0; rl < nrl; ++rl) {
+                    const int rw = blockIdx.x * nrl + rl;
+                    if (rw >= N) break;
+                    total += (unsigned)((min(seqlen[rw] * C, tile_elems) * (int)sizeof(T) + 15) & ~15);
+                }
+                cv_mbar_expect_tx(bar, total);
+                for (int rl = 0; rl < nrl; ++rl) {
+                    const int rw = blockIdx.x * nrl + rl;
+                    if (rw >= N) break;
+                    const unsigned bytes = (unsigned)((min(seqlen[rw] * C, tile_elems) * (int)sizeof(T) + 15) & ~15);
+                    cv_bulk_g2s((unsigned)__cvta_generic_to_shared(xtile + (size_t)rl * tile_elems),
+                                x + (size_t)rw * M * C, bytes, bar);
+                }
+            }
+        } else {
+            for (int rl = 0; rl < nrl; ++rl) {
+                const int rw = blockIdx.x * nrl + rl;
+                if (rw >= N) break;
+                const int cnt = min(seqlen[rw] * C, tile_elems);
+                const T* src = x + (size_t)rw * M * C;
+                T* dst = xtile + (size_t)rl * tile_elems;
+                for (int t = threadIdx.x; t < cnt; t += blockDim.x) cp_async_elem<T>(dst + t, src + t, true);
+            }
+            cp_async_commit();
         }
-        cp_async_commit();
     }
     load_chi_tile<T, P, E>(chi_tile, chi, rep0, RC, reps, F, fold);
     SignBits<E> sg;
     sg.template load<K>(radem, R, base, sub, ok);
-    if (SMEMX) cp_async_wait<0>();
-    __syncthreads();
+    if (SMEMX && !bulk) cp_async_wait<0>();
+    __syncthreads();                                 // chi tile visible; the mbarrier initialised by thread 0 as well
+    if (SMEMX && bulk) cv_mbar_wait((unsigned)__cvta_generic_to_shared(&seq_bar), 0);
     const T* my_chi = chi_tile + (rl_rep * K + sub) * CPITCH;
     T chr[E];
 #pragma unroll
@@ -312,21 +362,25 @@ static int launch_conv_core(const T* x, int64_t n, int64_t m, int64_t c, void* o
     // sequence tile: the longest sequence of the batch, rounded up to 16 bytes
     int tile_elems = max_seqlen * (int)c;
     tile_elems = (tile_elems + 3) & ~3;
+    // bulk (TMA) staging needs 16-byte aligned rows: then every rounded-up copy also stays inside its own row
+    const int bulk = (((size_t)m * c * sizeof(T)) % 16 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0) &&
+                     ((size_t)tile_elems * sizeof(T) <= (size_t)m * c * sizeof(T)) && (chi_bytes % 16 == 0) &&
+                     !getenv("XGPR_B200_CONV_NO_BULK");
     const size_t x_bytes = (size_t)nrl * tile_elems * sizeof(T);
     dim3 grid((unsigned)((n + nrl - 1) / nrl), (unsigned)((reps + RC - 1) / RC));
     if (chi_bytes + x_bytes <= 100 * 1024) {
-        const size_t smem = chi_bytes + x_bytes;
+        const size_t smem = chi_bytes + x_bytes;   // chi_bytes and every sequence tile are multiples of 16 bytes
         auto kern = conv_core_kernel<T, P, E, MODE, WARPS, true>;
         ensure_dyn_smem(kern, smem);
         kern<<<grid, WARPS * 32, smem, st>>>(x, out, grad, radem, chi, seq_dev, (int)n, (int)m, (int)c, (int)F, R,
                                              reps, RC, conv_width, scaling_type, cn, fold, base_scale, sigma,
-                                             tile_elems);
+                                             tile_elems, bulk);
     } else {
         auto kern = conv_core_kernel<T, P, E, MODE, WARPS, false>;
         ensure_dyn_smem(kern, chi_bytes);
         kern<<<grid, WARPS * 32, chi_bytes, st>>>(x, out, grad, radem, chi, seq_dev, (int)n, (int)m, (int)c, (int)F,
                                                   R, reps, RC, conv_width, scaling_type, cn, fold, base_scale,
-                                                  sigma, 0);
+                                                  sigma, 0, 0);
     }
     count_launch();
     return check_launch("conv_core_kernel");
