@@ -47,6 +47,15 @@ int xgpr_b200_fht2d_f64(double* x, int64_t n, int64_t p, void* stream);
  * x <- FWHT(x * radem * p^-1/2) row-wise; radem (p) int8 in {-1,+1}. */
 int xgpr_b200_srht_f32(float*  x, int64_t n, int64_t p, const int8_t* radem, int64_t radem_len, void* stream);
 int xgpr_b200_srht_f64(double* x, int64_t n, int64_t p, const int8_t* radem, int64_t radem_len, void* stream);
+/* Fused SRHT + column sampling -- the whole of SRHTCompressor.transform_x (src/xGPR/kernels/srht_compressor.py:70-97) in one
+ * pass: out (n, rank) = FWHT(zpad * radem * p_full^-1/2)[:, cols], zpad = z (n, m) zero-padded to p_full columns
+ * (p_full = 2^ceil(log2 m) = len(radem)); z is NOT modified.  cols: `rank` int32 column indices (device).  Same
+ * butterflies as xgpr_b200_srht (bit-identical values).  Supported widths: xgpr_b200_srht_sample_supported(). */
+int xgpr_b200_srht_sample_supported(int64_t p_full, int elem_bytes);
+int xgpr_b200_srht_sample_f32(const float* z, int64_t n, int64_t m, const int8_t* radem, int64_t p_full, const int32_t* cols,
+                              int64_t rank, float* out, void* stream);
+int xgpr_b200_srht_sample_f64(const double* z, int64_t n, int64_t m, const int8_t* radem, int64_t p_full,
+                              const int32_t* cols, int64_t rank, double* out, void* stream);
 
 /* ---- input staging: x[i, j] <- T( double(x[i, j]) * (col_weights ? col_weights[j] : 1) * sigma ), in place.
  * This is the NumPy expression the reference's kernel classes evaluate on the host before calling the
@@ -169,7 +178,7 @@ double xgpr_b200_tc_last_gemm_ms(void);
  *   0 = two-term Cody-Waite reduction + MUFU.SIN / MUFU.COS (abs. error <= ~4e-7);
  *   1 = pi/2 reduction + minimax polynomials on the FMA pipe (abs. error <= 7e-8: the class of glibc's cosf / sinf, which
  *       the reference calls at cpu/shared_fht_functions/shared_rfgen_ops.cpp:107-112);
- *   2 = CUDA's sincosf;   -1 = per-kernel-family defaults (fixed-vector RBF-family kernels: 1, convolution kernels: 0).
+ *   2 = CUDA's sincosf;   -1 = the default (0).
  * Measured cost and effect on fitted weights: DESIGN.md section 2. */
 int    xgpr_b200_set_accurate_sincos(int level);
 /* Tensor-core sketch accumulation, same scheme: acc (r, m) += A^T Z, A (n, r), Z (n, m) fp64 row-major

@@ -220,31 +220,56 @@ def test_conv_accumulates_into_output():
 
 
 @pytest.mark.parametrize("path", golden_files("l1_ard_"), ids=os.path.basename)
-def test_ard_golden(path):
+def _ard_tol(dt, ref):
+    """fp64: the tensor-core (DMMA) kernel sums the same products as the oracle in a different order -> 1e-9.
+    float32: the oracle rounds every product x W to float before widening it (ard_ops.cpp:98); the DMMA kernel keeps the
+    exact product, so the argument of cos / sin differs by <= 6e-8 relative per term -- the float32 feature contract
+    (rtol 1e-5, atol 1e-5 of scale) applies; the SIMT kernel (XGPR_B200_ARD_SIMT=1) reproduces the rounding exactly."""
+    if np.dtype(dt) == np.float64:
+        return dict(rtol=1e-9, atol=1e-10)
+    return dict(rtol=1e-5, atol=1e-5 * float(np.abs(ref).max()))
+
+
+def test_ard_golden(path, monkeypatch):
     g = load_golden(path)
     ext = _ext()
+    dt = _dt(path)
     n, f, L = g["x"].shape[0], g["w"].shape[0], g["grad"].shape[2]
-    out = torch.zeros((n, 2 * f), dtype=torch.float64, device=DEV)
-    grad = torch.zeros((n, 2 * f, L), dtype=torch.float64, device=DEV)
-    ext.cudaMiniARDGrad(T(g["x"]), out, T(g["w"]), T(g["smap"]), T(g["svals"]), grad, bool(g["fit_intercept"]))
-    np.testing.assert_allclose(out.cpu().numpy(), g["out"], rtol=1e-9, atol=1e-11)
-    np.testing.assert_allclose(grad.cpu().numpy(), g["grad"], rtol=1e-9, atol=1e-10)
+    for simt in (False, True):
+        if simt:
+            monkeypatch.setenv("XGPR_B200_ARD_SIMT", "1")
+        out = torch.zeros((n, 2 * f), dtype=torch.float64, device=DEV)
+        grad = torch.zeros((n, 2 * f, L), dtype=torch.float64, device=DEV)
+        ext.cudaMiniARDGrad(T(g["x"]), out, T(g["w"]), T(g["smap"]), T(g["svals"]), grad, bool(g["fit_intercept"]))
+        to = dict(rtol=1e-9, atol=1e-11) if simt else _ard_tol(dt, g["out"])
+        tg = dict(rtol=1e-9, atol=1e-10) if simt else _ard_tol(dt, g["grad"])
+        np.testing.assert_allclose(out.cpu().numpy(), g["out"], **to)
+        np.testing.assert_allclose(grad.cpu().numpy(), g["grad"], **tg)
 
 
-def test_ard_cfg5_shape():
+@pytest.mark.parametrize("dt", [np.float32, np.float64])
+@pytest.mark.parametrize("case", [(300, 128, 4096, [64, 64]), (77, 200, 500, [150, 50]), (130, 1000, 96, [1, 998, 1]),
+                                  (65, 37, 33, [37])])
+def test_ard_config_shapes(case, dt):
+    """cfg5-shaped (128 inputs, 2 lengthscales) and awkward shapes (odd F, groups that are not multiples of 4, an
+    interleaved sigma map, sigma varying INSIDE a group = the general path of the tensor-core kernel)."""
+    n, d, f, groups = case
     rng = np.random.default_rng(11)
-    n, d, f = 300, 128, 4096
-    x = rng.standard_normal((n, d)).astype(np.float32)
-    w = (rng.standard_normal((f, d)) * 0.3).astype(np.float32)
-    smap = np.repeat(np.arange(2, dtype=np.int32), 64)
-    svals = np.where(smap == 0, 0.7, 1.3)
-    ref_out, ref_grad = so.ard_grad(x, w, smap, svals, True, num_lengthscales=2)
+    x = rng.standard_normal((n, d)).astype(dt)
+    w = (rng.standard_normal((f, d)) * 0.3 / np.sqrt(d / 128)).astype(dt)
+    smap = np.repeat(np.arange(len(groups), dtype=np.int32), groups)
+    if d == 200:
+        smap = rng.permutation(smap).astype(np.int32)                 # groups interleaved along the columns
+    svals = np.asarray([0.7, 1.3, 0.9])[smap]
+    if d == 37:
+        svals = rng.uniform(0.5, 1.5, size=d)                         # not constant on the group
+    ref_out, ref_grad = so.ard_grad(x, w, smap, svals, True, num_lengthscales=len(groups))
     ext = _ext()
     out = torch.zeros((n, 2 * f), dtype=torch.float64, device=DEV)
-    grad = torch.zeros((n, 2 * f, 2), dtype=torch.float64, device=DEV)
+    grad = torch.zeros((n, 2 * f, len(groups)), dtype=torch.float64, device=DEV)
     ext.cudaMiniARDGrad(T(x), out, T(w), T(smap), T(svals), grad, True)
-    np.testing.assert_allclose(out.cpu().numpy(), ref_out, rtol=1e-9, atol=1e-11)
-    np.testing.assert_allclose(grad.cpu().numpy(), ref_grad, rtol=1e-9, atol=1e-10)
+    np.testing.assert_allclose(out.cpu().numpy(), ref_out, **_ard_tol(dt, ref_out))
+    np.testing.assert_allclose(grad.cpu().numpy(), ref_grad, **_ard_tol(dt, ref_grad))
 
 
 def test_error_behaviour():
@@ -297,3 +322,33 @@ def test_downstream_consumers(shape):
     w = torch.zeros((m, r), dtype=torch.float64, device=DEV)
     ext.cg_matvec_accum(zt, T(v), w)
     np.testing.assert_allclose(w.cpu().numpy(), z.T @ (z @ v), rtol=1e-10, atol=1e-11)
+
+
+@pytest.mark.parametrize("dt", [np.float64, np.float32])
+@pytest.mark.parametrize("shape", [(70, 1500, 100), (33, 8192, 512), (40, 16384, 512), (25, 20000, 700), (9, 1024, 2),
+                                   (300, 32768, 1024)])
+def test_fused_srht_sample_is_bit_exact(dt, shape):
+    """SRHTCompressor.transform_x in one pass (srht_sample_kernel: read the chunk once, keep `rank` columns; a 2-CTA
+    cluster with a DSMEM gather at P_M = 32,768) against pad + cudaSRHT + column gather (srht_compressor.py:70-97) --
+    the same butterflies, so the same bits -- and against the oracle's SRHT."""
+    from xgpr_b200.kernels import SRHTCompressor
+    n, m, rank = shape
+    ext = _ext()
+    rng = np.random.default_rng(2)
+    z = rng.standard_normal((n, m)).astype(dt)
+    comp = SRHTCompressor(rank, m, device="cuda", double_precision=(dt == np.float64), random_seed=7)
+    p = comp.padded_dims
+    if not ext.srht_sample_supported(p, torch.float64 if dt == np.float64 else torch.float32):
+        pytest.skip("width handled by the three-pass path")
+    zt = T(z)
+    keep = zt.clone()
+    fused = comp.transform_x(zt)
+    assert torch.equal(zt, keep), "the fused kernel must not modify its input"
+    padded = torch.zeros((n, p), dtype=zt.dtype, device=DEV)
+    padded[:, :m] = zt
+    ext.cudaSRHT(padded, comp.radem)
+    ref = padded[:, comp.truncated_sampler]
+    assert fused.shape == (n, rank) and torch.equal(fused, ref)
+    zp = np.zeros((n, p), dt)
+    zp[:, :m] = z
+    assert np.array_equal(fused.cpu().numpy(), so.srht_(zp, comp.radem.cpu().numpy())[:, comp.truncated_sampler.cpu().numpy()])

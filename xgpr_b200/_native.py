@@ -86,6 +86,13 @@ lib.xgpr_b200_cg_update_a_f64.restype = _int
 lib.xgpr_b200_cg_update_b_f64.argtypes = [_ptr, _ptr, _ptr, _ptr, _i64, _dbl, _int, _ptr, _ptr]
 lib.xgpr_b200_cg_update_b_f64.restype = _int
 EXPORTED += ["xgpr_b200_cres_zzv_gated_f32", "xgpr_b200_cg_update_a_f64", "xgpr_b200_cg_update_b_f64"]
+lib.xgpr_b200_srht_sample_supported.argtypes = [_i64, _int]
+lib.xgpr_b200_srht_sample_supported.restype = _int
+for _sfx in ("_f32", "_f64"):
+    _fn = getattr(lib, "xgpr_b200_srht_sample" + _sfx)
+    _fn.argtypes = [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _ptr]
+    _fn.restype = _int
+EXPORTED += ["xgpr_b200_srht_sample_supported", "xgpr_b200_srht_sample_f32", "xgpr_b200_srht_sample_f64"]
 lib.xgpr_b200_rbf_zzv_supported.argtypes = [_i64, _i64]
 lib.xgpr_b200_rbf_zzv_supported.restype = _int
 EXPORTED.append("xgpr_b200_rbf_zzv_supported")

@@ -10,6 +10,7 @@
 // owns one (row, frequency) pair, keeps rf in a register and its L bucket sums in shared memory.
 #include "common.cuh"
 #include <stdlib.h>
+#include <mutex>
 
 namespace xb {
 
@@ -99,22 +100,26 @@ __device__ __forceinline__ void ard_dmma(double (&c)[2], double a, double b) {
                  : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
 }
 
-template <typename T, int NG>
-__global__ void __launch_bounds__(256, NG <= 2 ? 2 : 1)
+// GENERAL = false: sigma is constant on every group (rf = sum_l sigma_l G_l in the epilogue, no extra accumulators);
+// GENERAL = true: rf gets its own accumulators fed by x * sigma.  Both instances are launched; `uniform_flag` (written by
+// ard_uniform_kernel) makes the one that does not apply return at once -- the host never reads sigma back.
+template <typename T, int NG, bool GENERAL>
+__global__ void __launch_bounds__(256, (NG <= 2 && !GENERAL) ? 2 : 1)
 ard_mma_kernel(const T* __restrict__ x, double* __restrict__ out, const T* __restrict__ w,
                const int32_t* __restrict__ sigma_map, const double* __restrict__ sigma_vals,
-               double* __restrict__ grad, int N, int D, int F, double scale, int npos_max) {
+               double* __restrict__ grad, int N, int D, int F, double scale, int npos_max, int wld, int w_resident,
+               const int* __restrict__ uniform_flag) {
+    if ((*uniform_flag != 0) == GENERAL) return;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    double* xs = reinterpret_cast<double*>(smem_raw);            // [64][AM_LD]   x tile, fp64
-    double* xg = xs + AM_ROWS * AM_LD;                           // [64][AM_LD]   x * sigma (general-sigma path)
-    double* ws = xg + AM_ROWS * AM_LD;                           // [64][AM_LD]   W tile, fp64
-    double* sigp = ws + AM_F * AM_LD;                            // [npos_max]    sigma at each permuted position
+    double* xs = reinterpret_cast<double*>(smem_raw);            // [64][AM_LD]   x chunk, fp64
+    double* xg = xs + AM_ROWS * AM_LD;                           // [64][AM_LD]   x * sigma (GENERAL only)
+    double* ws = xg + (GENERAL ? AM_ROWS * AM_LD : 0);           // [64][wld]     W: all columns (resident) or one chunk
+    double* sigp = ws + AM_F * wld;                              // [npos_max]    sigma at each permuted position
     int* perm = reinterpret_cast<int*>(sigp + npos_max);         // [npos_max]    permuted position -> column (-1 = padding)
     int* kgrp = perm + npos_max;                                 // [npos_max/4]  group of each 4-column step
     __shared__ int s_cnt[32][NG];                                // per 32-column chunk, per group: member count
     __shared__ int s_start[NG + 1];
     __shared__ double s_gsig[NG];
-    __shared__ int s_uniform;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g4 = lane >> 2, t4 = lane & 3;
     const int wr = warp >> 1, wf = warp & 1;                     // warp tile: rows wr*16.., freqs wf*32..
@@ -122,7 +127,6 @@ ard_mma_kernel(const T* __restrict__ x, double* __restrict__ out, const T* __res
 
     // ---- column permutation: groups contiguous (ascending k inside a group), each padded to a multiple of 4
     const int nchunk = (D + 31) / 32;                            // host guarantees D <= 1024
-    if (tid == 0) s_uniform = 1;
     for (int c = warp; c < nchunk; c += 8) {
         const int k = c * 32 + lane;
         int mv = (k < D) ? sigma_map[k] : -1;
@@ -167,55 +171,77 @@ ard_mma_kernel(const T* __restrict__ x, double* __restrict__ out, const T* __res
         for (int q = 1; q < NG; ++q) g += (4 * i >= s_start[q]) ? 1 : 0;
         kgrp[i] = g;
     }
-    if (tid < NG) {                                              // sigma constant on the group?  (MiniARD: always)
-        const int beg = s_start[tid], end = s_start[tid + 1];
+    if (tid < NG) {                                              // the group's sigma (GENERAL: unused)
         double sv = 0.0;
-        bool have = false, uni = true;
-        for (int i = beg; i < end; ++i)
-            if (perm[i] >= 0) {
-                if (!have) { sv = sigp[i]; have = true; }
-                else if (sigp[i] != sv) uni = false;
-            }
+        for (int q = s_start[tid]; q < s_start[tid + 1]; ++q)
+            if (perm[q] >= 0) { sv = sigp[q]; break; }
         s_gsig[tid] = sv;
-        if (!uni) s_uniform = 0;
     }
     __syncthreads();
-    const bool uniform = s_uniform != 0;
     const int nsteps_total = npos / 4;
-
-    for (int rt = blockIdx.y; rt * AM_ROWS < N; rt += gridDim.y) {
+    if (w_resident) {                                            // this CTA's 64 frequencies x every column, once
+        for (int t = tid; t < AM_F * npos; t += 256) {
+            const int ff = t / npos, pp = t % npos;
+            const int col = perm[pp], gf = f0 + ff;
+            ws[ff * wld + pp] = (col >= 0 && gf < F) ? (double)w[(size_t)gf * D + col] : 0.0;
+        }
+    }
+    // x chunk prefetch: thread owns elements t = tid + 256 i (i < 8) of a 64 x 32 chunk
+    T xr[8];
+    auto fetch = [&](int r0, int p0) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int t = tid + 256 * i, rr = t / AM_KC, kk = t % AM_KC;
+            const int col = (p0 + kk < npos) ? perm[p0 + kk] : -1;
+            const int gr = r0 + rr;
+            xr[i] = (col >= 0 && gr < N) ? x[(size_t)gr * D + col] : T(0);
+        }
+    };
+    int rt = blockIdx.y;
+    if (rt * AM_ROWS < N) fetch(rt * AM_ROWS, 0);
+    for (; rt * AM_ROWS < N; rt += gridDim.y) {
         const int r0 = rt * AM_ROWS;
-        double acc[NG][2][4][2], accr[2][4][2];
+        double acc[NG][2][4][2], accr[GENERAL ? 2 : 1][4][2];
 #pragma unroll
         for (int i = 0; i < 2; ++i)
 #pragma unroll
             for (int j = 0; j < 4; ++j)
 #pragma unroll
                 for (int e = 0; e < 2; ++e) {
-                    accr[i][j][e] = 0.0;
+                    if (GENERAL) accr[i][j][e] = 0.0;
 #pragma unroll
                     for (int g = 0; g < NG; ++g) acc[g][i][j][e] = 0.0;
                 }
         for (int p0 = 0; p0 < npos; p0 += AM_KC) {
             __syncthreads();                                     // previous chunk's fragments are consumed
-            for (int t = tid; t < AM_ROWS * AM_KC; t += 256) {
-                const int rr = t / AM_KC, kk = t % AM_KC;
-                const int col = (p0 + kk < npos) ? perm[p0 + kk] : -1;
-                const int gr = r0 + rr, gf = f0 + rr;
-                const double xv = (col >= 0 && gr < N) ? (double)x[(size_t)gr * D + col] : 0.0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int t = tid + 256 * i, rr = t / AM_KC, kk = t % AM_KC;
+                const double xv = (double)xr[i];
                 xs[rr * AM_LD + kk] = xv;
-                if (!uniform) xg[rr * AM_LD + kk] = xv * sigp[min(p0 + kk, npos_max - 1)];
-                ws[rr * AM_LD + kk] = (col >= 0 && gf < F) ? (double)w[(size_t)gf * D + col] : 0.0;
+                if (GENERAL) xg[rr * AM_LD + kk] = xv * sigp[min(p0 + kk, npos_max - 1)];
+            }
+            if (!w_resident) {
+                for (int t = tid; t < AM_F * AM_KC; t += 256) {
+                    const int ff = t / AM_KC, kk = t % AM_KC;
+                    const int col = (p0 + kk < npos) ? perm[p0 + kk] : -1;
+                    const int gf = f0 + ff;
+                    ws[ff * wld + kk] = (col >= 0 && gf < F) ? (double)w[(size_t)gf * D + col] : 0.0;
+                }
             }
             __syncthreads();
+            // the next chunk (or the next row tile's first chunk) travels while this one is multiplied
+            if (p0 + AM_KC < npos) fetch(r0, p0 + AM_KC);
+            else if ((rt + (int)gridDim.y) * AM_ROWS < N) fetch((rt + (int)gridDim.y) * AM_ROWS, 0);
             const int nsteps = min(AM_KC / 4, nsteps_total - p0 / 4);
+            const int wofs = w_resident ? p0 : 0;
             for (int ks = 0; ks < nsteps; ++ks) {
                 const int grp = kgrp[p0 / 4 + ks];               // warp-uniform
                 double a[2], b[4];
 #pragma unroll
                 for (int i = 0; i < 2; ++i) a[i] = xs[(wr * 16 + i * 8 + g4) * AM_LD + ks * 4 + t4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) b[j] = ws[(wf * 32 + j * 8 + g4) * AM_LD + ks * 4 + t4];
+                for (int j = 0; j < 4; ++j) b[j] = ws[(wf * 32 + j * 8 + g4) * wld + wofs + ks * 4 + t4];
 #pragma unroll
                 for (int g = 0; g < NG; ++g)
                     if (grp == g) {
@@ -224,7 +250,7 @@ ard_mma_kernel(const T* __restrict__ x, double* __restrict__ out, const T* __res
 #pragma unroll
                             for (int j = 0; j < 4; ++j) ard_dmma(acc[g][i][j], a[i], b[j]);
                     }
-                if (!uniform) {
+                if (GENERAL) {
 #pragma unroll
                     for (int i = 0; i < 2; ++i) {
                         const double as = xg[(wr * 16 + i * 8 + g4) * AM_LD + ks * 4 + t4];
@@ -242,11 +268,22 @@ ard_mma_kernel(const T* __restrict__ x, double* __restrict__ out, const T* __res
             for (int j = 0; j < 4; ++j) {
                 const int f = f0 + wf * 32 + j * 8 + 2 * t4;     // f and f + 1
                 if (row >= N || f >= F) continue;
+                const bool two = (f + 1 < F);
+                double* gp = grad + ((size_t)row * 2 * F + 2 * f) * NG;
+                // grad += on a caller-zeroed array, then rescaled (ard_ops.cpp:100,117-121): the old values are
+                // requested first so that their latency hides behind the two double-precision sincos
+                double old[2][NG];
+#pragma unroll
+                for (int e = 0; e < 2; ++e)
+#pragma unroll
+                    for (int g = 0; g < NG; ++g) old[e][g] = (e == 0 || two) ? __ldcs(gp + e * 2 * NG + g) : 0.0;
                 double cv[2], sv[2];
 #pragma unroll
                 for (int e = 0; e < 2; ++e) {
-                    double rf = accr[i][j][e];
-                    if (uniform) {
+                    double rf;
+                    if (GENERAL) {
+                        rf = accr[i][j][e];
+                    } else {
                         rf = 0.0;
 #pragma unroll
                         for (int g = 0; g < NG; ++g) rf = fma(s_gsig[g], acc[g][i][j][e], rf);
@@ -256,25 +293,22 @@ ard_mma_kernel(const T* __restrict__ x, double* __restrict__ out, const T* __res
                     cv[e] = scale * cs;
                     sv[e] = scale * sn;
                 }
-                const bool two = (f + 1 < F);
                 double* o = out + (size_t)row * 2 * F + 2 * f;
                 if (two) {
-                    reinterpret_cast<double2*>(o)[0] = make_double2(cv[0], sv[0]);
-                    reinterpret_cast<double2*>(o)[1] = make_double2(cv[1], sv[1]);
+                    __stcs(reinterpret_cast<double2*>(o), make_double2(cv[0], sv[0]));
+                    __stcs(reinterpret_cast<double2*>(o) + 1, make_double2(cv[1], sv[1]));
                 } else {
                     o[0] = cv[0];
                     o[1] = sv[0];
                 }
-                double* gp = grad + ((size_t)row * 2 * F + 2 * f) * NG;
 #pragma unroll
                 for (int e = 0; e < 2; ++e) {
                     if (e == 1 && !two) break;
 #pragma unroll
                     for (int g = 0; g < NG; ++g) {
-                        // grad += on a caller-zeroed array, then rescaled (ard_ops.cpp:100,117-121)
-                        const double gv = __dadd_rn(gp[e * 2 * NG + g], acc[g][i][j][e]);
-                        gp[e * 2 * NG + g] = -gv * sv[e];
-                        gp[e * 2 * NG + NG + g] = gv * cv[e];
+                        const double gv = __dadd_rn(old[e][g], acc[g][i][j][e]);
+                        __stcs(gp + e * 2 * NG + g, -gv * sv[e]);
+                        __stcs(gp + e * 2 * NG + NG + g, gv * cv[e]);
                     }
                 }
             }
@@ -282,23 +316,77 @@ ard_mma_kernel(const T* __restrict__ x, double* __restrict__ out, const T* __res
     }
 }
 
+// flag = 1 when sigma_vals is constant on every group of sigma_map (MiniARD: always, mini_ard.py:172-177)
+__global__ void ard_uniform_kernel(const int32_t* __restrict__ sigma_map, const double* __restrict__ sigma_vals, int D,
+                                   int L, int* __restrict__ flag) {
+    __shared__ int bad;
+    if (threadIdx.x == 0) bad = 0;
+    __syncthreads();
+    for (int k = threadIdx.x; k < D; k += blockDim.x) {
+        int mk = sigma_map[k];
+        mk = mk < 0 ? 0 : (mk >= L ? L - 1 : mk);
+        for (int q = 0; q < k; ++q) {                            // first earlier member of the same group
+            int mq = sigma_map[q];
+            mq = mq < 0 ? 0 : (mq >= L ? L - 1 : mq);
+            if (mq == mk) {
+                if (sigma_vals[q] != sigma_vals[k]) bad = 1;
+                break;
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) *flag = bad ? 0 : 1;
+}
+
+static int* ard_flag_buffer() {                                  // 4 bytes per device, allocated once
+    static std::mutex mu;
+    static int* buf[64] = {};
+    const int dev = current_device() & 63;
+    std::lock_guard<std::mutex> lk(mu);
+    if (!buf[dev] && cudaMalloc(&buf[dev], 64 * sizeof(int)) != cudaSuccess) {
+        cudaGetLastError();
+        buf[dev] = nullptr;
+    }
+    return buf[dev];
+}
+
 template <typename T, int NG>
 static int launch_ard_mma(const T* x, int64_t n, int64_t d, double* out, const T* w, int64_t F, const int32_t* sigma_map,
                           const double* sigma_vals, double* grad, double scale, cudaStream_t st) {
+    int* flag = ard_flag_buffer();
+    if (!flag) { set_error("out of memory on cuda"); return XGPR_B200_ECUDA; }
     const int npos_max = (int)((d + 3) / 4 * 4 + 4 * NG);
-    const size_t smem = (size_t)(3 * AM_ROWS * AM_LD) * 8 + (size_t)npos_max * 8 + (size_t)npos_max * 4 +
-                        (size_t)(npos_max / 4 + 1) * 4;
-    auto kern = ard_mma_kernel<T, NG>;
-    ensure_dyn_smem(kern, smem);
+    // W resident (64 frequencies x every permuted column, row stride == 4 mod 16 doubles: conflict-free fragment loads)
+    int wld_res = npos_max;
+    while (wld_res % 16 != 4) ++wld_res;
+    const size_t tail = (size_t)npos_max * 8 + (size_t)npos_max * 4 + (size_t)(npos_max / 4 + 1) * 4;
+    ard_uniform_kernel<<<1, 256, 0, st>>>(sigma_map, sigma_vals, (int)d, NG, flag);
+    count_launch();
     const int64_t ftiles = (F + AM_F - 1) / AM_F, rtiles = (n + AM_ROWS - 1) / AM_ROWS;
-    // each CTA keeps its column permutation and walks row tiles: ~8 CTAs per SM slot in flight over the whole grid
-    int64_t gy = (148 * 2 * 8 + ftiles - 1) / ftiles;
+    // each CTA keeps its column permutation (and W) and walks row tiles
+    int64_t gy = (148 * 2 * 4 + ftiles - 1) / ftiles;
     if (gy > rtiles) gy = rtiles;
     if (gy < 1) gy = 1;
     if (gy > 65535) gy = 65535;
     dim3 grid((unsigned)ftiles, (unsigned)gy);
-    kern<<<grid, 256, smem, st>>>(x, out, w, sigma_map, sigma_vals, grad, (int)n, (int)d, (int)F, scale, npos_max);
-    count_launch();
+    for (int general = 0; general < 2; ++general) {
+        const size_t xbytes = (size_t)(general ? 2 : 1) * AM_ROWS * AM_LD * 8;
+        const bool resident = xbytes + (size_t)AM_F * wld_res * 8 + tail <= 100 * 1024;
+        const int wld = resident ? wld_res : AM_LD;
+        const size_t smem = xbytes + (size_t)AM_F * wld * 8 + tail;
+        if (general) {
+            auto kern = ard_mma_kernel<T, NG, true>;
+            ensure_dyn_smem(kern, smem);
+            kern<<<grid, 256, smem, st>>>(x, out, w, sigma_map, sigma_vals, grad, (int)n, (int)d, (int)F, scale, npos_max,
+                                          wld, resident ? 1 : 0, flag);
+        } else {
+            auto kern = ard_mma_kernel<T, NG, false>;
+            ensure_dyn_smem(kern, smem);
+            kern<<<grid, 256, smem, st>>>(x, out, w, sigma_map, sigma_vals, grad, (int)n, (int)d, (int)F, scale, npos_max,
+                                          wld, resident ? 1 : 0, flag);
+        }
+        count_launch();
+    }
     return check_launch("ard_mma_kernel");
 }
 
@@ -314,7 +402,7 @@ int ard_dispatch(const T* x, int64_t n, int64_t d, double* out, const T* w, int6
     // the constant is declared T (ard_ops.cpp:87-92)
     const double ff0 = (double)F;
     const double scale0 = (double)(T)(fit_intercept ? sqrt(1.0 / (ff0 - 0.5)) : sqrt(1.0 / ff0));
-    static const bool simt_only = getenv("XGPR_B200_ARD_SIMT") != nullptr;
+    const bool simt_only = getenv("XGPR_B200_ARD_SIMT") != nullptr;   // the SIMT kernel reproduces the float product rounding
     if (L <= 3 && d <= 1024 && F < (1ll << 26) && !simt_only) {      // fp64 tensor-core path
         if (L == 1) return launch_ard_mma<T, 1>(x, n, d, out, w, F, sigma_map, sigma_vals, grad, scale0, st);
         if (L == 2) return launch_ard_mma<T, 2>(x, n, d, out, w, F, sigma_map, sigma_vals, grad, scale0, st);

@@ -62,6 +62,10 @@ int set_accurate_sincos(int level) {
 template <typename T, bool SRHT>
 int fht_dispatch(T* x, int64_t n, int64_t P, const int8_t* radem, int64_t radem_len, cudaStream_t st);
 template <typename T>
+int srht_sample(const T* z, int64_t n, int64_t m, const int8_t* radem, int64_t p_full, const int32_t* cols,
+                int64_t rank, T* out, cudaStream_t st);
+int srht_sample_supported(int64_t p_full, int elem_bytes);
+template <typename T>
 int scale_input(T* x, int64_t n, int64_t d, const double* w, double sigma, cudaStream_t st);
 template <typename T, bool GRAD>
 int rbf_dispatch(const T* x, int64_t n, int64_t d, double* out, double* grad, int64_t num_rffs,
@@ -125,6 +129,15 @@ int xgpr_b200_fht2d_f32(float* x, int64_t n, int64_t p, void* s) { return fht_di
 int xgpr_b200_fht2d_f64(double* x, int64_t n, int64_t p, void* s) { return fht_dispatch<double, false>(x, n, p, nullptr, 0, ST(s)); }
 int xgpr_b200_srht_f32(float* x, int64_t n, int64_t p, const int8_t* radem, int64_t rl, void* s) { return fht_dispatch<float, true>(x, n, p, radem, rl, ST(s)); }
 int xgpr_b200_srht_f64(double* x, int64_t n, int64_t p, const int8_t* radem, int64_t rl, void* s) { return fht_dispatch<double, true>(x, n, p, radem, rl, ST(s)); }
+int xgpr_b200_srht_sample_supported(int64_t p_full, int elem_bytes) { return srht_sample_supported(p_full, elem_bytes); }
+int xgpr_b200_srht_sample_f32(const float* z, int64_t n, int64_t m, const int8_t* radem, int64_t p_full, const int32_t* cols,
+                              int64_t rank, float* out, void* s) {
+    return srht_sample<float>(z, n, m, radem, p_full, cols, rank, out, ST(s));
+}
+int xgpr_b200_srht_sample_f64(const double* z, int64_t n, int64_t m, const int8_t* radem, int64_t p_full,
+                              const int32_t* cols, int64_t rank, double* out, void* s) {
+    return srht_sample<double>(z, n, m, radem, p_full, cols, rank, out, ST(s));
+}
 
 int xgpr_b200_scale_input_f32(float* x, int64_t n, int64_t d, const double* w, double sigma, void* s) { return scale_input<float>(x, n, d, w, sigma, ST(s)); }
 int xgpr_b200_scale_input_f64(double* x, int64_t n, int64_t d, const double* w, double sigma, void* s) { return scale_input<double>(x, n, d, w, sigma, ST(s)); }

@@ -101,13 +101,19 @@ fht_cta2_kernel(T* __restrict__ x, const int8_t* __restrict__ radem, int64_t N, 
     constexpr int E = 32, K = 32, SEG = 1024, P = NS * SEG, THREADS = 32 * NS, GROUPS = SEG / THREADS;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int off = warp * SEG;
-    T sc[E];
+    constexpr bool BITS = sizeof(T) == 8;               // fp64: one sign word instead of 32 doubles (register budget)
+    T sc[BITS ? 1 : E];
+    uint32_t sbits = 0;
     if (SRHT) {
         // nseg > 1: the "rows" are consecutive P-element segments of longer rows (two-pass path); gridDim.x is a multiple
         // of nseg there, so this CTA always sees segment (blockIdx.x % nseg) and its slice of the sign vector
         const int8_t* rd = radem + (int64_t)(blockIdx.x % nseg) * P;
 #pragma unroll
-        for (int r = 0; r < E; ++r) sc[r] = (T)rd[off + lane + K * r] * cnorm;
+        for (int r = 0; r < E; ++r) {
+            const int8_t sv = rd[off + lane + K * r];
+            if (BITS) sbits |= (sv < 0 ? 1u : 0u) << r;
+            else sc[r] = (T)sv * cnorm;
+        }
     }
     T v[E];
     int64_t row = blockIdx.x;
@@ -118,7 +124,8 @@ fht_cta2_kernel(T* __restrict__ x, const int8_t* __restrict__ radem, int64_t N, 
     for (; row < N; row += gridDim.x) {
         if (SRHT) {
 #pragma unroll
-            for (int r = 0; r < E; ++r) v[r] = mul_rn(v[r], sc[r]);
+            for (int r = 0; r < E; ++r)
+                v[r] = BITS ? flip_sign(mul_rn(v[r], cnorm), (sbits >> r) & 1u) : mul_rn(v[r], sc[r]);
         }
         warp_fwht<T, E, K>(v, lane);
 #pragma unroll
@@ -168,6 +175,188 @@ static int launch_fht_cta2(T* x, int64_t n, const int8_t* radem, cudaStream_t st
     count_launch();
     return check_launch("fht_cta2_kernel");
 }
+
+// ------------------------------------------------------------------ fused SRHT + column sampling (the compressor)
+// SRHTCompressor.transform_x keeps `rank` of the P_M transformed columns (src/xGPR/kernels/srht_compressor.py:70-97:
+// pad to P_M, SRHT in place, gather perm[:rank]) -- three full passes over an n x P_M matrix to keep 512 of 16,384
+// columns.  Here the row is read ONCE (zero-padded on the fly from M to P_M columns), transformed exactly as
+// fht_cta2_kernel does, written back to shared memory only, and the sampled columns are gathered from there:
+// HBM traffic = n M sizeof(T) in + n rank sizeof(T) out.
+// CL = 2 (P_M = 2 x NS x 1024, e.g. 32,768 in fp64 where a row no longer fits one CTA's shared memory): a 2-CTA cluster,
+// each CTA transforms one half (strides up to P_M / 4); the last stride (P_M / 2) pairs element p of the low half with
+// element p of the high half, which only the SAMPLED positions need: out = lo[p] + hi[p] or lo[p] - hi[p], read from the
+// two CTAs' shared memory (DSMEM).  Split cluster barriers (arrive after the gather, wait before the next row's write)
+// keep the next row's register phase off the barrier's critical path.
+__device__ __forceinline__ void cl_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cl_wait()   { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+__device__ __forceinline__ unsigned cl_rank() {
+    unsigned r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+template <typename T>
+__device__ __forceinline__ T ld_dsmem(const T* local_ptr, unsigned rank) {
+    const unsigned a = (unsigned)__cvta_generic_to_shared(local_ptr);
+    unsigned ra;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(a), "r"(rank));
+    T v;
+    if (sizeof(T) == 8) {
+        double d;
+        asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(d) : "r"(ra) : "memory");
+        v = (T)d;
+    } else {
+        float f;
+        asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(f) : "r"(ra) : "memory");
+        v = (T)f;
+    }
+    return v;
+}
+
+template <typename T, int NS, int CL>
+__global__ void __launch_bounds__(32 * NS)
+srht_sample_kernel(const T* __restrict__ z, int64_t N, int64_t M, const int8_t* __restrict__ radem,
+                   const int32_t* __restrict__ cols, int rank, T* __restrict__ out, T cnorm) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int E = 32, K = 32, SEG = 1024, PH = NS * SEG, THREADS = 32 * NS, GROUPS = SEG / THREADS;
+    T* buf = reinterpret_cast<T*>(smem_raw);
+    int32_t* scols = reinterpret_cast<int32_t*>(buf + PH);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int off = warp * SEG;
+    const unsigned half = (CL == 2) ? cl_rank() : 0u;
+    const int64_t col0 = (int64_t)half * PH + off + lane;
+    for (int c = threadIdx.x; c < rank; c += THREADS) scols[c] = cols[c];
+    // +-cnorm per element: as values for float; for double as ONE sign word (x * (-c) == -(x * c) exactly), which keeps
+    // the 512-thread fp64 instances inside their 128-register budget
+    constexpr bool BITS = sizeof(T) == 8;
+    T sc[BITS ? 1 : E];
+    uint32_t sbits = 0;
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        const int8_t sv = radem[col0 + K * r];
+        if (BITS) sbits |= (sv < 0 ? 1u : 0u) << r;
+        else sc[r] = (T)sv * cnorm;
+    }
+    // this CTA's share of the sampled columns
+    const int share = (CL == 2) ? (rank + 1) / 2 : rank;
+    const int c_beg = (int)half * share, c_end = min(rank, c_beg + share);
+
+    const int64_t nrows_step = gridDim.x / CL;
+    int64_t row = blockIdx.x / CL;
+    T v[E];
+    if (row < N) {
+#pragma unroll
+        for (int r = 0; r < E; ++r) v[r] = (col0 + K * r < M) ? z[row * M + col0 + K * r] : T(0);
+    }
+    bool first = true;
+    for (; row < N; row += nrows_step) {
+#pragma unroll
+        for (int r = 0; r < E; ++r) v[r] = BITS ? flip_sign(mul_rn(v[r], cnorm), (sbits >> r) & 1u) : mul_rn(v[r], sc[r]);
+        warp_fwht<T, E, K>(v, lane);
+        if (!first) {                                    // every reader of the previous row's buf is done
+            if (CL == 2) cl_wait(); else __syncthreads();
+        }
+        first = false;
+#pragma unroll
+        for (int r = 0; r < E; ++r) buf[off + lane + K * r] = v[r];
+        __syncthreads();
+        const int64_t nxt = row + nrows_step;
+        if (nxt < N) {                                   // loads in flight during the shared-memory phases
+#pragma unroll
+            for (int r = 0; r < E; ++r) v[r] = (col0 + K * r < M) ? z[nxt * M + col0 + K * r] : T(0);
+        }
+#pragma unroll
+        for (int q = 0; q < GROUPS; ++q) {
+            const int o = threadIdx.x + q * THREADS;
+            T w[NS];
+#pragma unroll
+            for (int sidx = 0; sidx < NS; ++sidx) w[sidx] = buf[o + sidx * SEG];
+#pragma unroll
+            for (int h = 1; h < NS; h <<= 1)
+#pragma unroll
+                for (int i = 0; i < NS; ++i)
+                    if ((i & h) == 0) {
+                        const T a = w[i], b = w[i + h];
+                        w[i]     = add_rn(a, b);
+                        w[i + h] = sub_rn(a, b);
+                    }
+#pragma unroll
+            for (int sidx = 0; sidx < NS; ++sidx) buf[o + sidx * SEG] = w[sidx];
+        }
+        if (CL == 2) { cl_arrive(); cl_wait(); } else __syncthreads();
+        T* orow = out + row * rank;
+        for (int c = c_beg + threadIdx.x; c < c_end; c += THREADS) {
+            const int pos = scols[c];
+            if (CL == 2) {
+                const int p = pos & (PH - 1);
+                const T a = ld_dsmem<T>(buf + p, 0u), b = ld_dsmem<T>(buf + p, 1u);
+                orow[c] = (pos < PH) ? add_rn(a, b) : sub_rn(a, b);
+            } else {
+                orow[c] = buf[pos];
+            }
+        }
+        if (CL == 2) cl_arrive();
+    }
+    if (CL == 2 && !first) cl_wait();                    // do not exit while the peer may still read this CTA's buf
+}
+
+template <typename T, int NS, int CL>
+static int launch_srht_sample(const T* z, int64_t n, int64_t m, const int8_t* radem, const int32_t* cols, int rank,
+                              T* out, int64_t p_full, cudaStream_t st) {
+    const size_t smem = (size_t)NS * 1024 * sizeof(T) + (size_t)rank * sizeof(int32_t);
+    auto kern = srht_sample_kernel<T, NS, CL>;
+    ensure_dyn_smem(kern, smem);
+    int per_sm = (int)((220 * 1024) / smem);
+    if (per_sm < 1) per_sm = 1;
+    if (per_sm * 32 * NS > 2048) per_sm = 2048 / (32 * NS);
+    int64_t clusters = (int64_t)148 * per_sm / CL;
+    if (clusters > n) clusters = n;
+    if (clusters < 1) clusters = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(clusters * CL), 1, 1);
+    cfg.blockDim = dim3(32 * NS, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = CL;
+    attr.val.clusterDim.y = 1;
+    attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+    const T cnorm = norm_constant<T>(p_full);
+    cudaLaunchKernelEx(&cfg, kern, z, n, m, radem, cols, rank, out, cnorm);
+    count_launch();
+    return check_launch("srht_sample_kernel");
+}
+
+int srht_sample_supported(int64_t p_full, int elem_bytes) {
+    if (p_full == 32768) return 1;                                       // 2-CTA cluster, 16,384 per CTA
+    if (p_full < 1024 || p_full > 16384 || (p_full & (p_full - 1))) return 0;
+    return (size_t)p_full * elem_bytes <= 200 * 1024;
+}
+
+// out (n, rank) = SRHT(z zero-padded to p_full columns)[:, cols]
+template <typename T>
+int srht_sample(const T* z, int64_t n, int64_t m, const int8_t* radem, int64_t p_full, const int32_t* cols,
+                int64_t rank, T* out, cudaStream_t st) {
+    XB_REQUIRE(n > 0 && m > 0, "no datapoints");
+    XB_REQUIRE(z && radem && cols && out, "null pointer");
+    XB_REQUIRE(m <= p_full && rank > 0 && rank <= p_full && rank <= 8192, "incorrect array dims passed");
+    XB_REQUIRE(srht_sample_supported(p_full, (int)sizeof(T)), "fused SRHT sampling: unsupported padded width");
+    const int r = (int)rank;
+    switch (p_full) {
+        case 1024:  return launch_srht_sample<T, 1, 1>(z, n, m, radem, cols, r, out, p_full, st);
+        case 2048:  return launch_srht_sample<T, 2, 1>(z, n, m, radem, cols, r, out, p_full, st);
+        case 4096:  return launch_srht_sample<T, 4, 1>(z, n, m, radem, cols, r, out, p_full, st);
+        case 8192:  return launch_srht_sample<T, 8, 1>(z, n, m, radem, cols, r, out, p_full, st);
+        case 16384: return launch_srht_sample<T, 16, 1>(z, n, m, radem, cols, r, out, p_full, st);
+        default:    return launch_srht_sample<T, 16, 2>(z, n, m, radem, cols, r, out, p_full, st);
+    }
+}
+template int srht_sample<float>(const float*, int64_t, int64_t, const int8_t*, int64_t, const int32_t*, int64_t, float*,
+                                cudaStream_t);
+template int srht_sample<double>(const double*, int64_t, int64_t, const int8_t*, int64_t, const int32_t*, int64_t, double*,
+                                 cudaStream_t);
 
 // ------------------------------------------------------------------ row larger than shared memory
 // Pass A: the CTA kernel above on SEGP-element segments (treated as rows).  Pass B: the remaining

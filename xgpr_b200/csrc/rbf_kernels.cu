@@ -9,7 +9,6 @@
 // three sign-flip/FWHT rounds, the chi scale and cos/sin happen in registers (sorf_core.cuh), and the
 // interleaved fp64 [cos, sin] pairs leave through a padded per-warp shared-memory tile so that every
 // 128-bit global store of a warp covers whole 128-byte lines.  No scratch buffer, no per-call allocation.
-#define XB_SINCOS_DEFAULT_LEVEL 1   // HBM-bound fixed-vector kernels: polynomial cos / sin by default (sorf_core.cuh)
 #include "sorf_core.cuh"
 #include "sorf_warp.cuh"   // cta_sorf for P > 1024
 #include <stdlib.h>
@@ -175,9 +174,10 @@ rbf_core_kernel(const T* __restrict__ x, double* __restrict__ out, double* __res
 // Shared-memory kernel for P > 1024 (rare: more than 1024 input features).  One CTA per row.
 template <typename T>
 __device__ __forceinline__ void rbf_post(T v, T chi, double scale, double2* __restrict__ dst) {
-    const T a = mul_rn(v, chi);
-    T sn, cs;
-    sincos_t(a, &sn, &cs);
+    const T a[1] = {mul_rn(v, chi)};
+    T sn1[1], cs1[1];
+    sincos_group<1>(a, sn1, cs1);                    // honours the cos / sin accuracy level (sorf_core.cuh)
+    const T sn = sn1[0], cs = cs1[0];
     double2 o;
     o.x = (double)cs * scale;
     o.y = (double)sn * scale;
@@ -187,9 +187,10 @@ template <typename T>
 __device__ __forceinline__ void rbf_post_grad(T v, T chi, double scale, double sigma,
                                               double2* __restrict__ dst, double2* __restrict__ gdst) {
     const T g = mul_rn(v, chi);
-    const T p = (T)((double)g * sigma);
-    T sn, cs;
-    sincos_t(p, &sn, &cs);
+    const T p[1] = {(T)((double)g * sigma)};
+    T sn1[1], cs1[1];
+    sincos_group<1>(p, sn1, cs1);
+    const T sn = sn1[0], cs = cs1[0];
     const T cv = (T)((double)cs * scale);
     const T sv = (T)((double)sn * scale);
     double2 o, go;
@@ -235,9 +236,13 @@ rbf_cta_kernel(const T* __restrict__ x, double* __restrict__ out, double* __rest
 // thread finishes the NS = P / 1024 cross-segment strides in registers on {o + s * 1024}.  Two block barriers per round
 // instead of log2 P (cta_sorf above runs 11-14 per round and measured 0.19 of HBM, profiles/r02a_rbfcta_full.md); after
 // the third round the values are already spread thread-consecutively, so chi, cos / sin and the 16-byte [cos, sin] stores
-// follow directly, coalesced.  The zero-padded row is staged once per row and reused by every repeat.
-// Same butterflies in the same ascending-stride order, same one-rounding sign multiply as cta_sorf: bit-identical
-// pre-activations.
+// follow directly, coalesced.
+// A CTA owns ONE repeat (blockIdx.x, the fast grid index, so the CTAs that share a row run together and the row is read
+// from HBM once) and walks rows: the repeat's three sign diagonals live in 3 x 32 bits per lane for the whole kernel
+// (the first version re-read 96 sign bytes per lane per row from global memory and stalled on them: long-scoreboard 4.2,
+// issue 40 %, profiles/r02b_rbfcta_full.md), and the next row is prefetched into registers during the shared-memory phases.
+// Same butterflies in the same ascending-stride order; x * (-c) == -(x * c) exactly, so "multiply by c, flip the sign bit"
+// equals cta_sorf's one-rounding multiply by +-c: bit-identical pre-activations.
 template <typename T, int NS, bool GRAD>
 __global__ void __launch_bounds__(32 * NS)
 rbf_cta2_kernel(const T* __restrict__ x, double* __restrict__ out, double* __restrict__ grad,
@@ -245,67 +250,83 @@ rbf_cta2_kernel(const T* __restrict__ x, double* __restrict__ out, double* __res
                 int N, int D, int F, int64_t R, int reps, T cnorm, double scale, double sigma) {
     constexpr int E = 32, K = 32, SEG = 1024, P = NS * SEG, THREADS = 32 * NS, GROUPS = SEG / THREADS;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    T* xin = reinterpret_cast<T*>(smem_raw);
-    T* buf = xin + P;
+    T* buf = reinterpret_cast<T*>(smem_raw);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int off = warp * SEG;
-    for (int row = blockIdx.x; row < N; row += gridDim.x) {
-        const T* xr = x + (size_t)row * D;
-        for (int j = threadIdx.x; j < P; j += THREADS) xin[j] = (j < D) ? xr[j] : T(0);
-        __syncthreads();
+    const int rep = blockIdx.x;
+    const int64_t base = (int64_t)rep * P;
+    uint32_t sbits[3];
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+        uint32_t b = 0;
+        const int8_t* rd = radem + (int64_t)s * R + base + off + lane;
+#pragma unroll
+        for (int r = 0; r < E; ++r) b |= (rd[K * r] < 0 ? 1u : 0u) << r;
+        sbits[s] = b;
+    }
+    // chi of this thread's epilogue positions (o + sidx * SEG), invariant over rows when GROUPS == 1
+    T v[E];
+    int row = blockIdx.y;
+    if (row < N) {
+        const T* xr = x + (size_t)row * D + off + lane;
+#pragma unroll
+        for (int r = 0; r < E; ++r) v[r] = (off + lane + K * r < D) ? xr[K * r] : T(0);
+    }
+    for (; row < N; row += gridDim.y) {
         double2* orow = reinterpret_cast<double2*>(out + (size_t)row * 2 * F);
         double2* grow = GRAD ? reinterpret_cast<double2*>(grad + (size_t)row * 2 * F) : nullptr;
-        for (int rep = 0; rep < reps; ++rep) {
-            const int64_t base = (int64_t)rep * P;
-            T v[E];
-#pragma unroll
-            for (int r = 0; r < E; ++r) v[r] = xin[off + lane + K * r];
 #pragma unroll 1
-            for (int s = 0; s < 3; ++s) {
-                const int8_t* rd = radem + (int64_t)s * R + base + off + lane;
+        for (int s = 0; s < 3; ++s) {
+            const uint32_t sb = sbits[s];
 #pragma unroll
-                for (int r = 0; r < E; ++r) v[r] = mul_rn(v[r], (T)rd[K * r] * cnorm);     // one rounding, as cta_sorf
-                warp_fwht<T, E, K>(v, lane);
+            for (int r = 0; r < E; ++r) v[r] = flip_sign(mul_rn(v[r], cnorm), (sb >> r) & 1u);
+            warp_fwht<T, E, K>(v, lane);
 #pragma unroll
-                for (int r = 0; r < E; ++r) buf[off + lane + K * r] = v[r];
-                __syncthreads();
+            for (int r = 0; r < E; ++r) buf[off + lane + K * r] = v[r];
+            __syncthreads();
+            if (s == 2) {                                // next row's loads fly during the last shared-memory phase
+                const int nxt = row + gridDim.y;
+                if (nxt < N) {
+                    const T* xr = x + (size_t)nxt * D + off + lane;
 #pragma unroll
-                for (int q = 0; q < GROUPS; ++q) {
-                    const int o = threadIdx.x + q * THREADS;
-                    T w[NS];
+                    for (int r = 0; r < E; ++r) v[r] = (off + lane + K * r < D) ? xr[K * r] : T(0);
+                }
+            }
 #pragma unroll
-                    for (int sidx = 0; sidx < NS; ++sidx) w[sidx] = buf[o + sidx * SEG];
+            for (int q = 0; q < GROUPS; ++q) {
+                const int o = threadIdx.x + q * THREADS;
+                T w[NS];
 #pragma unroll
-                    for (int h = 1; h < NS; h <<= 1)
+                for (int sidx = 0; sidx < NS; ++sidx) w[sidx] = buf[o + sidx * SEG];
 #pragma unroll
-                        for (int i = 0; i < NS; ++i)
-                            if ((i & h) == 0) {
-                                const T a = w[i], b = w[i + h];
-                                w[i]     = add_rn(a, b);
-                                w[i + h] = sub_rn(a, b);
-                            }
-                    if (s < 2) {
+                for (int h = 1; h < NS; h <<= 1)
 #pragma unroll
-                        for (int sidx = 0; sidx < NS; ++sidx) buf[o + sidx * SEG] = w[sidx];
-                    } else {
+                    for (int i = 0; i < NS; ++i)
+                        if ((i & h) == 0) {
+                            const T a = w[i], b = w[i + h];
+                            w[i]     = add_rn(a, b);
+                            w[i + h] = sub_rn(a, b);
+                        }
+                if (s < 2) {
 #pragma unroll
-                        for (int sidx = 0; sidx < NS; ++sidx) {
-                            const int64_t idx = base + o + sidx * SEG;
-                            if (idx < F) {
-                                if (GRAD) rbf_post_grad<T>(w[sidx], chi[idx], scale, sigma, orow + idx, grow + idx);
-                                else      rbf_post<T>(w[sidx], chi[idx], scale, orow + idx);
-                            }
+                    for (int sidx = 0; sidx < NS; ++sidx) buf[o + sidx * SEG] = w[sidx];
+                } else {
+#pragma unroll
+                    for (int sidx = 0; sidx < NS; ++sidx) {
+                        const int64_t idx = base + o + sidx * SEG;
+                        if (idx < F) {
+                            if (GRAD) rbf_post_grad<T>(w[sidx], chi[idx], scale, sigma, orow + idx, grow + idx);
+                            else      rbf_post<T>(w[sidx], chi[idx], scale, orow + idx);
                         }
                     }
                 }
-                __syncthreads();                         // cross-segment reads / writes of buf are complete
-                if (s < 2) {
+            }
+            __syncthreads();                             // cross-segment reads / writes of buf are complete
+            if (s < 2) {
 #pragma unroll
-                    for (int r = 0; r < E; ++r) v[r] = buf[off + lane + K * r];
-                }
+                for (int r = 0; r < E; ++r) v[r] = buf[off + lane + K * r];
             }
         }
-        __syncthreads();                                 // xin is rewritten by the next row
     }
 }
 
@@ -314,17 +335,20 @@ static int launch_cta2(const T* x, int64_t n, int64_t d, double* out, double* gr
                        const T* chi, int64_t F, double scale, double sigma, cudaStream_t st) {
     constexpr int64_t P = (int64_t)NS * 1024;
     const int reps = (int)((F + P - 1) / P);
-    const size_t smem = 2 * (size_t)P * sizeof(T);
+    const size_t smem = (size_t)P * sizeof(T);
     auto kern = rbf_cta2_kernel<T, NS, GRAD>;
     ensure_dyn_smem(kern, smem);
     int per_sm = (int)((220 * 1024) / smem);
     if (per_sm * 32 * NS > 2048) per_sm = 2048 / (32 * NS);
     if (per_sm > 16) per_sm = 16;
     if (per_sm < 1) per_sm = 1;
-    int64_t blocks = (int64_t)148 * per_sm;
-    if (blocks > n) blocks = n;
-    kern<<<(unsigned)blocks, 32 * NS, smem, st>>>(x, out, grad, radem, chi, (int)n, (int)d, (int)F, R, reps,
-                                                 norm_constant<T>(P), scale, sigma);
+    int64_t gy = ((int64_t)148 * per_sm + reps - 1) / reps;      // row lanes: one resident wave over all repeats
+    if (gy > n) gy = n;
+    if (gy > 65535) gy = 65535;
+    if (gy < 1) gy = 1;
+    dim3 grid((unsigned)reps, (unsigned)gy);
+    kern<<<grid, 32 * NS, smem, st>>>(x, out, grad, radem, chi, (int)n, (int)d, (int)F, R, reps,
+                                      norm_constant<T>(P), scale, sigma);
     count_launch();
     return check_launch("rbf_cta2_kernel");
 }
@@ -423,7 +447,7 @@ int rbf_dispatch(const T* x, int64_t n, int64_t d, double* out, double* grad, in
     }
 #undef XB_CASE
     static const bool cta_v1 = getenv("XGPR_B200_RBF_CTA_V1") != nullptr;
-    if (!cta_v1 && 2 * (size_t)P * sizeof(T) <= 200 * 1024) {
+    if (!cta_v1 && (size_t)P * sizeof(T) <= 200 * 1024 && (F + P - 1) / P <= 65535) {
         switch (P) {
             case 2048:  return launch_cta2<T, 2, GRAD>(x, n, d, out, grad, radem, R, chi, F, scale, sigma, st);
             case 4096:  return launch_cta2<T, 4, GRAD>(x, n, d, out, grad, radem, R, chi, F, scale, sigma, st);

@@ -10,7 +10,6 @@
 //   ZV  : per (row, repeat) slot, dot of the slot's (cos, sin) pairs with v; warp reduce; one fp64 atomic per warp
 //   ZTV : per slot, fp64 register accumulators over the CTA's rows of t[row] * (cos, sin); atomics into w at the end
 // The intercept column (Z[:, 0] = 1, kernel_baseclass.py:296-297) is honoured in both.
-#define XB_SINCOS_DEFAULT_LEVEL 1   // HBM-bound fixed-vector kernels: polynomial cos / sin by default (sorf_core.cuh)
 #include "sorf_core.cuh"
 
 namespace xb {

@@ -28,8 +28,7 @@ _ACCURATE = {"level": _env_level(), "devices": set()}
 
 def set_accurate_sincos(level):
     """float32 cos / sin of the feature kernels (include/xgpr_b200.h): 0 / False = Cody-Waite + MUFU (<= ~4e-7 absolute),
-    1 / True = polynomial on the FMA pipe (<= 7e-8), 2 = CUDA's sincosf, -1 / None = the per-kernel-family defaults
-    (fixed-vector kernels 1, convolution kernels 0).  Also selectable with XGPR_B200_ACCURATE_SINCOS=<level>.  The setting
+    1 / True = polynomial on the FMA pipe (<= 7e-8), 2 = CUDA's sincosf, -1 / None = the default (0).  Also selectable with XGPR_B200_ACCURATE_SINCOS=<level>.  The setting
     is a per-device constant: it is (re)applied lazily to every device the next call launches on."""
     _ACCURATE["level"] = -1 if level is None else int(level)
     _ACCURATE["devices"].clear()
@@ -89,6 +88,25 @@ def cudaSRHT(inputArr, radem):
     check(getattr(lib, "xgpr_b200_srht" + _SFX[x.dtype])(x.data_ptr(), x.shape[0], x.shape[1], r.data_ptr(),
                                                          r.shape[0], _stream()))
     return 0
+
+
+def srht_sample_supported(p_full, dtype):
+    return bool(lib.xgpr_b200_srht_sample_supported(int(p_full), 8 if dtype == torch.float64 else 4))
+
+
+def srht_sample(z, radem, cols, out):
+    """out (n, rank) = SRHT(z zero-padded to len(radem) columns)[:, cols] in one pass over z (z is not modified):
+    SRHTCompressor.transform_x fused (srht_compressor.py:70-97).  cols: int32 device vector."""
+    z = _dev(z, "z", _SFX, 2)
+    r = _dev(radem, "radem", (torch.int8,), 1)
+    c = _dev(cols, "cols", (torch.int32,), 1)
+    o = _dev(out, "out", (z.dtype,), 2)
+    if o.shape[0] != z.shape[0] or o.shape[1] != c.shape[0] or z.shape[1] > r.shape[0]:
+        raise RuntimeError("wrong array sizes")
+    check(getattr(lib, "xgpr_b200_srht_sample" + _SFX[z.dtype])(z.data_ptr(), z.shape[0], z.shape[1], r.data_ptr(),
+                                                               r.shape[0], c.data_ptr(), c.shape[0], o.data_ptr(),
+                                                               _stream()))
+    return out
 
 
 def scale_input_(x, sigma=1.0, col_weights=None):

@@ -36,6 +36,16 @@ class SRHTCompressor:
             raise RuntimeError("xgpr_b200 runs on device='cuda' only (no CPU fallback).")
         if len(features.shape) != 2 or features.shape[1] != self.input_size:
             raise RuntimeError("Input with unexpected size passed to a compressor module.")
+        if not no_compression and isinstance(features, torch.Tensor) and features.is_cuda and features.dim() == 2 \
+                and ext.srht_sample_supported(self.padded_dims, self.dtype):
+            # one pass: read the chunk once, write only the sampled columns (csrc/fht_kernels.cu srht_sample_kernel)
+            src = features if (features.dtype == self.dtype and features.is_contiguous()) else \
+                features.to(self.dtype).contiguous()
+            cols = getattr(self, "_cols_i32", None)
+            if cols is None or cols.device != src.device:
+                cols = self._cols_i32 = self.truncated_sampler.to(device=src.device, dtype=torch.int32).contiguous()
+            out = torch.empty((src.shape[0], self.compression_size), dtype=self.dtype, device=src.device)
+            return ext.srht_sample(src, self.radem, cols, out)
         if features.shape[1] < self.padded_dims:
             xfeatures = torch.zeros((features.shape[0], self.padded_dims), dtype=self.dtype, device=features.device)
             xfeatures[:, :features.shape[1]] = features

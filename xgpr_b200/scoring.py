@@ -118,14 +118,22 @@ def _cho_solve(chol, target):
 
 def exact_nmll_reg_grad(z_trans_z, z_trans_y, y_trans_y, hparams, ndatapoints, dz_dsigma_ty, inner_deriv):
     """NMLL and its gradient w/r/t the LOG hyperparameters.  nmll_gradient_tools.py:94-161; z_trans_z is modified in
-    place exactly as there (lambda^2 added, then removed again after the factorisation)."""
+    place exactly as there (lambda^2 added, then removed again after the factorisation).
+
+    Same quantities, different algebra for the two O(M^3) pieces the reference flags "TODO: Optimize" (:172, :181-183).
+    With A = Z^T Z + lambda^2 I = L L^T the reference forms L^-1 explicitly for ||L^-1||_F^2 (:205, :151) and, per
+    kernel hyperparameter, solves A X = D_i with M right-hand sides only to take trace(X) (:155, :159) -- 1/3 + 2 nh
+    M^3-sized triangular solves.  Both are traces against A^-1:
+        ||L^-1||_F^2 = trace(A^-1),        trace(A^-1 D_i) = sum(A^-1 o D_i)   (D_i = dZ_i^T Z + Z^T dZ_i is symmetric),
+    so ONE Cholesky inverse (potri, 2/3 M^3) serves every hyperparameter and the per-hyperparameter work drops to an
+    O(M^2) elementwise sum: 2.7x fewer flops for one lengthscale, 4.7x for MiniARD with two."""
     m = z_trans_z.shape[0]
     lam = float(hparams[0])
     z_trans_z.diagonal().add_(lam ** 2)
     chol = torch.linalg.cholesky(z_trans_z)
     weights = _cho_solve(chol, z_trans_y)
     z_trans_z.diagonal().sub_(lam ** 2)
-    chol_inv = torch.linalg.solve_triangular(chol, torch.eye(m, dtype=torch.float64, device=chol.device), upper=False)
+    a_inv = torch.cholesky_inverse(chol)
     nll1 = float(0.5 * (y_trans_y - z_trans_y @ weights))
     nll2 = float(torch.log(chol.diagonal()).sum())
     negloglik, beta = optimize_alpha_beta(lam, np.array([nll1, nll2]), float(ndatapoints), float(m))
@@ -135,14 +143,14 @@ def exact_nmll_reg_grad(z_trans_z, z_trans_y, y_trans_y, hparams, ndatapoints, d
     dnll_dlambda = (1 / (beta ** 2 * lam ** 3)) * (float(z_trans_y @ weights) - y_trans_y)
     dnll_dlambda += (1 / (beta ** 2 * lam)) * float(weights @ weights)
     dnll_dlambda += (ndatapoints - m) / lam
-    dnll_dlambda += lam * float((chol_inv ** 2).sum())
+    dnll_dlambda += lam * float(a_inv.diagonal().sum())
     grad[0] = float(dnll_dlambda)
     for i in range(grad.shape[0] - 1):
-        trace_term = _cho_solve(chol, inner_deriv[:, :, i].contiguous())
+        d_i = inner_deriv[:, :, i]
         dnll_dsigma = -2 * float(weights @ dz_dsigma_ty[:, i])
-        dnll_dsigma += float(weights @ (inner_deriv[:, :, i] @ weights))
+        dnll_dsigma += float(weights @ (d_i @ weights))
         dnll_dsigma *= (0.5 / alpha ** 2)
-        dnll_dsigma += 0.5 * float(trace_term.diagonal().sum())
+        dnll_dsigma += 0.5 * float((a_inv * d_i).sum())
         grad[i + 1] = float(dnll_dsigma)
     grad *= hparams
     return negloglik, grad, beta
