@@ -17,7 +17,8 @@ def _stale():
     if not os.path.exists(LIB):
         return True
     t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "xgpr_b200.h")]
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f != "nb_module.cpp"] + \
+        [os.path.join(HERE, "..", "include", "xgpr_b200.h")]
     return any(os.path.getmtime(d) > t for d in deps)
 
 
@@ -46,6 +47,38 @@ def build(force=False, verbose=False):
     if verbose:
         print("\n".join(log))
     return LIB
+
+
+NB_DIRS = [os.environ.get("XGPR_B200_NANOBIND", ""), "/root/reference/ext/nanobind"]
+
+
+def nanobind_module_path():
+    import sysconfig
+    return os.path.join(LIBDIR, "xgpr_cuda_rfgen_cpp_ext" + sysconfig.get_config_var("EXT_SUFFIX"))
+
+
+def build_nanobind(force=False):
+    """The nanobind face of the C ABI (csrc/nb_module.cpp -> lib/xgpr_cuda_rfgen_cpp_ext.<abi>.so, linked against
+    libxgpr_b200.so next to it).  Needs the nanobind sources: the reference vendors them (ext/nanobind); without them
+    (e.g. on the GPU box) the prebuilt module that travelled with the tree is used, or the ctypes face alone.
+    Returns the module path or None."""
+    import sysconfig
+    nb = next((d for d in NB_DIRS if d and os.path.exists(os.path.join(d, "src", "nb_combined.cpp"))), None)
+    out = nanobind_module_path()
+    src = os.path.join(CSRC, "nb_module.cpp")
+    if nb is None:
+        return out if os.path.exists(out) else None
+    deps = [src, os.path.join(HERE, "..", "include", "xgpr_b200.h")]
+    if not force and os.path.exists(out) and all(os.path.getmtime(d) <= os.path.getmtime(out) for d in deps):
+        return out
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    cmd = [cxx, "-std=c++17", "-O2", "-DNDEBUG", "-fPIC", "-shared", "-fvisibility=hidden", "-fno-strict-aliasing",
+           "-DNB_COMPACT_ASSERTIONS", "-I" + os.path.join(nb, "include"),
+           "-I" + os.path.join(nb, "ext", "robin_map", "include"), "-I" + sysconfig.get_paths()["include"],
+           src, os.path.join(nb, "src", "nb_combined.cpp"), "-o", out, "-L" + LIBDIR, "-lxgpr_b200",
+           "-Wl,-rpath,$ORIGIN"]
+    subprocess.check_call(cmd)
+    return out
 
 
 if __name__ == "__main__":
