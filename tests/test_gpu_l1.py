@@ -219,7 +219,6 @@ def test_conv_accumulates_into_output():
     np.testing.assert_allclose(out.cpu().numpy() - 2.5, ref, rtol=1e-5, atol=1e-5 * float(np.abs(ref).max()))
 
 
-@pytest.mark.parametrize("path", golden_files("l1_ard_"), ids=os.path.basename)
 def _ard_tol(dt, ref):
     """fp64: the tensor-core (DMMA) kernel sums the same products as the oracle in a different order -> 1e-9.
     float32: the oracle rounds every product x W to float before widening it (ard_ops.cpp:98); the DMMA kernel keeps the
@@ -230,6 +229,7 @@ def _ard_tol(dt, ref):
     return dict(rtol=1e-5, atol=1e-5 * float(np.abs(ref).max()))
 
 
+@pytest.mark.parametrize("path", golden_files("l1_ard_"), ids=os.path.basename)
 def test_ard_golden(path, monkeypatch):
     g = load_golden(path)
     ext = _ext()
