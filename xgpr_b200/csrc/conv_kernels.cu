@@ -16,6 +16,7 @@
 #include <stdlib.h>
 #include <unordered_map>
 #include <utility>
+#include <vector>
 
 namespace xb {
 
@@ -56,20 +57,21 @@ __device__ __forceinline__ void cv_mbar_wait(unsigned bar, unsigned parity) {
 // overlapping window is served on-chip and global memory sees each input element once per repeat group.  The copy is ONE
 // 1-D bulk copy (TMA, cp.async.bulk + mbarrier) per sequence -- a sequence's seqlen * C leading elements are contiguous --
 // issued by one thread, whenever the rows are 16-byte aligned (`bulk`); otherwise element-wise cp.async.
-template <typename T, int P, int E, int MODE, int WARPS, bool SMEMX>
+template <typename T, int P, int E, int MODE, int WARPS, bool SMEMX, int CHSEL = 8>
 __global__ void __launch_bounds__(WARPS * 32, (E <= 16 && sizeof(T) == 4 && MODE != CONV_GRAD) ? 2 : 1)
 conv_core_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __restrict__ grad,
                  const int8_t* __restrict__ radem, const T* __restrict__ chi,
                  const int32_t* __restrict__ seqlen, int N, int M, int C, int F, int64_t R,
                  int reps, int RC, int conv_width, int scaling_type, T cnorm, T fold, double base_scale,
-                 double sigma, int tile_elems, int bulk) {
+                 double sigma, int tile_elems, int bulk, const int32_t* __restrict__ order) {
     constexpr int K = P / E;
     constexpr int V = 32 / K;
     constexpr int S = WARPS * V;
     constexpr bool FOLD = is_pow4(P);
-    // cos / sin group size: 4 for the float sum-pool instance at E = 16, whose 32 fp64 accumulators + 16 chi values leave
-    // no room for 3 x 8 temporaries under the 128-register cap of 2 CTAs / SM (it spilled 44-52 bytes with groups of 8)
-    constexpr int CH = (MODE == CONV_FGEN && sizeof(T) == 4 && E == 16) ? 4 : cmin(8, E);
+    // cos / sin group size CHSEL: 8, or 4 for the float sum-pool instance at E = 16 when XGPR_B200_CONV_CH4 is set (its 32
+    // fp64 accumulators + 16 chi values spill 44-52 bytes with groups of 8 under the 128-register cap of 2 CTAs / SM;
+    // groups of 4 spill 4-16 bytes but pay twice the range checks -- measured a wash, profiles/r02d)
+    constexpr int CH = cmin(CHSEL, E);
     constexpr int CPITCH = ChiTile<T, E>::PITCH;
     constexpr int NACC = (MODE == CONV_GRAD) ? 4 : ((MODE == CONV_FGEN) ? 2 : 0);
 
@@ -85,7 +87,11 @@ conv_core_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __re
     const int rep = rep0 + rl_rep;
     const int rowlane = g / RC;
     const int nrl = S / RC;
-    const int row = blockIdx.x * nrl + rowlane;
+    // `order` lists the sequences longest first (host, counting sort): CTAs are dispatched in blockIdx order, so the long
+    // sequences start early and the short ones fill the tail of the grid (LPT scheduling), and the sequences that share
+    // a CTA have similar lengths.  Ragged batches lost ~10 % to tail imbalance in natural order.
+    const int slot_row = blockIdx.x * nrl + rowlane;
+    const int row = (slot_row < N) ? (order ? order[slot_row] : slot_row) : N;
     const bool ok = (rep < reps) && (row < N);
     const int64_t base = (int64_t)rep * P;
     const int wlen = conv_width * C;
@@ -99,14 +105,16 @@ conv_core_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __re
                 cv_mbar_init(bar, 1);
                 unsigned total = 0;
                 for (int rl = 0; rl < nrl; ++rl) {
-                    const int rw = blockIdx.x * nrl + rl;
-                    if (rw >= N) break;
+                    const int sr = blockIdx.x * nrl + rl;
+                    if (sr >= N) break;
+                    const int rw = order ? order[sr] : sr;
                     total += (unsigned)((min(seqlen[rw] * C, tile_elems) * (int)sizeof(T) + 15) & ~15);
                 }
                 cv_mbar_expect_tx(bar, total);
                 for (int rl = 0; rl < nrl; ++rl) {
-                    const int rw = blockIdx.x * nrl + rl;
-                    if (rw >= N) break;
+                    const int sr = blockIdx.x * nrl + rl;
+                    if (sr >= N) break;
+                    const int rw = order ? order[sr] : sr;
                     const unsigned bytes = (unsigned)((min(seqlen[rw] * C, tile_elems) * (int)sizeof(T) + 15) & ~15);
                     cv_bulk_g2s((unsigned)__cvta_generic_to_shared(xtile + (size_t)rl * tile_elems),
                                 x + (size_t)rw * M * C, bytes, bar);
@@ -114,8 +122,9 @@ conv_core_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __re
             }
         } else {
             for (int rl = 0; rl < nrl; ++rl) {
-                const int rw = blockIdx.x * nrl + rl;
-                if (rw >= N) break;
+                const int sr = blockIdx.x * nrl + rl;
+                if (sr >= N) break;
+                const int rw = order ? order[sr] : sr;
                 const int cnt = min(seqlen[rw] * C, tile_elems);
                 const T* src = x + (size_t)rw * M * C;
                 T* dst = xtile + (size_t)rl * tile_elems;
@@ -306,16 +315,22 @@ struct SeqKeyHash { size_t operator()(const std::pair<int, void*>& k) const {
     return std::hash<void*>()(k.second) ^ (std::hash<int>()(k.first) * 0x9e3779b97f4a7c15ull); } };
 static std::unordered_map<std::pair<int, void*>, SeqBuf, SeqKeyHash> g_seq;
 
-static int stage_seqlen(const int32_t* host, int64_t n, cudaStream_t st, const int32_t** dev_out) {
+// dev_out[0..n) = seqlengths; when the lengths differ, order_out = dev_out + n lists the sequences longest first
+// (counting sort over the lengths, O(n + max length); nullptr when they are all equal).
+static int stage_seqlen(const int32_t* host, int64_t n, int32_t min_len, int32_t max_len, cudaStream_t st,
+                        const int32_t** dev_out, const int32_t** order_out) {
     std::lock_guard<std::mutex> lk(g_seq_mu);
     SeqBuf& b = g_seq[std::make_pair(current_device(), (void*)st)];
-    if (b.cap < (size_t)n) {
+    const bool ragged = (max_len > min_len) && n > 1;
+    *order_out = nullptr;
+    const int64_t need = ragged ? 2 * n : n;
+    if (b.cap < (size_t)need) {
         if (b.dev) {
             cudaStreamSynchronize(st);
             cudaFree(b.dev);
         }
         size_t cap = 1024;
-        while (cap < (size_t)n) cap <<= 1;
+        while (cap < (size_t)need) cap <<= 1;
         if (cudaMalloc(&b.dev, cap * sizeof(int32_t)) != cudaSuccess) {
             b.dev = nullptr; b.cap = 0;
             cudaGetLastError();
@@ -327,6 +342,20 @@ static int stage_seqlen(const int32_t* host, int64_t n, cudaStream_t st, const i
     if (cudaMemcpyAsync(b.dev, host, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st) != cudaSuccess) {
         set_error("seqlengths copy failed: %s", cudaGetErrorString(cudaGetLastError()));
         return XGPR_B200_ECUDA;
+    }
+    if (ragged) {
+        static thread_local std::vector<int32_t> order, start;
+        order.resize((size_t)n);
+        start.assign((size_t)(max_len - min_len) + 2, 0);
+        for (int64_t i = 0; i < n; ++i) ++start[(size_t)(max_len - host[i]) + 1];      // bucket 0 = the longest
+        for (size_t k = 1; k < start.size(); ++k) start[k] += start[k - 1];
+        for (int64_t i = 0; i < n; ++i) order[(size_t)start[(size_t)(max_len - host[i])]++] = (int32_t)i;
+        // pageable source: cudaMemcpyAsync returns once the buffer has been staged, so `order` may be reused afterwards
+        if (cudaMemcpyAsync(b.dev + n, order.data(), (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st) != cudaSuccess) {
+            set_error("seqlengths copy failed: %s", cudaGetErrorString(cudaGetLastError()));
+            return XGPR_B200_ECUDA;
+        }
+        *order_out = b.dev + n;
     }
     *dev_out = b.dev;
     return XGPR_B200_OK;
@@ -344,7 +373,7 @@ template <typename T, int MODE> __host__ __device__ constexpr int conv_e(int p) 
 template <typename T, int P, int MODE>
 static int launch_conv_core(const T* x, int64_t n, int64_t m, int64_t c, void* out, double* grad,
                             const int8_t* radem, int64_t R, const T* chi, int64_t F, const int32_t* seq_dev,
-                            int max_seqlen, int conv_width, int scaling_type, double base_scale, double sigma,
+                            const int32_t* order_dev, int max_seqlen, int conv_width, int scaling_type, double base_scale, double sigma,
                             cudaStream_t st) {
     constexpr int E = conv_e<T, MODE>(P);
     constexpr int K = P / E;
@@ -370,17 +399,25 @@ static int launch_conv_core(const T* x, int64_t n, int64_t m, int64_t c, void* o
     dim3 grid((unsigned)((n + nrl - 1) / nrl), (unsigned)((reps + RC - 1) / RC));
     if (chi_bytes + x_bytes <= 100 * 1024) {
         const size_t smem = chi_bytes + x_bytes;   // chi_bytes and every sequence tile are multiples of 16 bytes
-        auto kern = conv_core_kernel<T, P, E, MODE, WARPS, true>;
-        ensure_dyn_smem(kern, smem);
-        kern<<<grid, WARPS * 32, smem, st>>>(x, out, grad, radem, chi, seq_dev, (int)n, (int)m, (int)c, (int)F, R,
-                                             reps, RC, conv_width, scaling_type, cn, fold, base_scale, sigma,
-                                             tile_elems, bulk);
+        if (MODE == CONV_FGEN && sizeof(T) == 4 && E == 16 && getenv("XGPR_B200_CONV_CH4")) {
+            auto kern = conv_core_kernel<T, P, E, MODE, WARPS, true, 4>;
+            ensure_dyn_smem(kern, smem);
+            kern<<<grid, WARPS * 32, smem, st>>>(x, out, grad, radem, chi, seq_dev, (int)n, (int)m, (int)c, (int)F, R,
+                                                 reps, RC, conv_width, scaling_type, cn, fold, base_scale, sigma,
+                                                 tile_elems, bulk, order_dev);
+        } else {
+            auto kern = conv_core_kernel<T, P, E, MODE, WARPS, true>;
+            ensure_dyn_smem(kern, smem);
+            kern<<<grid, WARPS * 32, smem, st>>>(x, out, grad, radem, chi, seq_dev, (int)n, (int)m, (int)c, (int)F, R,
+                                                 reps, RC, conv_width, scaling_type, cn, fold, base_scale, sigma,
+                                                 tile_elems, bulk, order_dev);
+        }
     } else {
         auto kern = conv_core_kernel<T, P, E, MODE, WARPS, false>;
         ensure_dyn_smem(kern, chi_bytes);
         kern<<<grid, WARPS * 32, chi_bytes, st>>>(x, out, grad, radem, chi, seq_dev, (int)n, (int)m, (int)c, (int)F,
                                                   R, reps, RC, conv_width, scaling_type, cn, fold, base_scale,
-                                                  sigma, 0, 0);
+                                                  sigma, 0, 0, order_dev);
     }
     count_launch();
     return check_launch("conv_core_kernel");
@@ -412,12 +449,14 @@ int conv_dispatch(const T* x, int64_t n, int64_t m, int64_t c, void* out, int64_
                "All sequence lengths must be >= conv width and < array size.");
 
     const int32_t* seq_dev = nullptr;
-    int rc = stage_seqlen(seq_host, n, st, &seq_dev);
+    const int32_t* order_dev = nullptr;
+    // XGPR_B200_CONV_NO_ORDER: natural order (A/B switch for the longest-first dispatch)
+    int rc = stage_seqlen(seq_host, n, getenv("XGPR_B200_CONV_NO_ORDER") ? mxl : mn, mxl, st, &seq_dev, &order_dev);
     if (rc != XGPR_B200_OK) return rc;
     const double base_scale = sqrt(1.0 / (double)F);   // rbf_convolution.cpp:40
 
 #define XB_CASE(PP)                                                                                        \
-    case PP: return launch_conv_core<T, PP, MODE>(x, n, m, c, out, grad, radem, R, chi, F, seq_dev, (int)mxl, \
+    case PP: return launch_conv_core<T, PP, MODE>(x, n, m, c, out, grad, radem, R, chi, F, seq_dev, order_dev, (int)mxl, \
                                                   conv_width, scaling_type, base_scale, sigma, st);
     switch (P) {
         XB_CASE(2) XB_CASE(4) XB_CASE(8) XB_CASE(16) XB_CASE(32) XB_CASE(64)

@@ -244,7 +244,7 @@ rbf_cta_kernel(const T* __restrict__ x, double* __restrict__ out, double* __rest
 // Same butterflies in the same ascending-stride order; x * (-c) == -(x * c) exactly, so "multiply by c, flip the sign bit"
 // equals cta_sorf's one-rounding multiply by +-c: bit-identical pre-activations.
 template <typename T, int NS, bool GRAD>
-__global__ void __launch_bounds__(32 * NS)
+__global__ void __launch_bounds__(32 * NS, (sizeof(T) == 4 && NS <= 8) ? 640 / (32 * NS) : 1)   // >= 20 warps / SM in float
 rbf_cta2_kernel(const T* __restrict__ x, double* __restrict__ out, double* __restrict__ grad,
                 const int8_t* __restrict__ radem, const T* __restrict__ chi,
                 int N, int D, int F, int64_t R, int reps, T cnorm, double scale, double sigma) {
@@ -362,10 +362,10 @@ __host__ __device__ constexpr int rbf_k(int p) {
     return cmin(32, (p / 16 > cmin(4, p / 2)) ? p / 16 : cmin(4, p / 2));
 }
 
-template <typename T, int P, bool GRAD, bool C32 = false>
+template <typename T, int P, bool GRAD, bool C32 = false, int KDIV = 1>
 static int launch_core(const T* x, int64_t n, int64_t d, double* out, double* grad, const int8_t* radem,
                        int64_t R, const T* chi, int64_t F, double scale, double sigma, cudaStream_t st) {
-    constexpr int K = rbf_k(P);
+    constexpr int K = rbf_k(P) / KDIV;               // KDIV = 2: twice the elements per lane, one shuffle stage fewer
     constexpr int E = P / K;
     constexpr int WARPS = 8;
     constexpr int V = 32 / K;
@@ -438,6 +438,11 @@ int rbf_dispatch(const T* x, int64_t n, int64_t d, double* out, double* grad, in
     double scale = fit_intercept ? sqrt(1.0 / (ff - 0.5)) : sqrt(1.0 / ff);
     if (!GRAD) scale = (double)(T)scale;
 
+    // experiment switch: float32 P = 512 / 1024 with 32 / 64 elements per lane (K = 16): 4 shuffle stages instead of 5
+    if (sizeof(T) == 4 && !GRAD && getenv("XGPR_B200_RBF_WIDE_E")) {
+        if (P == 512) return launch_core<T, 512, GRAD, false, 2>(x, n, d, out, grad, radem, R, chi, F, scale, sigma, st);
+        if (P == 1024) return launch_core<T, 1024, GRAD, false, 2>(x, n, d, out, grad, radem, R, chi, F, scale, sigma, st);
+    }
 #define XB_CASE(PP) \
     case PP: return launch_core<T, PP, GRAD>(x, n, d, out, grad, radem, R, chi, F, scale, sigma, st);
     switch (P) {
