@@ -202,13 +202,24 @@ conv_core_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __re
                         // (differs from the oracle's per-window multiply by <= 1 ulp of fp64)
                         acc[r0 + i][0] = __dadd_rn(acc[r0 + i][0], (double)cs[i]);
                         acc[r0 + i][1] = __dadd_rn(acc[r0 + i][1], (double)sn[i]);
-                    } else {
+                    } else if (sizeof(T) == 8) {
+                        // T = double: exactly the oracle's expressions (shared_rfgen_ops.cpp:142-155)
                         const T cv = (T)((double)cs[i] * scale);
                         const T sv = (T)((double)sn[i] * scale);
                         acc[r0 + i][0] = __dadd_rn(acc[r0 + i][0], (double)cv);
                         acc[r0 + i][1] = __dadd_rn(acc[r0 + i][1], (double)sv);
                         acc[r0 + i][2] = __dsub_rn(acc[r0 + i][2], (double)mul_rn(sv, gv[i]));
                         acc[r0 + i][3] = __dadd_rn(acc[r0 + i][3], (double)mul_rn(cv, gv[i]));
+                    } else {
+                        // T = float: the oracle rounds cosVal / sinVal and the two products to float before widening them
+                        // again -- 8 conversions per value on the 16-lane XU pipe, which bound this mode at 0.37 of the
+                        // issue roof (r01).  Here the three float values are widened once and the rest is fp64: 3 XU
+                        // conversions instead of 8, each term within 6e-8 relative of the oracle's (contract: 1e-5).
+                        const double cd = (double)cs[i] * scale, sd = (double)sn[i] * scale, gd = (double)gv[i];
+                        acc[r0 + i][0] = __dadd_rn(acc[r0 + i][0], cd);
+                        acc[r0 + i][1] = __dadd_rn(acc[r0 + i][1], sd);
+                        acc[r0 + i][2] = fma(-sd, gd, acc[r0 + i][2]);
+                        acc[r0 + i][3] = fma(cd, gd, acc[r0 + i][3]);
                     }
                 }
             }

@@ -438,8 +438,9 @@ int rbf_dispatch(const T* x, int64_t n, int64_t d, double* out, double* grad, in
     double scale = fit_intercept ? sqrt(1.0 / (ff - 0.5)) : sqrt(1.0 / ff);
     if (!GRAD) scale = (double)(T)scale;
 
-    // experiment switch: float32 P = 512 / 1024 with 32 / 64 elements per lane (K = 16): 4 shuffle stages instead of 5
-    if (sizeof(T) == 4 && !GRAD && getenv("XGPR_B200_RBF_WIDE_E")) {
+    // float32 P = 512 / 1024: 32 / 64 elements per lane (K = 16), i.e. 4 shuffle stages instead of 5 -- the MIO pipe binds
+    // these widths; measured +3.7 % / +3.4 % (profiles/r02d_ab.md).  XGPR_B200_RBF_NARROW_E restores K = 32.
+    if (sizeof(T) == 4 && !GRAD && !getenv("XGPR_B200_RBF_NARROW_E")) {
         if (P == 512) return launch_core<T, 512, GRAD, false, 2>(x, n, d, out, grad, radem, R, chi, F, scale, sigma, st);
         if (P == 1024) return launch_core<T, 1024, GRAD, false, 2>(x, n, d, out, grad, radem, R, chi, F, scale, sigma, st);
     }

@@ -507,6 +507,7 @@ class ConjugateGrad:
         state[1:2].copy_(torch.linalg.norm(r).reshape(1))
         state[2:3].fill_(float(tol))
 
+        n_ar0, b_ar0 = self.comm.n_allreduce, self.comm.bytes_allreduce
         lag = max(1, int(self.poll_lag))
         flags = torch.zeros(lag + 2, dtype=torch.float64).pin_memory()
         events = [torch.cuda.Event() for _ in range(lag + 2)]
@@ -528,6 +529,9 @@ class ConjugateGrad:
             flags[slot:slot + 1].copy_(skip, non_blocking=True)
             events[slot].record()
             launched += 1
+        if self.comm.world > 1:               # graph replays issue the captured all-reduce without passing through comm
+            self.comm.n_allreduce = n_ar0 + launched
+            self.comm.bytes_allreduce = b_ar0 + launched * w.numel() * w.element_size()
         st = state.cpu()
         done = bool(st[5] != 0.0)
         niter = int(st[6]) if done else launched
