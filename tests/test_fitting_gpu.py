@@ -101,6 +101,27 @@ def test_device_cg_matches_host_loop(m):
     assert not conv and nit == 3 and len(losses) == 3 and np.isfinite(losses).all()
 
 
+def test_fit_cg_overlapped_build_matches_two_step_fit():
+    """fitting.fit_cg (the solve's resident features are built on a side stream under the preconditioner's serial
+    factorisation) against the two-step build_preconditioner + CG fit: same iteration count, same weights."""
+    from xgpr_b200 import fitting
+    from xgpr_b200.kernels import RBF
+    rng = np.random.default_rng(4)
+    x = rng.standard_normal((6000, 32)).astype(np.float32)
+    y = np.sin(x[:, :4].sum(1)) + 0.1 * rng.standard_normal(6000)
+    kern = RBF(x.shape, 4096, random_seed=123, device="cuda")
+    kern.set_hyperparams(np.log(np.asarray([0.5, 0.3])), logspace=True)
+    ds = fitting.build_shard_dataset(torch.from_numpy(x).cuda(), y, None, chunk_size=2048)
+    w1, n1, _, pre1 = fitting.fit_cg(kern, ds, 128, "srht", 1e-8, 300)
+    pre0 = fitting.RandNysPreconditioner(kern, ds, 128, False, 123, "srht")
+    w0, n0, _ = fitting.cg_fit_lib_internal(kern, ds, 1e-8, 300, pre0, False)
+    np.testing.assert_allclose(pre1.achieved_ratio, pre0.achieved_ratio, rtol=1e-9)
+    assert abs(n1 - n0) <= 1
+    assert float((w1 - w0).abs().max() / w0.abs().max()) < 1e-7
+    w2, n2, _, _ = fitting.fit_cg(kern, ds, 128, "srht_2", 1e-8, 300)
+    assert float((w2 - w0).abs().max() / w0.abs().max()) < 1e-6
+
+
 def test_fused_predict_matches_materialised():
     """predict() through the fused featurise-dot kernel (Z never written) against (Z * w).sum(1) on transform_x."""
     from xgpr_b200 import fitting

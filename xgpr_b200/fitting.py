@@ -321,6 +321,7 @@ class ConjugateGrad:
         self.use_graph = os.environ.get("XGPR_B200_CG_GRAPH", "1") != "0"
         self.poll_lag = 2
         self.last_fit_info = {}
+        self._prep_event = None
 
     def _staged_blocks(self, dataset, kernel, budget_bytes=8 << 30):
         """The sigma-scaled device copies of the shard's x blocks for the fused passes.  x * sigma does not change during
@@ -438,6 +439,26 @@ class ConjugateGrad:
         if keep is not None:
             self._resident = (key, keep)
 
+    def prepare_async(self, dataset, kernel):
+        """Start building the resident float32 encoding of the shard's features on a SIDE stream and return at once.
+        Meant to be called while the GPU is under-used -- `RandNysPreconditioner(..., overlap_hook=...)` calls it between
+        its accumulation pass and its serial factorisation (a few ms of small cuSOLVER kernels, replicated on every rank:
+        the Amdahl term of the sharded fit), so the solve that follows finds its features ready.  No-op when the solve
+        would not use the resident encoding.  `fit` waits for the side stream before its first matvec."""
+        if not (self.device_cg and self.ops is _cuda_ops and kernel.device == "cuda" and _fused_ok(kernel, self.ops)
+                and self.keep_resident and getattr(kernel, "resident_ok", lambda: False)()):
+            return
+        cur = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            c = self._resident_encoding(dataset, kernel)
+            done = torch.cuda.Event()
+            done.record(side)
+        if c is not None:
+            c.record_stream(cur)
+        self._prep_event = done
+
     # ---- one right-hand side, device-resident recurrences -----------------------------------------------------------
     def _device_cg_ok(self, kernel, resid, nmll_settings):
         return (self.device_cg and self.ops is _cuda_ops and not nmll_settings and resid.shape[2] == 1 and resid.is_cuda
@@ -455,6 +476,9 @@ class ConjugateGrad:
         every rank sees bit-identical all-reduced w, takes the same decision at the same iteration, and so issues the same
         number of collectives."""
         ops = self.ops
+        if self._prep_event is not None:       # prepare_async built the resident encoding on a side stream
+            torch.cuda.current_stream().wait_event(self._prep_event)
+            self._prep_event = None
         dev, m = resid.device, resid.shape[0]
         lam2 = float(kernel.get_lambda()) ** 2
         r = resid[:, 0, 0].clone().contiguous()
@@ -544,16 +568,31 @@ class ConjugateGrad:
 
     @staticmethod
     def _capture(iteration):
-        """One CG iteration as a CUDA graph (NCCL's all-reduce is capturable); None if capture is not possible."""
+        """One CG iteration as a CUDA graph (NCCL's all-reduce is capturable); None if capture is not possible.
+        Uses CUDAGraph.capture_begin / capture_end directly: the `torch.cuda.graph` context manager also runs
+        gc.collect(), a device-wide synchronize and empty_cache() -- milliseconds of serial host work (and a cold allocator
+        afterwards) that a 0.1 s sharded solve cannot afford."""
+        cur = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        graph = torch.cuda.CUDAGraph()
+        began = False
         try:
-            graph = torch.cuda.CUDAGraph()
-            side = torch.cuda.Stream()
-            side.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.graph(graph, stream=side, capture_error_mode="thread_local"):
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                graph.capture_begin(capture_error_mode="thread_local")
+                began = True
                 iteration()
-            torch.cuda.current_stream().wait_stream(side)
+                graph.capture_end()
+                began = False
+            cur.wait_stream(side)
             return graph
         except Exception as exc:             # keep the stream-ordered eager launches
+            if began:
+                try:
+                    with torch.cuda.stream(side):
+                        graph.capture_end()
+                except Exception:
+                    pass
             warnings.warn(f"CUDA-graph capture of the CG iteration failed ({exc}); launching eagerly.")
             return None
 
@@ -633,6 +672,19 @@ def cg_fit_lib_internal(kernel, dataset, cg_tol=1e-4, max_iter=500, precondition
     return weights, n_iter, losses
 
 
+def fit_cg(kernel, dataset, max_rank=512, method="srht", cg_tol=1e-6, max_iter=500, random_state=123, verbose=False,
+           comm=None, ops=_cuda_ops):
+    """`build_preconditioner` + `fit(mode="cg", preconditioner=...)` of the reference model class
+    (model_baseclass.py:225-260, xgp_regression.py:381-470) as one call: the preconditioner build's serial factorisation
+    overlaps with the construction of the solve's resident features.  Returns (weights, n_iter, losses, preconditioner)."""
+    comm = comm or RowShardComm()
+    op = ConjugateGrad(comm, ops)
+    pre = RandNysPreconditioner(kernel, dataset, max_rank, verbose, random_state, method, comm, ops,
+                                overlap_hook=lambda: op.prepare_async(dataset, kernel))
+    weights, n_iter, losses = cg_fit_lib_internal(kernel, dataset, cg_tol, max_iter, pre, verbose, comm, ops, op)
+    return weights, n_iter, losses, pre
+
+
 # ----------------------------------------------------------------------------------------- randomised Nystrom
 def _single_pass_srht_zty(dataset, kernel, compressor, acc_results, z_trans_y, ops):
     """rand_nys_constructors.py:96-123: acc (rank, M) += SRHT(Z)[:, perm[:rank]]^T Z ; z^T y ; y^T y.
@@ -689,8 +741,9 @@ def _tall_svd(mat):
     return u, s
 
 
-def initialize_srht(dataset, rank, kernel, random_state, comm, ops, compressor_cls):
-    """rand_nys_constructors.py:221-296 (single pass)."""
+def initialize_srht(dataset, rank, kernel, random_state, comm, ops, compressor_cls, overlap_hook=None):
+    """rand_nys_constructors.py:221-296 (single pass).  `overlap_hook` is called once, after the accumulation pass and its
+    all-reduces have been issued and before the serial factorisation (see ConjugateGrad.prepare_async)."""
     dev = _device_of(kernel)
     m = kernel.get_num_rffs()
     acc_results, z_trans_y = _new((rank, m), dev), _new((m,), dev)
@@ -698,6 +751,8 @@ def initialize_srht(dataset, rank, kernel, random_state, comm, ops, compressor_c
     y_trans_y = _single_pass_srht_zty(dataset, kernel, compressor, acc_results, z_trans_y, ops)
     comm.all_reduce_(acc_results)
     comm.all_reduce_(z_trans_y, y_trans_y)
+    if overlap_hook is not None:
+        overlap_hook()
 
     c_mat = compressor.transform_x(acc_results)
     # c_mat = Omega^T Z^T Z Omega is symmetric PSD and the reference forms Y c_mat^(-1/2) from its SVD
@@ -720,7 +775,8 @@ def initialize_srht(dataset, rank, kernel, random_state, comm, ops, compressor_c
     return u_mat, s_mat ** 2, z_trans_y, float(y_trans_y[0])
 
 
-def initialize_srht_multipass(dataset, rank, kernel, random_state, comm, ops, compressor_cls, n_passes=2):
+def initialize_srht_multipass(dataset, rank, kernel, random_state, comm, ops, compressor_cls, n_passes=2,
+                              overlap_hook=None):
     """rand_nys_constructors.py:128-218 (SRHT pass, then QR + Z^T (Z Q) passes, shifted Cholesky, SVD)."""
     dev = _device_of(kernel)
     m = kernel.get_num_rffs()
@@ -736,6 +792,8 @@ def initialize_srht_multipass(dataset, rank, kernel, random_state, comm, ops, co
         acc_results.zero_()
         _single_pass_gauss(dataset, kernel, q_mat, acc_results, ops, holder)
         comm.all_reduce_(acc_results)
+    if overlap_hook is not None:
+        overlap_hook()
     norm = float(torch.sqrt((acc_results ** 2).sum()))
     shift = float(np.spacing(norm))
     acc_results += shift * q_mat
@@ -750,7 +808,7 @@ class RandNysPreconditioner:
     """rand_nys_preconditioners.py:14-72."""
 
     def __init__(self, kernel, dataset, max_rank, verbose=False, random_state=123, method="srht", comm=None,
-                 ops=_cuda_ops, compressor_cls=None):
+                 ops=_cuda_ops, compressor_cls=None, overlap_hook=None):
         if method not in ["srht_2", "srht_3", "srht"]:
             raise RuntimeError("Unknown method supplied for tuning preconditioner construction.")
         comm = comm or RowShardComm()
@@ -758,10 +816,11 @@ class RandNysPreconditioner:
             from .kernels import SRHTCompressor as compressor_cls
         if method.startswith("srht_"):
             self.u_mat, self.eig, self.z_trans_y, self.y_trans_y = initialize_srht_multipass(
-                dataset, max_rank, kernel, random_state, comm, ops, compressor_cls, int(method.split("_")[1]))
+                dataset, max_rank, kernel, random_state, comm, ops, compressor_cls, int(method.split("_")[1]),
+                overlap_hook)
         else:
             self.u_mat, self.eig, self.z_trans_y, self.y_trans_y = initialize_srht(
-                dataset, max_rank, kernel, random_state, comm, ops, compressor_cls)
+                dataset, max_rank, kernel, random_state, comm, ops, compressor_cls, overlap_hook)
         lambda_ = kernel.get_lambda()
         min_eig = float(self.eig.min())
         self.eig = self.eig + lambda_ ** 2
