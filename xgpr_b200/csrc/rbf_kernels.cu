@@ -251,12 +251,10 @@ rbf_cta2_kernel(const T* __restrict__ x, double* __restrict__ out, double* __res
     constexpr int E = 32, K = 32, SEG = 1024, P = NS * SEG, THREADS = 32 * NS, GROUPS = SEG / THREADS;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* buf = reinterpret_cast<T*>(smem_raw);
-    T* chis = buf + P;                                  // this repeat's chi (0 past num_freqs), read once per CTA
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int off = warp * SEG;
     const int rep = blockIdx.x;
     const int64_t base = (int64_t)rep * P;
-    for (int j = threadIdx.x; j < P; j += THREADS) chis[j] = (base + j < F) ? chi[base + j] : T(0);
     uint32_t sbits[3];
 #pragma unroll
     for (int s = 0; s < 3; ++s) {
@@ -337,7 +335,7 @@ static int launch_cta2(const T* x, int64_t n, int64_t d, double* out, double* gr
                        const T* chi, int64_t F, double scale, double sigma, cudaStream_t st) {
     constexpr int64_t P = (int64_t)NS * 1024;
     const int reps = (int)((F + P - 1) / P);
-    const size_t smem = 2 * (size_t)P * sizeof(T);
+    const size_t smem = (size_t)P * sizeof(T);
     auto kern = rbf_cta2_kernel<T, NS, GRAD>;
     ensure_dyn_smem(kern, smem);
     int per_sm = (int)((220 * 1024) / smem);
@@ -455,7 +453,7 @@ int rbf_dispatch(const T* x, int64_t n, int64_t d, double* out, double* grad, in
     }
 #undef XB_CASE
     static const bool cta_v1 = getenv("XGPR_B200_RBF_CTA_V1") != nullptr;
-    if (!cta_v1 && 2 * (size_t)P * sizeof(T) <= 200 * 1024 && (F + P - 1) / P <= 65535) {
+    if (!cta_v1 && (size_t)P * sizeof(T) <= 200 * 1024 && (F + P - 1) / P <= 65535) {
         switch (P) {
             case 2048:  return launch_cta2<T, 2, GRAD>(x, n, d, out, grad, radem, R, chi, F, scale, sigma, st);
             case 4096:  return launch_cta2<T, 4, GRAD>(x, n, d, out, grad, radem, R, chi, F, scale, sigma, st);
