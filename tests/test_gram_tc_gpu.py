@@ -218,3 +218,28 @@ def test_ztzq_argument_errors():
     with pytest.raises(RuntimeError):
         ext.ztzq_accum_tc(z, torch.zeros((128, 8), dtype=torch.float64, device=DEV),
                           torch.zeros((128, 9), dtype=torch.float64, device=DEV))
+
+
+@pytest.mark.parametrize("bad", [float("nan"), float("inf")])
+def test_tc_gram_propagates_non_finite_input(bad):
+    """A NaN / Inf in Z must poison the Gram (as the reference's fp64 `@` does, so that the Cholesky behind exact_nmll fails
+    and the caller gets DEFAULT_SCORE_IF_PROBLEM) instead of being clamped into a plausible-looking finite matrix."""
+    import torch
+    from xgpr_b200 import ext
+    g = torch.Generator(device="cuda")
+    g.manual_seed(3)
+    z = torch.randn((1000, 512), dtype=torch.float64, device="cuda", generator=g)
+    z[123, 45] = bad
+    out = torch.zeros((512, 512), dtype=torch.float64, device="cuda")
+    ext.ztz_accum_tc(z, out)
+    assert not bool(torch.isfinite(out[45, :]).any()) and not bool(torch.isfinite(out[:, 45]).any())
+    keep = torch.ones(512, dtype=torch.bool, device="cuda")
+    keep[45] = False
+    clean = out[keep][:, keep]
+    ref = z[:, keep].T @ z[:, keep]
+    assert bool(torch.isfinite(clean).all())
+    assert float((clean - ref).abs().max()) < 1e-9 * float(ref.abs().max())
+    a = torch.randn((1000, 64), dtype=torch.float64, device="cuda", generator=g)
+    acc = torch.zeros((64, 512), dtype=torch.float64, device="cuda")
+    ext.atb_accum_tc(a, z, acc)
+    assert not bool(torch.isfinite(acc[:, 45]).any()) and bool(torch.isfinite(acc[:, keep]).all())

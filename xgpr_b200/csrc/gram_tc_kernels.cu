@@ -49,11 +49,16 @@ tc_colmax_kernel(const double* __restrict__ z, int64_t n, int64_t m, unsigned lo
     if (col >= m) return;
     const int64_t n0 = (int64_t)blockIdx.y * rows_per_block;
     const int64_t n1 = (n0 + rows_per_block < n) ? n0 + rows_per_block : n;
-    double mx = 0.0;
+    // the maximum is taken on the BIT PATTERNS of |z| (they order like the values for non-negative doubles, with
+    // Inf and NaN above every finite number): fmax would drop a NaN and the Gram of corrupt input would come out finite
+    unsigned long long mx = 0ull;
     const double* p = z + n0 * m + col;
 #pragma unroll 8
-    for (int64_t r = n0; r < n1; ++r, p += m) mx = fmax(mx, fabs(*p));
-    atomicMax(cmax + col, (unsigned long long)__double_as_longlong(mx));
+    for (int64_t r = n0; r < n1; ++r, p += m) {
+        const unsigned long long b = (unsigned long long)__double_as_longlong(fabs(*p));
+        mx = b > mx ? b : mx;
+    }
+    atomicMax(cmax + col, mx);
 }
 
 // exponent e with mx <= 2^(e-1); colscale = 2^e.  With 8-bit digits the leading digit rint(x * 256) must stay <= 127, so a
@@ -63,9 +68,13 @@ __global__ void tc_exponent_kernel(const unsigned long long* __restrict__ cmax, 
     const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (col >= m) return;
     const double mx = __longlong_as_double((long long)cmax[col]);
+    if (!(mx < 1e300)) {                              // Inf, NaN or absurdly large input: poison the column / row, as
+        colscale[col] = __longlong_as_double(0x7ff8000000000000ll);   // the reference's fp64 `@` would (the epilogue
+        return;                                       // multiplies by colscale_i * colscale_j, so G gets NaN and the
+    }                                                 // Cholesky that follows fails loudly instead of on garbage)
     int q = 0;
     double f = 0.0;
-    if (mx > 0.0 && mx < 1e300) f = frexp(mx, &q);    // mx = f * 2^q, f in [0.5, 1)  =>  mx <= 2^q
+    if (mx > 0.0) f = frexp(mx, &q);                  // mx = f * 2^q, f in [0.5, 1)  =>  mx <= 2^q
     if (digit_bits == 8 && f >= 0.9921875) ++q;
     colscale[col] = ldexp(1.0, q + 1);
 }
@@ -125,11 +134,17 @@ tc_rowmax_kernel(const double* __restrict__ z, int64_t n, int64_t m, unsigned lo
     const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (row >= n) return;
     const double* p = z + row * m;
-    double mx = 0.0;
-    for (int64_t k = lane; k < m; k += 32) mx = fmax(mx, fabs(p[k]));
+    unsigned long long mx = 0ull;                     // bit patterns: NaN / Inf propagate (see tc_colmax_kernel)
+    for (int64_t k = lane; k < m; k += 32) {
+        const unsigned long long b = (unsigned long long)__double_as_longlong(fabs(p[k]));
+        mx = b > mx ? b : mx;
+    }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if (lane == 0) rmax[row] = (unsigned long long)__double_as_longlong(mx);
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long b = __shfl_xor_sync(0xffffffffu, mx, o);
+        mx = b > mx ? b : mx;
+    }
+    if (lane == 0) rmax[row] = mx;
 }
 
 // planes[k][row][col], col contiguous with stride m_pad (zero beyond m); each thread slices 4 consecutive columns

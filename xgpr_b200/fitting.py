@@ -122,6 +122,22 @@ class ShardDataset:
             sl = None if self._sequence_lengths is None else self._sequence_lengths[lo:hi]
             yield self._xdata[lo:hi, ...], sl
 
+    def get_coalesced_data(self, min_rows, with_y=True):
+        """The same rows in the same order as get_chunked_data / get_chunked_x_data, in work chunks of a whole number of
+        dataset chunks totalling >= min_rows rows.  The reference's default chunk_size is 2,000 rows
+        (online_data_handling.py:26) -- 43 us of GPU work at 46 M rows/s, behind three launches and the Python of a chunk
+        iteration -- so the passes whose result is a sum over rows (Z^T y, Z^T Z, the CG matvec, the Nystrom sketch) walk
+        the in-memory shard in larger slices; only fp64 summation order changes.  Passes that draw per-chunk random
+        subsamples (the NMLL gradient, the rank-ratio probe) keep the dataset's own chunking."""
+        step = self._chunk_size * max(1, int(min_rows) // self._chunk_size)
+        for lo in range(0, self._n_local, step):
+            hi = min(lo + step, self._n_local)
+            sl = None if self._sequence_lengths is None else self._sequence_lengths[lo:hi]
+            if with_y:
+                yield self._xdata[lo:hi, ...], self._ychunk(lo, hi), sl
+            else:
+                yield self._xdata[lo:hi, ...], sl
+
 
 def build_shard_dataset(xdata, ydata, sequence_lengths=None, chunk_size=2000, comm=None):
     """y is standardised with the GLOBAL mean / std (dataset_builder.py:14-70 computes them over the whole
@@ -140,14 +156,29 @@ def _new(shape, like_device):
     return torch.zeros(shape, dtype=torch.float64, device=like_device)
 
 
+def _work_rows(kernel, budget_bytes=4 << 30, cap=65536):
+    """Rows per work chunk: about `budget_bytes` of fp64 features (8 M bytes per row), at most `cap`."""
+    return int(max(1, min(cap, budget_bytes // (8 * max(1, kernel.get_num_rffs())))))
+
+
+def _xy_chunks(dataset, kernel):
+    fn = getattr(dataset, "get_coalesced_data", None)
+    return fn(_work_rows(kernel), True) if fn is not None else dataset.get_chunked_data()
+
+
+def _x_chunks(dataset, kernel):
+    fn = getattr(dataset, "get_coalesced_data", None)
+    return fn(_work_rows(kernel), False) if fn is not None else dataset.get_chunked_x_data()
+
+
 def _transformed_chunks(dataset, kernel):
     """kernel.transform_x over the shard's chunks; on the GPU through the kernel's double-buffered transform_stream, so
     a host-resident chunk's copy runs under the previous chunk's feature generation."""
     stream = getattr(kernel, "transform_stream", None)
     if stream is not None and kernel.device == "cuda":
-        yield from stream(dataset.get_chunked_x_data())
+        yield from stream(_x_chunks(dataset, kernel))
         return
-    for xdata, ldata in dataset.get_chunked_x_data():
+    for xdata, ldata in _x_chunks(dataset, kernel):
         yield kernel.transform_x(xdata, ldata)
 
 
@@ -155,14 +186,14 @@ def _transformed_xy_chunks(dataset, kernel):
     """(Z, y) per chunk, as kernel.transform_x_y over dataset.get_chunked_data(), through the double-buffered stream."""
     stream = getattr(kernel, "transform_stream", None)
     if stream is None or kernel.device != "cuda":
-        for xin, yin, ldata in dataset.get_chunked_data():
+        for xin, yin, ldata in _xy_chunks(dataset, kernel):
             yield kernel.transform_x_y(xin, yin, ldata)
         return
     from .kernels.base import to_device
     ys = []
 
     def x_chunks():
-        for xin, yin, ldata in dataset.get_chunked_data():
+        for xin, yin, ldata in _xy_chunks(dataset, kernel):
             ys.append(yin)
             yield xin, ldata
 
@@ -201,7 +232,7 @@ def calc_zty(dataset, kernel, comm=None, ops=_cuda_ops):
         # fused featurise -> Z^T y: the features are regenerated in registers and never written (rbf_ztv); the next
         # chunk's x and y are copied under this chunk's kernel (stage_stream)
         def chunks():
-            for xin, yin, ldata in dataset.get_chunked_data():
+            for xin, yin, ldata in _xy_chunks(dataset, kernel):
                 yield xin, ldata, yin
 
         for xin, _, (y,) in kernel.stage_stream(chunks(), extra=lambda item: (_as_f64(item[2]),)):
@@ -335,11 +366,11 @@ class ConjugateGrad:
         nbytes = int(np.prod(xdata.shape)) * (8 if kernel.double_precision else 4)
         if nbytes > budget_bytes:
             return ((kernel.stage_scaled(x), torch.empty(x.shape[0], dtype=torch.float64, device=_device_of(kernel)))
-                    for x, _ in dataset.get_chunked_x_data())
+                    for x, _ in _x_chunks(dataset, kernel))
         if isinstance(xdata, torch.Tensor) and xdata.is_cuda:
             pieces = [xdata]
         else:
-            pieces = [x for x, _ in dataset.get_chunked_x_data()]
+            pieces = [x for x, _ in _x_chunks(dataset, kernel)]
         blocks = []
         for x in pieces:
             xs = kernel.stage_scaled(x)
@@ -403,7 +434,7 @@ class ConjugateGrad:
             return None
         lo = 0
         direct = getattr(kernel, "resident_generate", None) if kernel.get_xdim()[-1] <= 1024 else None
-        for xdata, ldata in dataset.get_chunked_x_data():
+        for xdata, ldata in _x_chunks(dataset, kernel):
             if direct is not None:               # the feature kernel writes the float32 values itself
                 direct(xdata, c[lo:lo + xdata.shape[0]])
                 lo += xdata.shape[0]
@@ -707,7 +738,7 @@ def _single_pass_gauss(dataset, kernel, q_mat, acc_results, ops, scratch_holder)
         for z in _transformed_chunks(dataset, kernel):
             tc(z, q_mat, acc_results)
         return
-    for xdata, ldata in dataset.get_chunked_x_data():
+    for xdata, ldata in _x_chunks(dataset, kernel):
         z = kernel.transform_x(xdata, ldata)
         s = scratch_holder.get("s")
         if s is None or s.shape[0] < z.shape[0] or s.shape[1] != q_mat.shape[1]:
@@ -727,12 +758,14 @@ def _psd_eig(c_mat):
 def _tall_svd(mat):
     """(U, s) of a tall (M, rank) matrix B -- the replicated, serial step of the Nystrom build.
     On the GPU: eigh of the small Gram B^T B (s^2 and V; 6 ms at 16384 x 512 against 22 ms for cuSOLVER's Jacobi SVD and
-    43-60 ms for gesvd), U = B V / s.  eigh resolves s^2 to eps * s_max^2 absolutely, so when the spectrum spans more than
-    1e10 (the small singular values would lose more than ~6 digits) the Jacobi SVD is used instead."""
+    43-60 ms for gesvd), U = B V / s.  eigh resolves s^2 to eps * s_max^2 absolutely, so the smallest eigenvalue (which
+    feeds achieved_ratio, the prefactor and the log-determinant) and the orthogonality of U carry a relative error of
+    eps * s_max^2 / s_min^2: when the spectrum of s^2 spans more than 1e8 (more than ~2e-8 relative) the Jacobi SVD is
+    used instead."""
     if mat.is_cuda:
         evals, evecs = torch.linalg.eigh(mat.T @ mat)
         evals, evecs = evals.flip(0), evecs.flip(1)
-        if float(evals[-1]) > 1e-10 * float(evals[0]):
+        if float(evals[-1]) > 1e-8 * float(evals[0]):
             s = torch.sqrt(evals)
             return (mat @ evecs) / s[None, :], s
         u, s, _ = torch.linalg.svd(mat, full_matrices=False, driver="gesvdj")
