@@ -610,8 +610,16 @@ def gram_headline(dev, rank, n=32768, m=8192, slices=5, bits=8, steps=3):
             "slices": slices, "bits": bits, "launches": launches, "int8_ops": int8_ops}
 
 
+def tensor_peak_sustained():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p)).get("bf16_tflops_sustained", 0.0)) or None
+    return 1400.0
+
+
 def gram_record(gram, gram_ms, gram_gemm_ms, gram_dfma_ms):
     bf16_peak = tensor_peak()
+    bf16_sus = tensor_peak_sustained()
     tops = gram["int8_ops"] / (gram_gemm_ms * 1e-3) / 1e12
     return {
         "metric": "Z^T Z accumulation (exact-fit Gram), fp64-equivalent TFLOP/s per GPU",
@@ -624,6 +632,10 @@ def gram_record(gram, gram_ms, gram_gemm_ms, gram_dfma_ms):
                      "achieved": tops, "peak": None if bf16_peak is None else 2.0 * bf16_peak, "unit": "TOP/s (int8)",
                      "frac": None if bf16_peak is None else tops / (2.0 * bf16_peak),
                      "peak_source": "2 x measured bf16 burst TFLOP/s (MEASURED_PEAKS.json); int8 issues at twice the bf16 rate",
+                     # the GEMM is timed inside a ~60 ms loop of 13 ms launches, i.e. under the power cap: the sustained
+                     # figure is the denominator the profiling guide names for that case; both are reported
+                     "peak_sustained": None if bf16_sus is None else 2.0 * bf16_sus,
+                     "frac_sustained": None if bf16_sus is None else tops / (2.0 * bf16_sus),
                      "kernel_ms": gram_gemm_ms, "algorithmic_ops_per_launch": gram["int8_ops"]}}
 
 

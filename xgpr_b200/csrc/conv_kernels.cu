@@ -58,7 +58,7 @@ __device__ __forceinline__ void cv_mbar_wait(unsigned bar, unsigned parity) {
 // 1-D bulk copy (TMA, cp.async.bulk + mbarrier) per sequence -- a sequence's seqlen * C leading elements are contiguous --
 // issued by one thread, whenever the rows are 16-byte aligned (`bulk`); otherwise element-wise cp.async.
 template <typename T, int P, int E, int MODE, int WARPS, bool SMEMX, int CHSEL = 8>
-__global__ void __launch_bounds__(WARPS * 32, (E <= 16 && sizeof(T) == 4 && MODE != CONV_GRAD) ? 2 : 1)
+__global__ void __launch_bounds__(WARPS * 32, (E <= 16 && sizeof(T) == 4) ? 2 : 1)   // float: 2 CTAs / SM, all modes
 conv_core_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __restrict__ grad,
                  const int8_t* __restrict__ radem, const T* __restrict__ chi,
                  const int32_t* __restrict__ seqlen, int N, int M, int C, int F, int64_t R,
