@@ -130,3 +130,29 @@ def test_transform_accepts_resident_and_pinned_inputs():
     z2 = k.transform_x(xd)
     assert torch.equal(z0, z1) and torch.equal(z0, z2)
     assert torch.equal(xd.cpu(), torch.from_numpy(x.astype(np.float32)))   # caller's tensor untouched
+
+
+def test_maxpool_feature_extractor_draws_bit_identical():
+    """FHTMaxpoolConv1dFeatureExtractor (conv_feature_extractor.py:19-118): same host draws as the reference class."""
+    from xgpr_b200.kernels import FHTMaxpoolConv1dFeatureExtractor
+    g = load_golden(os.path.join(GOLDEN, "l2_maxpool_extractor.npz"))
+    fe = FHTMaxpoolConv1dFeatureExtractor(21, 768, random_seed=123, device="cpu", conv_width=9)
+    assert np.array_equal(fe.radem_diag, g["radem"]) and np.array_equal(fe.chi_arr, g["chi"])
+    assert fe.chi_arr.dtype == np.float32 and fe.radem_diag.dtype == np.int8
+    with pytest.raises(ValueError):
+        fe.transform_x(g["x"], None)
+    with pytest.raises(RuntimeError):
+        fe.transform_x(g["x"], g["seqlen"])              # device="cpu": no CPU fallback here
+
+
+@pytest.mark.gpu
+def test_maxpool_feature_extractor_matches_reference():
+    """... and the same features, bit for bit (float32 max-pool of bit-identical pre-activations)."""
+    from xgpr_b200.kernels import FHTMaxpoolConv1dFeatureExtractor
+    g = load_golden(os.path.join(GOLDEN, "l2_maxpool_extractor.npz"))
+    fe = FHTMaxpoolConv1dFeatureExtractor(21, 768, random_seed=123, device="cuda", conv_width=9)
+    out = fe.transform_x(g["x"], g["seqlen"])
+    assert out.dtype.is_floating_point and tuple(out.shape) == (7, 768)
+    assert np.array_equal(out.cpu().numpy(), g["out"])
+    with pytest.raises(ValueError):
+        fe.transform_x(g["x"][:, :, :5], g["seqlen"])

@@ -3,6 +3,7 @@ from .ard import MiniARD
 from .base import KernelBaseclass
 from .conv import (Conv1dCauchy, Conv1dMatern, Conv1dRBF, ConvKernelBaseclass, GraphCauchy, GraphMatern,
                    GraphRBF)
+from .feature_extractor import FHTMaxpoolConv1dFeatureExtractor
 from .linear import Linear
 from .sorf import RBF, Cauchy, Matern, SORFKernelBaseclass
 from .srht import SRHTCompressor
