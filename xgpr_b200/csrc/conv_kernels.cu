@@ -71,7 +71,7 @@ conv_core_kernel(const T* __restrict__ x, void* __restrict__ out_v, double* __re
     // cos / sin group size CHSEL: 8, or 4 for the float sum-pool instance at E = 16 when XGPR_B200_CONV_CH4 is set (its 32
     // fp64 accumulators + 16 chi values spill 44-52 bytes with groups of 8 under the 128-register cap of 2 CTAs / SM;
     // groups of 4 spill 4-16 bytes but pay twice the range checks -- measured a wash, profiles/r02d)
-    constexpr int CH = cmin(CHSEL, E);
+    constexpr int CH = (MODE == CONV_GRAD && sizeof(T) == 4) ? cmin(4, E) : cmin(CHSEL, E);   // gradient: 4 (registers)
     constexpr int CPITCH = ChiTile<T, E>::PITCH;
     constexpr int NACC = (MODE == CONV_GRAD) ? 4 : ((MODE == CONV_FGEN) ? 2 : 0);
 
