@@ -92,7 +92,8 @@ def test_device_cg_matches_host_loop(m):
     assert abs(n1 - n0) <= 2 and len(l1) == n1 and len(l0) == n0
     np.testing.assert_allclose(l1[:8], l0[:8], rtol=1e-6)
     assert l1[-1] < 1e-8 and l0[-1] < 1e-8
-    assert float((w1 - w0).abs().max() / w0.abs().max()) < 1e-7
+    # both solves stop at a 1e-8 relative residual, possibly one iteration apart: the solutions agree to that level
+    assert float((w1 - w0).abs().max() / w0.abs().max()) < 1e-6
     # without a preconditioner, and a tolerance it cannot reach in 3 iterations: stops at maxiter, not converged
     op = fitting.ConjugateGrad()
     resid = torch.zeros((m, 2, 1), dtype=torch.float64, device="cuda")
@@ -117,7 +118,7 @@ def test_fit_cg_overlapped_build_matches_two_step_fit():
     w0, n0, _ = fitting.cg_fit_lib_internal(kern, ds, 1e-8, 300, pre0, False)
     np.testing.assert_allclose(pre1.achieved_ratio, pre0.achieved_ratio, rtol=1e-9)
     assert abs(n1 - n0) <= 1
-    assert float((w1 - w0).abs().max() / w0.abs().max()) < 1e-7
+    assert float((w1 - w0).abs().max() / w0.abs().max()) < 1e-6
     w2, n2, _, _ = fitting.fit_cg(kern, ds, 128, "srht_2", 1e-8, 300)
     assert float((w2 - w0).abs().max() / w0.abs().max()) < 1e-6
 
