@@ -273,10 +273,16 @@ ard_mma_kernel(const T* __restrict__ x, double* __restrict__ out, const T* __res
                 // grad += on a caller-zeroed array, then rescaled (ard_ops.cpp:100,117-121): the old values are
                 // requested first so that their latency hides behind the two double-precision sincos
                 double old[2][NG];
+                if (NG == 2 && two) {                            // 16-byte loads: gp is 32-byte aligned (f is even)
+                    const double2 o0 = __ldcs(reinterpret_cast<const double2*>(gp));
+                    const double2 o1 = __ldcs(reinterpret_cast<const double2*>(gp + 4));
+                    old[0][0] = o0.x; old[0][NG - 1] = o0.y; old[1][0] = o1.x; old[1][NG - 1] = o1.y;
+                } else {
 #pragma unroll
-                for (int e = 0; e < 2; ++e)
+                    for (int e = 0; e < 2; ++e)
 #pragma unroll
-                    for (int g = 0; g < NG; ++g) old[e][g] = (e == 0 || two) ? __ldcs(gp + e * 2 * NG + g) : 0.0;
+                        for (int g = 0; g < NG; ++g) old[e][g] = (e == 0 || two) ? __ldcs(gp + e * 2 * NG + g) : 0.0;
+                }
                 double cv[2], sv[2];
 #pragma unroll
                 for (int e = 0; e < 2; ++e) {
@@ -301,15 +307,24 @@ ard_mma_kernel(const T* __restrict__ x, double* __restrict__ out, const T* __res
                     o[0] = cv[0];
                     o[1] = sv[0];
                 }
+                // the 2 NG values of one frequency are contiguous, and so are the two frequencies: 4 NG doubles per thread,
+                // written as 16-byte pieces
+                double vals[4 * NG];
 #pragma unroll
-                for (int e = 0; e < 2; ++e) {
-                    if (e == 1 && !two) break;
+                for (int e = 0; e < 2; ++e)
 #pragma unroll
                     for (int g = 0; g < NG; ++g) {
                         const double gv = __dadd_rn(old[e][g], acc[g][i][j][e]);
-                        __stcs(gp + e * 2 * NG + g, -gv * sv[e]);
-                        __stcs(gp + e * 2 * NG + NG + g, gv * cv[e]);
+                        vals[e * 2 * NG + g] = -gv * sv[e];
+                        vals[e * 2 * NG + NG + g] = gv * cv[e];
                     }
+                if (two) {
+#pragma unroll
+                    for (int q = 0; q < 2 * NG; ++q)
+                        __stcs(reinterpret_cast<double2*>(gp) + q, make_double2(vals[2 * q], vals[2 * q + 1]));
+                } else {
+#pragma unroll
+                    for (int q = 0; q < 2 * NG; ++q) __stcs(gp + q, vals[q]);
                 }
             }
         }
@@ -403,7 +418,8 @@ int ard_dispatch(const T* x, int64_t n, int64_t d, double* out, const T* w, int6
     const double ff0 = (double)F;
     const double scale0 = (double)(T)(fit_intercept ? sqrt(1.0 / (ff0 - 0.5)) : sqrt(1.0 / ff0));
     const bool simt_only = getenv("XGPR_B200_ARD_SIMT") != nullptr;   // the SIMT kernel reproduces the float product rounding
-    if (L <= 3 && d <= 1024 && F < (1ll << 26) && !simt_only) {      // fp64 tensor-core path
+    const bool aligned16 = ((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(grad)) & 15) == 0;
+    if (L <= 3 && d <= 1024 && F < (1ll << 26) && !simt_only && aligned16) {      // fp64 tensor-core path
         if (L == 1) return launch_ard_mma<T, 1>(x, n, d, out, w, F, sigma_map, sigma_vals, grad, scale0, st);
         if (L == 2) return launch_ard_mma<T, 2>(x, n, d, out, w, F, sigma_map, sigma_vals, grad, scale0, st);
         return launch_ard_mma<T, 3>(x, n, d, out, w, F, sigma_map, sigma_vals, grad, scale0, st);
