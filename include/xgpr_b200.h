@@ -120,6 +120,16 @@ int xgpr_b200_ard_grad_f32(const float*  x, int64_t n, int64_t d, double* out, c
 int xgpr_b200_ard_grad_f64(const double* x, int64_t n, int64_t d, double* out, const double* w,
                            int64_t num_freqs, const int32_t* sigma_map, const double* sigma_vals,
                            double* grad, int64_t num_lengthscales, int fit_intercept, void* stream);
+/* Same values WITHOUT reading `grad`: the reference accumulates `gradArr[...] += ...` onto the caller's zero-filled array
+ * before rescaling it (cpu_rf_gen/rbf_ops/ard_ops.cpp:100, :117-121), so xgpr_b200_ard_grad_* must read the whole gradient
+ * array it then overwrites.  The overwrite form writes what a zero-filled array would receive; out and grad may be
+ * uninitialised storage (no memset, no read: 8 M L bytes per row less HBM traffic each). */
+int xgpr_b200_ard_grad_overwrite_f32(const float*  x, int64_t n, int64_t d, double* out, const float*  w,
+                                     int64_t num_freqs, const int32_t* sigma_map, const double* sigma_vals,
+                                     double* grad, int64_t num_lengthscales, int fit_intercept, void* stream);
+int xgpr_b200_ard_grad_overwrite_f64(const double* x, int64_t n, int64_t d, double* out, const double* w,
+                                     int64_t num_freqs, const int32_t* sigma_map, const double* sigma_vals,
+                                     double* grad, int64_t num_lengthscales, int fit_intercept, void* stream);
 
 /* ---- cudaConv1dMaxpool  (xgpr_cuda_rfgen_cpp_ext.cpp:61-68; gpu_rf_gen/convolution_ops/convolution.cu:140-241)
  * x (n, m, c); out (n, num_freqs) f32, out = max(out, .) (caller zero-fills => ReLU);

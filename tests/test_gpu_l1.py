@@ -270,6 +270,21 @@ def test_ard_config_shapes(case, dt):
     ext.cudaMiniARDGrad(T(x), out, T(w), T(smap), T(svals), grad, True)
     np.testing.assert_allclose(out.cpu().numpy(), ref_out, **_ard_tol(dt, ref_out))
     np.testing.assert_allclose(grad.cpu().numpy(), ref_grad, **_ard_tol(dt, ref_grad))
+    # overwrite form: the same bits into storage full of garbage
+    out2 = torch.full((n, 2 * f), float("nan"), dtype=torch.float64, device=DEV)
+    grad2 = torch.full((n, 2 * f, len(groups)), float("nan"), dtype=torch.float64, device=DEV)
+    ext.cudaMiniARDGrad(T(x), out2, T(w), T(smap), T(svals), grad2, True, overwrite=True)
+    assert torch.equal(out2, out) and torch.equal(grad2, grad)
+    # and the reference contract: a non-zero gradArr is accumulated onto before the rescale (ard_ops.cpp:100,117-121)
+    g0 = torch.full_like(grad, 0.25)
+    out3 = torch.zeros_like(out)
+    ext.cudaMiniARDGrad(T(x), out3, T(w), T(smap), T(svals), g0, True)
+    L = len(groups)
+    pairs = out3.view(n, f, 2)
+    expect = grad.view(n, f, 2, L).clone()
+    expect[:, :, 0, :] += -0.25 * pairs[:, :, 1:2]
+    expect[:, :, 1, :] += 0.25 * pairs[:, :, 0:1]
+    np.testing.assert_allclose(g0.view(n, f, 2, L).cpu().numpy(), expect.cpu().numpy(), rtol=1e-9, atol=1e-12)
 
 
 def test_error_behaviour():

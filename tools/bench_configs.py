@@ -98,6 +98,10 @@ def ard_case(n=65536, d=128, m=8192):
     ms = timeit(lambda: ext.cudaMiniARDGrad(x, out, k.precomputed_weights, k.ard_position_key, k.full_ard_weights,
                                             grad, True), reps=3, warm=1)
     report(name, n, ms, d * 4 + m * 8 * 3, flops=2.0 * n * d * (m // 2))
+    ms = timeit(lambda: ext.cudaMiniARDGrad(x, out, k.precomputed_weights, k.ard_position_key, k.full_ard_weights,
+                                            grad, True, overwrite=True), reps=3, warm=1)
+    report(name.replace("(kernel only)", "(overwrite form, kernel only)"), n, ms, d * 4 + m * 8 * 3,
+           flops=2.0 * n * d * (m // 2))
 
 
 def main():

@@ -29,6 +29,7 @@ SIGNATURES = {
     "xgpr_b200_rbf_zzv": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _int, _ptr, _ptr, _ptr],
     "xgpr_b200_rbf_grad": [_ptr, _i64, _i64, _ptr, _ptr, _i64, _ptr, _i64, _ptr, _i64, _dbl, _int, _ptr],
     "xgpr_b200_ard_grad": [_ptr, _i64, _i64, _ptr, _ptr, _i64, _ptr, _ptr, _ptr, _i64, _int, _ptr],
+    "xgpr_b200_ard_grad_overwrite": [_ptr, _i64, _i64, _ptr, _ptr, _i64, _ptr, _ptr, _ptr, _i64, _int, _ptr],
     "xgpr_b200_conv1d_maxpool": [_ptr, _i64, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr, _int, _ptr],
     "xgpr_b200_conv1d_fgen": [_ptr, _i64, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr, _int, _int, _ptr],
     "xgpr_b200_conv1d_grad": [_ptr, _i64, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr, _ptr, _dbl,

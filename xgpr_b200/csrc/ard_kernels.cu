@@ -103,7 +103,12 @@ __device__ __forceinline__ void ard_dmma(double (&c)[2], double a, double b) {
 // GENERAL = false: sigma is constant on every group (rf = sum_l sigma_l G_l in the epilogue, no extra accumulators);
 // GENERAL = true: rf gets its own accumulators fed by x * sigma.  Both instances are launched; `uniform_flag` (written by
 // ard_uniform_kernel) makes the one that does not apply return at once -- the host never reads sigma back.
-template <typename T, int NG, bool GENERAL>
+// ACCUM = true: the reference's contract -- `gradArr[...] += G` on the caller's (zero-filled) array before the rescale
+// (ard_ops.cpp:100, :117-121), i.e. every launch READS the gradient array it then overwrites (ncu r02c: 8.6 GB of the
+// 21.4 GB of DRAM traffic, and 25 % of the stall samples wait on those loads).  ACCUM = false (xgpr_b200_ard_grad_overwrite_*)
+// writes the same values a zero-filled array would receive without reading it, so the caller can pass uninitialised
+// storage and skip its memset as well: what the MiniARD plugin class uses.
+template <typename T, int NG, bool GENERAL, bool ACCUM>
 __global__ void __launch_bounds__(256, (NG <= 2 && !GENERAL) ? 2 : 1)
 ard_mma_kernel(const T* __restrict__ x, double* __restrict__ out, const T* __restrict__ w,
                const int32_t* __restrict__ sigma_map, const double* __restrict__ sigma_vals,
@@ -273,7 +278,12 @@ ard_mma_kernel(const T* __restrict__ x, double* __restrict__ out, const T* __res
                 // grad += on a caller-zeroed array, then rescaled (ard_ops.cpp:100,117-121): the old values are
                 // requested first so that their latency hides behind the two double-precision sincos
                 double old[2][NG];
-                if (NG == 2 && two) {                            // 16-byte loads: gp is 32-byte aligned (f is even)
+                if (!ACCUM) {
+#pragma unroll
+                    for (int e = 0; e < 2; ++e)
+#pragma unroll
+                        for (int g = 0; g < NG; ++g) old[e][g] = 0.0;
+                } else if (NG == 2 && two) {                     // 16-byte loads: gp is 32-byte aligned (f is even)
                     const double2 o0 = __ldcs(reinterpret_cast<const double2*>(gp));
                     const double2 o1 = __ldcs(reinterpret_cast<const double2*>(gp + 4));
                     old[0][0] = o0.x; old[0][NG - 1] = o0.y; old[1][0] = o1.x; old[1][NG - 1] = o1.y;
@@ -314,7 +324,7 @@ ard_mma_kernel(const T* __restrict__ x, double* __restrict__ out, const T* __res
                 for (int e = 0; e < 2; ++e)
 #pragma unroll
                     for (int g = 0; g < NG; ++g) {
-                        const double gv = __dadd_rn(old[e][g], acc[g][i][j][e]);
+                        const double gv = ACCUM ? __dadd_rn(old[e][g], acc[g][i][j][e]) : acc[g][i][j][e];
                         vals[e * 2 * NG + g] = -gv * sv[e];
                         vals[e * 2 * NG + NG + g] = gv * cv[e];
                     }
@@ -365,7 +375,7 @@ static int* ard_flag_buffer() {                                  // 4 bytes per 
     return buf[dev];
 }
 
-template <typename T, int NG>
+template <typename T, int NG, bool ACCUM>
 static int launch_ard_mma(const T* x, int64_t n, int64_t d, double* out, const T* w, int64_t F, const int32_t* sigma_map,
                           const double* sigma_vals, double* grad, double scale, cudaStream_t st) {
     int* flag = ard_flag_buffer();
@@ -390,12 +400,12 @@ static int launch_ard_mma(const T* x, int64_t n, int64_t d, double* out, const T
         const int wld = resident ? wld_res : AM_LD;
         const size_t smem = xbytes + (size_t)AM_F * wld * 8 + tail;
         if (general) {
-            auto kern = ard_mma_kernel<T, NG, true>;
+            auto kern = ard_mma_kernel<T, NG, true, ACCUM>;
             ensure_dyn_smem(kern, smem);
             kern<<<grid, 256, smem, st>>>(x, out, w, sigma_map, sigma_vals, grad, (int)n, (int)d, (int)F, scale, npos_max,
                                           wld, resident ? 1 : 0, flag);
         } else {
-            auto kern = ard_mma_kernel<T, NG, false>;
+            auto kern = ard_mma_kernel<T, NG, false, ACCUM>;
             ensure_dyn_smem(kern, smem);
             kern<<<grid, 256, smem, st>>>(x, out, w, sigma_map, sigma_vals, grad, (int)n, (int)d, (int)F, scale, npos_max,
                                           wld, resident ? 1 : 0, flag);
@@ -408,7 +418,7 @@ static int launch_ard_mma(const T* x, int64_t n, int64_t d, double* out, const T
 template <typename T>
 int ard_dispatch(const T* x, int64_t n, int64_t d, double* out, const T* w, int64_t F,
                  const int32_t* sigma_map, const double* sigma_vals, double* grad, int64_t L,
-                 int fit_intercept, cudaStream_t st) {
+                 int fit_intercept, int overwrite, cudaStream_t st) {
     // validation: cpu_rf_gen/rbf_ops/ard_ops.cpp:66-82 (shapes are implied by the flat C signature)
     XB_REQUIRE(n > 0, "no datapoints");
     XB_REQUIRE(d > 0 && F > 0 && L > 0, "Wrong array sizes.");
@@ -420,10 +430,16 @@ int ard_dispatch(const T* x, int64_t n, int64_t d, double* out, const T* w, int6
     const bool simt_only = getenv("XGPR_B200_ARD_SIMT") != nullptr;   // the SIMT kernel reproduces the float product rounding
     const bool aligned16 = ((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(grad)) & 15) == 0;
     if (L <= 3 && d <= 1024 && F < (1ll << 26) && !simt_only && aligned16) {      // fp64 tensor-core path
-        if (L == 1) return launch_ard_mma<T, 1>(x, n, d, out, w, F, sigma_map, sigma_vals, grad, scale0, st);
-        if (L == 2) return launch_ard_mma<T, 2>(x, n, d, out, w, F, sigma_map, sigma_vals, grad, scale0, st);
-        return launch_ard_mma<T, 3>(x, n, d, out, w, F, sigma_map, sigma_vals, grad, scale0, st);
+#define XB_ARD(NGV)                                                                                              \
+        return overwrite ? launch_ard_mma<T, NGV, false>(x, n, d, out, w, F, sigma_map, sigma_vals, grad, scale0, st) \
+                         : launch_ard_mma<T, NGV, true>(x, n, d, out, w, F, sigma_map, sigma_vals, grad, scale0, st)
+        if (L == 1) XB_ARD(1);
+        if (L == 2) XB_ARD(2);
+        XB_ARD(3);
+#undef XB_ARD
     }
+    // SIMT kernel: accumulates onto the array, so the overwrite form zero-fills it first
+    if (overwrite) cudaMemsetAsync(grad, 0, sizeof(double) * (size_t)n * 2 * (size_t)F * (size_t)L, st);
     constexpr int TF = 32, TR = 8, KC = 32;
     const size_t smem = (size_t)L * TF * TR * 8 + KC * 8 + (size_t)KC * (TF + 1) * sizeof(T) +
                         (size_t)TR * KC * sizeof(T) + KC * 4;
@@ -453,8 +469,8 @@ int ard_dispatch(const T* x, int64_t n, int64_t d, double* out, const T* w, int6
 }
 
 template int ard_dispatch<float>(const float*, int64_t, int64_t, double*, const float*, int64_t, const int32_t*,
-                                 const double*, double*, int64_t, int, cudaStream_t);
+                                 const double*, double*, int64_t, int, int, cudaStream_t);
 template int ard_dispatch<double>(const double*, int64_t, int64_t, double*, const double*, int64_t, const int32_t*,
-                                  const double*, double*, int64_t, int, cudaStream_t);
+                                  const double*, double*, int64_t, int, int, cudaStream_t);
 
 }  // namespace xb

@@ -85,7 +85,7 @@ int conv_dispatch(const T* x, int64_t n, int64_t m, int64_t c, void* out, int64_
 template <typename T>
 int ard_dispatch(const T* x, int64_t n, int64_t d, double* out, const T* w, int64_t F,
                  const int32_t* sigma_map, const double* sigma_vals, double* grad, int64_t L,
-                 int fit_intercept, cudaStream_t st);
+                 int fit_intercept, int overwrite, cudaStream_t st);
 int zty_accum(const double* z, int64_t n, int64_t m, const double* y, double* zty, cudaStream_t st);
 int ztz_accum(const double* z, int64_t n, int64_t m, double* ztz, cudaStream_t st);
 int atb_accum(const double* a, const double* b, int64_t n, int64_t r, int64_t m, double* c, cudaStream_t st);
@@ -187,11 +187,20 @@ int xgpr_b200_rbf_zzv_f64(const double* x, int64_t n, int64_t d, const int8_t* r
 
 int xgpr_b200_ard_grad_f32(const float* x, int64_t n, int64_t d, double* out, const float* w, int64_t nf, const int32_t* smap,
                            const double* svals, double* grad, int64_t L, int fi, void* s) {
-    return ard_dispatch<float>(x, n, d, out, w, nf, smap, svals, grad, L, fi, ST(s));
+    return ard_dispatch<float>(x, n, d, out, w, nf, smap, svals, grad, L, fi, 0, ST(s));
 }
 int xgpr_b200_ard_grad_f64(const double* x, int64_t n, int64_t d, double* out, const double* w, int64_t nf, const int32_t* smap,
                            const double* svals, double* grad, int64_t L, int fi, void* s) {
-    return ard_dispatch<double>(x, n, d, out, w, nf, smap, svals, grad, L, fi, ST(s));
+    return ard_dispatch<double>(x, n, d, out, w, nf, smap, svals, grad, L, fi, 0, ST(s));
+}
+
+int xgpr_b200_ard_grad_overwrite_f32(const float* x, int64_t n, int64_t d, double* out, const float* w, int64_t nf,
+                                     const int32_t* smap, const double* svals, double* grad, int64_t L, int fi, void* s) {
+    return ard_dispatch<float>(x, n, d, out, w, nf, smap, svals, grad, L, fi, 1, ST(s));
+}
+int xgpr_b200_ard_grad_overwrite_f64(const double* x, int64_t n, int64_t d, double* out, const double* w, int64_t nf,
+                                     const int32_t* smap, const double* svals, double* grad, int64_t L, int fi, void* s) {
+    return ard_dispatch<double>(x, n, d, out, w, nf, smap, svals, grad, L, fi, 1, ST(s));
 }
 
 int xgpr_b200_conv1d_maxpool_f32(const float* x, int64_t n, int64_t m, int64_t c, float* out, int64_t num_rffs, const int8_t* radem,

@@ -286,7 +286,9 @@ def cudaRBFGrad(inputArr, outputArr, gradArr, radem, chiArr, sigma, fitIntercept
     return 0
 
 
-def cudaMiniARDGrad(inputArr, outputArr, precompWeights, sigmaMap, sigmaVals, gradArr, fitIntercept):
+def cudaMiniARDGrad(inputArr, outputArr, precompWeights, sigmaMap, sigmaVals, gradArr, fitIntercept, overwrite=False):
+    """overwrite=True (an addition to the reference signature): outputArr / gradArr are written without being read, i.e.
+    the values a zero-filled gradArr would receive -- they may be torch.empty storage (include/xgpr_b200.h)."""
     x = _dev(inputArr, "inputArr", _SFX, 2)
     o = _dev(outputArr, "outputArr", (torch.float64,), 2)
     w = _dev(precompWeights, "precompWeights", _SFX, 2)
@@ -302,7 +304,7 @@ def cudaMiniARDGrad(inputArr, outputArr, precompWeights, sigmaMap, sigmaVals, gr
     if w.shape[1] != x.shape[1] or o.shape[1] != 2 * w.shape[0] or sm.shape[0] != w.shape[1] \
             or sv.shape[0] != sm.shape[0]:
         raise RuntimeError("Wrong array sizes.")
-    check(getattr(lib, "xgpr_b200_ard_grad" + _SFX[x.dtype])(
+    check(getattr(lib, ("xgpr_b200_ard_grad_overwrite" if overwrite else "xgpr_b200_ard_grad") + _SFX[x.dtype])(
         x.data_ptr(), x.shape[0], x.shape[1], o.data_ptr(), w.data_ptr(), w.shape[0], sm.data_ptr(),
         sv.data_ptr(), g.data_ptr(), g.shape[2], int(bool(fitIntercept)), _stream()))
     return 0

@@ -109,9 +109,10 @@ class MiniARD(KernelBaseclass):
         if self.precomputed_weights is None:
             self.precompute_weights()
         nscales = int(self.split_pts.shape[0] - 1)
-        xtrans = torch.zeros((input_x.shape[0], self.num_rffs), dtype=torch.float64, device=input_x.device)
-        dz_dsigma = torch.zeros((input_x.shape[0], self.num_rffs, nscales), dtype=torch.float64,
+        # overwrite form: no zero-fill and no read-back of the 8 M L bytes per row the reference's `+=` contract costs
+        xtrans = torch.empty((input_x.shape[0], self.num_rffs), dtype=torch.float64, device=input_x.device)
+        dz_dsigma = torch.empty((input_x.shape[0], self.num_rffs, nscales), dtype=torch.float64,
                                 device=input_x.device)
         ext.cudaMiniARDGrad(input_x, xtrans, self.precomputed_weights, self.ard_position_key,
-                            self.full_ard_weights, dz_dsigma, self.fit_intercept)
+                            self.full_ard_weights, dz_dsigma, self.fit_intercept, overwrite=True)
         return xtrans, dz_dsigma
