@@ -24,6 +24,7 @@
 namespace cg = cooperative_groups;
 
 #include <mutex>
+#include <stdlib.h>
 
 namespace xb {
 
@@ -49,7 +50,22 @@ unscale_to_f32_kernel(const double* __restrict__ z, int64_t count, double scale,
         c[i] = (float)(z[i] / scale);
 }
 
-template <int EPT>
+// float -> double on the INTEGER pipe, exact for every finite float that is zero or normal (cos / sin values are):
+// hi = sign | (exponent + 896) << 20 | mantissa[22:3], lo = mantissa[2:0] << 29.  Six ALU instructions against one
+// F2F.F64.F32 on the 16-lane XU pipe -- slower by itself (round 1 measured 4.0 TB/s with every conversion done this way),
+// but the two pipes run side by side: MIX = 1 sends 3 of the 8 conversions per float4 (one in the dot phase, two in the
+// accumulate phase) through the ALU, which takes the XU load from 0.125 to ~0.08 clk per feature.
+__device__ __forceinline__ double widen_alu(float f) {
+    const int u = __float_as_int(f);
+    int hi = ((u >> 3) & (int)0x8FFFFFFF) + 0x38000000;     // arithmetic shift keeps the sign in bit 31
+    hi = ((u << 1) == 0) ? (u & (int)0x80000000) : hi;     // +-0 stays +-0
+    return __hiloint2double(hi, u << 29);
+}
+template <int MIX> __device__ __forceinline__ double widen(float f, bool alu) {
+    return (MIX != 0 && alu) ? widen_alu(f) : (double)f;
+}
+
+template <int EPT, int MIX>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CR_THREADS, 1)
 cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict__ vs, double* __restrict__ w,
                 double scale, int fit_intercept, int64_t rows_per_cluster, const double* __restrict__ skip) {
@@ -120,10 +136,10 @@ cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict
             for (int k = 0; k < PCS; ++k) {
                 float4 q = *reinterpret_cast<const float4*>(st + k * 4 * CR_THREADS);
                 if (one && k == 0) q.x = 1.0f;
-                d0 = fma((double)q.x, v[4 * k], d0);
-                d1 = fma((double)q.y, v[4 * k + 1], d1);
-                d0 = fma((double)q.z, v[4 * k + 2], d0);
-                d1 = fma((double)q.w, v[4 * k + 3], d1);
+                d0 = fma(widen<MIX>(q.x, false), v[4 * k], d0);
+                d1 = fma(widen<MIX>(q.y, false), v[4 * k + 1], d1);
+                d0 = fma(widen<MIX>(q.z, false), v[4 * k + 2], d0);
+                d1 = fma(widen<MIX>(q.w, true), v[4 * k + 3], d1);
             }
             dot[r] = d0 + d1;
         }
@@ -168,10 +184,10 @@ cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict
             for (int k = 0; k < PCS; ++k) {
                 float4 q = *reinterpret_cast<const float4*>(st + k * 4 * CR_THREADS);
                 if (one && k == 0) q.x = 1.0f;
-                acc[4 * k] = fma((double)q.x, t, acc[4 * k]);
-                acc[4 * k + 1] = fma((double)q.y, t, acc[4 * k + 1]);
-                acc[4 * k + 2] = fma((double)q.z, t, acc[4 * k + 2]);
-                acc[4 * k + 3] = fma((double)q.w, t, acc[4 * k + 3]);
+                acc[4 * k] = fma(widen<MIX>(q.x, false), t, acc[4 * k]);
+                acc[4 * k + 1] = fma(widen<MIX>(q.y, true), t, acc[4 * k + 1]);
+                acc[4 * k + 2] = fma(widen<MIX>(q.z, false), t, acc[4 * k + 2]);
+                acc[4 * k + 3] = fma(widen<MIX>(q.w, true), t, acc[4 * k + 3]);
             }
         }
         issue(2 * b + 3);                                // into the two stages this batch has just finished with
@@ -201,13 +217,13 @@ int unscale_to_f32(const double* z, int64_t count, double scale, float* c, cudaS
 
 int cres_zzv_supported(int64_t m) { return (m == 4096 || m == 8192 || m == 16384) ? 1 : 0; }
 
-template <int EPT>
+template <int EPT, int MIX>
 static int launch_cres(const float* c, int64_t n, const double* vs, double* w, double scale, int fit_intercept,
                        const double* skip, cudaStream_t st) {
     constexpr int HC = CR_THREADS * EPT;
     constexpr int RB = cr_batch_rows(EPT);
     constexpr int SMEM = CR_STAGES * (RB / 2) * HC * 4 + (2 * RB * (CR_THREADS / 32) + 4 * RB) * 8;
-    auto kern = cres_zzv_kernel<EPT>;
+    auto kern = cres_zzv_kernel<EPT, MIX>;
     static int clusters_dev[64] = {};                    // attribute + occupancy are per device
     static std::mutex mu;
     const int dev_id = current_device();
@@ -248,10 +264,18 @@ int cres_zzv(const float* c, int64_t n, int64_t m, const double* vs, double* w, 
     XB_REQUIRE(c && vs && w, "null pointer");
     XB_REQUIRE(cres_zzv_supported(m), "resident matvec: num_rffs must be 4096, 8192 or 16384");
     XB_REQUIRE((reinterpret_cast<uintptr_t>(c) & 15) == 0, "resident matvec: C must be 16-byte aligned");
+    static const bool mix = getenv("XGPR_B200_CRES_MIX") != nullptr;        // A/B switch, see widen_alu
+    if (mix) {
+        switch (m) {
+            case 4096: return launch_cres<4, 1>(c, n, vs, w, scale, fit_intercept, skip, st);
+            case 8192: return launch_cres<8, 1>(c, n, vs, w, scale, fit_intercept, skip, st);
+            default:   return launch_cres<16, 1>(c, n, vs, w, scale, fit_intercept, skip, st);
+        }
+    }
     switch (m) {
-        case 4096: return launch_cres<4>(c, n, vs, w, scale, fit_intercept, skip, st);
-        case 8192: return launch_cres<8>(c, n, vs, w, scale, fit_intercept, skip, st);
-        default:   return launch_cres<16>(c, n, vs, w, scale, fit_intercept, skip, st);
+        case 4096: return launch_cres<4, 0>(c, n, vs, w, scale, fit_intercept, skip, st);
+        case 8192: return launch_cres<8, 0>(c, n, vs, w, scale, fit_intercept, skip, st);
+        default:   return launch_cres<16, 0>(c, n, vs, w, scale, fit_intercept, skip, st);
     }
 }
 
