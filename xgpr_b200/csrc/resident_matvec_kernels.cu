@@ -65,7 +65,7 @@ template <int MIX> __device__ __forceinline__ double widen(float f, bool alu) {
     return (MIX != 0 && alu) ? widen_alu(f) : (double)f;
 }
 
-template <int EPT, int MIX>
+template <int EPT, int MIX, bool PF = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CR_THREADS, 1)
 cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict__ vs, double* __restrict__ w,
                 double scale, int fit_intercept, int64_t rows_per_cluster, const double* __restrict__ skip) {
@@ -119,10 +119,25 @@ cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict
         }
         cr_commit();
     };
+    // L2 prefetch (cp.async.bulk.prefetch.L2, one instruction per row half): the ring keeps only one stage (64 KB per SM)
+    // in flight while a batch is processed -- about what Little's law needs at DRAM latency, and the long-scoreboard
+    // stalls on cp.async.wait said so (ncu r02k) -- so the rows of the batch AFTER the ring's look-ahead are pulled into L2,
+    // from where the later cp.async completes at L2 latency.
+    auto prefetch_l2 = [&](int64_t g) {                  // stage g = rows [row_beg + g * SR, + SR)
+        if (PF && tid < SR) {
+            const int64_t row = row_beg + g * SR + tid;
+            if (row < row_end)
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(c + row * m + col0), "r"(HC * 4) : "memory");
+        }
+    };
     issue(0);
     issue(1);
     issue(2);
+    prefetch_l2(3);
+    prefetch_l2(4);
     for (int64_t b = 0; b < batches; ++b) {
+        prefetch_l2(2 * b + 5);
+        prefetch_l2(2 * b + 6);
         cr_wait<1>();                                    // stages 2b and 2b+1 have landed; 2b+2 stays in flight
         const int par = (int)(b & 1);
         const int64_t brow = row_beg + b * RB;
@@ -217,13 +232,13 @@ int unscale_to_f32(const double* z, int64_t count, double scale, float* c, cudaS
 
 int cres_zzv_supported(int64_t m) { return (m == 4096 || m == 8192 || m == 16384) ? 1 : 0; }
 
-template <int EPT, int MIX>
+template <int EPT, int MIX, bool PF = false>
 static int launch_cres(const float* c, int64_t n, const double* vs, double* w, double scale, int fit_intercept,
                        const double* skip, cudaStream_t st) {
     constexpr int HC = CR_THREADS * EPT;
     constexpr int RB = cr_batch_rows(EPT);
     constexpr int SMEM = CR_STAGES * (RB / 2) * HC * 4 + (2 * RB * (CR_THREADS / 32) + 4 * RB) * 8;
-    auto kern = cres_zzv_kernel<EPT, MIX>;
+    auto kern = cres_zzv_kernel<EPT, MIX, PF>;
     static int clusters_dev[64] = {};                    // attribute + occupancy are per device
     static std::mutex mu;
     const int dev_id = current_device();
@@ -265,6 +280,14 @@ int cres_zzv(const float* c, int64_t n, int64_t m, const double* vs, double* w, 
     XB_REQUIRE(cres_zzv_supported(m), "resident matvec: num_rffs must be 4096, 8192 or 16384");
     XB_REQUIRE((reinterpret_cast<uintptr_t>(c) & 15) == 0, "resident matvec: C must be 16-byte aligned");
     static const bool mix = getenv("XGPR_B200_CRES_MIX") != nullptr;        // A/B switch, see widen_alu
+    static const bool pf = getenv("XGPR_B200_CRES_PF") != nullptr;          // A/B switch: L2 prefetch + mixed widening
+    if (pf) {
+        switch (m) {
+            case 4096: return launch_cres<4, 1, true>(c, n, vs, w, scale, fit_intercept, skip, st);
+            case 8192: return launch_cres<8, 1, true>(c, n, vs, w, scale, fit_intercept, skip, st);
+            default:   return launch_cres<16, 1, true>(c, n, vs, w, scale, fit_intercept, skip, st);
+        }
+    }
     if (mix) {
         switch (m) {
             case 4096: return launch_cres<4, 1>(c, n, vs, w, scale, fit_intercept, skip, st);
