@@ -68,7 +68,7 @@ template <int MIX> __device__ __forceinline__ double widen(float f, bool alu) {
 template <int EPT, int MIX, bool PF = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CR_THREADS, 1)
 cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict__ vs, double* __restrict__ w,
-                double scale, int fit_intercept, int64_t rows_per_cluster, const double* __restrict__ skip) {
+                double scale, int fit_intercept, int64_t rows_per_cluster, const double* __restrict__ skip, int pf_dist) {
     // gate for stream-ordered solvers (cg_kernels.cu): a non-zero *skip means "the solve has converged", and the launch
     // becomes a no-op.  Both CTAs of a cluster read the same word, before any cluster barrier.
     if (skip != nullptr && *skip != 0.0) return;
@@ -133,11 +133,10 @@ cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict
     issue(0);
     issue(1);
     issue(2);
-    prefetch_l2(3);
-    prefetch_l2(4);
+    for (int g = 3; g < 3 + 2 * pf_dist; ++g) prefetch_l2(g);
     for (int64_t b = 0; b < batches; ++b) {
-        prefetch_l2(2 * b + 5);
-        prefetch_l2(2 * b + 6);
+        prefetch_l2(2 * b + 3 + 2 * pf_dist);            // pf_dist batches beyond the ring's own look-ahead
+        prefetch_l2(2 * b + 4 + 2 * pf_dist);
         cr_wait<1>();                                    // stages 2b and 2b+1 have landed; 2b+2 stays in flight
         const int par = (int)(b & 1);
         const int64_t brow = row_beg + b * RB;
@@ -267,7 +266,9 @@ static int launch_cres(const float* c, int64_t n, const double* vs, double* w, d
     int64_t rows_per = (n + nclusters - 1) / nclusters;
     rows_per = ((rows_per + RB - 1) / RB) * RB;
     nclusters = (n + rows_per - 1) / rows_per;
-    kern<<<(unsigned)(2 * nclusters), CR_THREADS, SMEM, st>>>(c, n, vs, w, scale, fit_intercept, rows_per, skip);
+    static const int pf_env = getenv("XGPR_B200_CRES_PF_DIST") ? atoi(getenv("XGPR_B200_CRES_PF_DIST")) : 1;
+    kern<<<(unsigned)(2 * nclusters), CR_THREADS, SMEM, st>>>(c, n, vs, w, scale, fit_intercept, rows_per, skip,
+                                                             pf_env < 1 ? 1 : (pf_env > 8 ? 8 : pf_env));
     count_launch();
     return check_launch("cres_zzv_kernel");
 }
