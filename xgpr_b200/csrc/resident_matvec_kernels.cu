@@ -280,22 +280,15 @@ int cres_zzv(const float* c, int64_t n, int64_t m, const double* vs, double* w, 
     XB_REQUIRE(c && vs && w, "null pointer");
     XB_REQUIRE(cres_zzv_supported(m), "resident matvec: num_rffs must be 4096, 8192 or 16384");
     XB_REQUIRE((reinterpret_cast<uintptr_t>(c) & 15) == 0, "resident matvec: C must be 16-byte aligned");
-    static const bool mix = getenv("XGPR_B200_CRES_MIX") != nullptr;        // A/B switch, see widen_alu
-    static const bool pf = getenv("XGPR_B200_CRES_PF") != nullptr;          // A/B switch: L2 prefetch + mixed widening
-    if (pf) {
-        switch (m) {
-            case 4096: return launch_cres<4, 1, true>(c, n, vs, w, scale, fit_intercept, skip, st);
-            case 8192: return launch_cres<8, 1, true>(c, n, vs, w, scale, fit_intercept, skip, st);
-            default:   return launch_cres<16, 1, true>(c, n, vs, w, scale, fit_intercept, skip, st);
-        }
-    }
-    if (mix) {
-        switch (m) {
-            case 4096: return launch_cres<4, 1>(c, n, vs, w, scale, fit_intercept, skip, st);
-            case 8192: return launch_cres<8, 1>(c, n, vs, w, scale, fit_intercept, skip, st);
-            default:   return launch_cres<16, 1>(c, n, vs, w, scale, fit_intercept, skip, st);
-        }
-    }
+    // Variant per width, from the A/B on a B200 (profiles/r02l_cres_ab.md; GB/s of C at 262,144 rows):
+    //   16,384 columns: base 4,953 | mixed widening 5,080 | + L2 prefetch 5,525   -> prefetch + mix
+    //    8,192 columns: base 4,967 | 5,016 | 5,277                                -> prefetch + mix
+    //    4,096 columns: base 4,468 | 4,275 | 4,125                                -> base
+    // XGPR_B200_CRES_BASE forces the base kernel everywhere; XGPR_B200_CRES_PF_DIST sets the prefetch distance in batches
+    // (1 is best: 2 already loses 17 %, the prefetches start to compete with the demand stream).
+    static const bool base_only = getenv("XGPR_B200_CRES_BASE") != nullptr;
+    if (!base_only && m == 16384) return launch_cres<16, 1, true>(c, n, vs, w, scale, fit_intercept, skip, st);
+    if (!base_only && m == 8192) return launch_cres<8, 1, true>(c, n, vs, w, scale, fit_intercept, skip, st);
     switch (m) {
         case 4096: return launch_cres<4, 0>(c, n, vs, w, scale, fit_intercept, skip, st);
         case 8192: return launch_cres<8, 0>(c, n, vs, w, scale, fit_intercept, skip, st);
