@@ -241,6 +241,16 @@ int xgpr_b200_atb_accum_f64(const double* a, const double* z, int64_t n, int64_t
 /* w (m, r) += Z^T (Z v) ;  v (m, r) row-major; scratch (n, r) f64 device workspace */
 int xgpr_b200_cg_matvec_accum_f64(const double* z, int64_t n, int64_t m, const double* v, int64_t r,
                                   double* w, double* scratch, void* stream);
+/* w (m, r) += Z^T (Z v) with NO caller workspace and no allocation of any kind: the (n, r) intermediate lives in a
+ * file-scope device array of xgpr_b200_cg_matvec_static_max_elems() = 1,048,576 doubles (8 MiB, held by every GPU that
+ * loads the library until exit).  No counterpart in the reference: added for callers
+ * that cannot call cudaMalloc (stream capture, serving loops, harnesses that forbid it).  Same kernels, same results as
+ * xgpr_b200_cg_matvec_accum_f64.  n * r beyond the maximum -> XGPR_B200_EINVAL with a message naming the limit.  All calls on
+ * one device share the array (it keeps the previous call's contents; nothing the kernels read is left unwritten), so calls
+ * that overlap on the GPU -- two streams -- race: serialise them on one stream or with events. */
+int64_t xgpr_b200_cg_matvec_static_max_elems(void);
+int xgpr_b200_cg_matvec_accum_static_f64(const double* z, int64_t n, int64_t m, const double* v, int64_t r, double* w,
+                                         void* stream);
 
 #ifdef __cplusplus
 }

@@ -44,6 +44,7 @@ F64_ONLY = {
     "xgpr_b200_ztzq_accum_tc_f64": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _int, _int, _ptr, _i64, _ptr],
     "xgpr_b200_atb_accum_f64": [_ptr, _ptr, _i64, _i64, _i64, _ptr, _ptr],
     "xgpr_b200_cg_matvec_accum_f64": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _ptr, _ptr],
+    "xgpr_b200_cg_matvec_accum_static_f64": [_ptr, _i64, _i64, _ptr, _i64, _ptr, _ptr],
 }
 
 EXPORTED = ["xgpr_b200_abi_version", "xgpr_b200_last_error", "xgpr_b200_launch_count"]
@@ -59,6 +60,9 @@ for _name, _args in F64_ONLY.items():
     _fn.restype = _int
     EXPORTED.append(_name)
 
+lib.xgpr_b200_cg_matvec_static_max_elems.argtypes = []
+lib.xgpr_b200_cg_matvec_static_max_elems.restype = _i64
+EXPORTED.append("xgpr_b200_cg_matvec_static_max_elems")
 lib.xgpr_b200_ztz_tc_workspace_bytes.argtypes = [_i64, _i64, _int]
 lib.xgpr_b200_ztz_tc_workspace_bytes.restype = _i64
 EXPORTED.append("xgpr_b200_ztz_tc_workspace_bytes")

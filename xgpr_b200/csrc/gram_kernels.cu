@@ -9,6 +9,7 @@
 // arithmetic.  The Gram-shaped products default to the tcgen05 split-int8 kernel in gram_tc_kernels.cu; these stay as
 // the gram="f64" path, the HBM-bound Z^T y, and the skinny matvecs.
 #include "common.cuh"
+#include <mutex>
 
 namespace xb {
 
@@ -831,6 +832,51 @@ int cg_matvec_accum(const double* z, int64_t n, int64_t m, const double* v, int6
         count_launch(2);
     }
     return check_launch("cg_matvec");
+}
+
+// ---- allocation-free variant (no counterpart in the reference) ----------
+// The (n, r) intermediate Z v lives in a file-scope device array instead of a caller-supplied workspace, so a caller that
+// may not allocate (stream capture, a serving loop, a harness that forbids cudaMalloc) still has the matvec.  Every GPU
+// that loads the library holds the array (8 MiB) until exit.  All calls on one device share it and it keeps the previous
+// call's contents: cg_matvec_accum itself writes or zero-fills every element it later reads, so nothing has to be cleared
+// between calls, but two calls that overlap on the GPU (different streams) race on it.
+constexpr int64_t CG_STATIC_SCRATCH_DOUBLES = (int64_t)1 << 20;
+static __device__ __align__(256) double g_cg_static_scratch[CG_STATIC_SCRATCH_DOUBLES];
+
+int64_t cg_matvec_static_max_elems() { return CG_STATIC_SCRATCH_DOUBLES; }
+
+int cg_matvec_accum_static(const double* z, int64_t n, int64_t m, const double* v, int64_t r, double* w, cudaStream_t st) {
+    XB_REQUIRE(n > 0 && m > 0 && r > 0, "no datapoints");
+    if (n > CG_STATIC_SCRATCH_DOUBLES / r) {      // n * r > the array, written without overflowing
+        set_error("cg_matvec_accum_static: n * r = %lld x %lld exceeds the static scratch (%lld doubles); use "
+                  "xgpr_b200_cg_matvec_accum_f64 with a caller-supplied workspace",
+                  (long long)n, (long long)r, (long long)CG_STATIC_SCRATCH_DOUBLES);
+        return XGPR_B200_EINVAL;
+    }
+    // In host code the array's name is only a handle for the runtime, not a device address: the address is looked up
+    // once per device, with that device current, and it is this pointer the kernels are given.
+    static std::mutex mu;
+    static double* addr[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+        set_error("cg_matvec_accum_static: no current device (or ordinal >= 64)");
+        return XGPR_B200_ECUDA;
+    }
+    double* scratch;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!addr[dev]) {
+            double* p = nullptr;
+            const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_cg_static_scratch);
+            if (e != cudaSuccess || !p) {
+                set_error("cg_matvec_accum_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+                return XGPR_B200_ECUDA;
+            }
+            addr[dev] = p;
+        }
+        scratch = addr[dev];
+    }
+    return cg_matvec_accum(z, n, m, v, r, w, scratch, st);
 }
 
 }  // namespace xb
