@@ -65,7 +65,7 @@ template <int MIX> __device__ __forceinline__ double widen(float f, bool alu) {
     return (MIX != 0 && alu) ? widen_alu(f) : (double)f;
 }
 
-template <int EPT, int MIX, bool PF = false>
+template <int EPT, int MIX, bool PF = false, bool INTER = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CR_THREADS, 1)
 cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict__ vs, double* __restrict__ w,
                 double scale, int fit_intercept, int64_t rows_per_cluster, const double* __restrict__ skip, int pf_dist) {
@@ -91,9 +91,20 @@ cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict
     const int64_t m = 2 * (int64_t)HC;
     const int64_t col0 = (int64_t)crank * HC;
     const int64_t cl = blockIdx.x >> 1;
-    const int64_t row_beg = cl * rows_per_cluster;
-    const int64_t row_end = (row_beg + rows_per_cluster < n) ? row_beg + rows_per_cluster : n;
-    const int64_t batches = (row_end > row_beg) ? (row_end - row_beg + RB - 1) / RB : 0;
+    // !INTER: cluster cl owns the contiguous rows [cl * rows_per_cluster, + rows_per_cluster).
+    // INTER: rows_per_cluster carries the NUMBER OF CLUSTERS; batch j of cluster cl is global batch cl + j * nclus, so at
+    // any moment all clusters stream one narrow window of C (TLB / DRAM page locality on shards of tens of GB) instead of
+    // 70-odd streams hundreds of MB apart.
+    constexpr bool inter = INTER;
+    const int64_t nclus = inter ? rows_per_cluster : 1;
+    const int64_t row_beg = inter ? 0 : cl * rows_per_cluster;
+    const int64_t row_end = inter ? n : ((row_beg + rows_per_cluster < n) ? row_beg + rows_per_cluster : n);
+    const int64_t tot_batches = (n + RB - 1) / RB;
+    const int64_t batches = inter ? (cl < tot_batches ? (tot_batches - cl + nclus - 1) / nclus : 0)
+                                  : ((row_end > row_beg) ? (row_end - row_beg + RB - 1) / RB : 0);
+    auto stage_row = [&](int64_t g) -> int64_t {         // first row of ring stage g (a batch is stages 2b, 2b + 1)
+        return inter ? (cl + (g >> 1) * nclus) * RB + (g & 1) * SR : row_beg + g * SR;
+    };
     const bool icpt = fit_intercept && crank == 0 && tid == 0;      // owns global column 0 (piece 0, element 0)
 
     double v[EPT], acc[EPT];
@@ -105,12 +116,12 @@ cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict
             acc[4 * k + i] = 0.0;
         }
 
-    // stage g holds rows [row_beg + g * SR, + SR); every thread copies exactly the pieces it reads itself
+    // stage g holds rows [stage_row(g), + SR); every thread copies exactly the pieces it reads itself
     auto issue = [&](int64_t g) {
         float* st = ring + (g % CR_STAGES) * SR * HC;
 #pragma unroll
         for (int r = 0; r < SR; ++r) {
-            const int64_t row = row_beg + g * SR + r;
+            const int64_t row = stage_row(g) + r;
             const bool ok = row < row_end;
             const float* src = c + (ok ? row : 0) * m + col0 + 4 * tid;
 #pragma unroll
@@ -123,9 +134,9 @@ cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict
     // in flight while a batch is processed -- about what Little's law needs at DRAM latency, and the long-scoreboard
     // stalls on cp.async.wait said so (ncu r02k) -- so the rows of the batch AFTER the ring's look-ahead are pulled into L2,
     // from where the later cp.async completes at L2 latency.
-    auto prefetch_l2 = [&](int64_t g) {                  // stage g = rows [row_beg + g * SR, + SR)
+    auto prefetch_l2 = [&](int64_t g) {                  // stage g = rows [stage_row(g), + SR)
         if (PF && tid < SR) {
-            const int64_t row = row_beg + g * SR + tid;
+            const int64_t row = stage_row(g) + tid;
             if (row < row_end)
                 asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(c + row * m + col0), "r"(HC * 4) : "memory");
         }
@@ -139,7 +150,7 @@ cres_zzv_kernel(const float* __restrict__ c, int64_t n, const double* __restrict
         prefetch_l2(2 * b + 4 + 2 * pf_dist);
         cr_wait<1>();                                    // stages 2b and 2b+1 have landed; 2b+2 stays in flight
         const int par = (int)(b & 1);
-        const int64_t brow = row_beg + b * RB;
+        const int64_t brow = stage_row(2 * b);
         double dot[RB];
 #pragma unroll
         for (int r = 0; r < RB; ++r) {
@@ -231,13 +242,13 @@ int unscale_to_f32(const double* z, int64_t count, double scale, float* c, cudaS
 
 int cres_zzv_supported(int64_t m) { return (m == 4096 || m == 8192 || m == 16384) ? 1 : 0; }
 
-template <int EPT, int MIX, bool PF = false>
+template <int EPT, int MIX, bool PF = false, bool INTER = false>
 static int launch_cres(const float* c, int64_t n, const double* vs, double* w, double scale, int fit_intercept,
                        const double* skip, cudaStream_t st) {
     constexpr int HC = CR_THREADS * EPT;
     constexpr int RB = cr_batch_rows(EPT);
     constexpr int SMEM = CR_STAGES * (RB / 2) * HC * 4 + (2 * RB * (CR_THREADS / 32) + 4 * RB) * 8;
-    auto kern = cres_zzv_kernel<EPT, MIX, PF>;
+    auto kern = cres_zzv_kernel<EPT, MIX, PF, INTER>;
     static int clusters_dev[64] = {};                    // attribute + occupancy are per device
     static std::mutex mu;
     const int dev_id = current_device();
@@ -267,6 +278,7 @@ static int launch_cres(const float* c, int64_t n, const double* vs, double* w, d
     rows_per = ((rows_per + RB - 1) / RB) * RB;
     nclusters = (n + rows_per - 1) / rows_per;
     static const int pf_env = getenv("XGPR_B200_CRES_PF_DIST") ? atoi(getenv("XGPR_B200_CRES_PF_DIST")) : 1;
+    if (INTER) rows_per = nclusters;                     // batches dealt round-robin to the clusters
     kern<<<(unsigned)(2 * nclusters), CR_THREADS, SMEM, st>>>(c, n, vs, w, scale, fit_intercept, rows_per, skip,
                                                              pf_env < 1 ? 1 : (pf_env > 8 ? 8 : pf_env));
     count_launch();
@@ -287,6 +299,14 @@ int cres_zzv(const float* c, int64_t n, int64_t m, const double* vs, double* w, 
     // XGPR_B200_CRES_BASE forces the base kernel everywhere; XGPR_B200_CRES_PF_DIST sets the prefetch distance in batches
     // (1 is best: 2 already loses 17 %, the prefetches start to compete with the demand stream).
     static const bool base_only = getenv("XGPR_B200_CRES_BASE") != nullptr;
+    // Batches are dealt round-robin to the clusters (all SMs stream one narrow window of C) rather than one contiguous
+    // row range per cluster: +1.5 - 2.5 % at every shard size (profiles/r02n_cres_interleave.jsonl: 1M rows 5,095 ->
+    // 5,213 GB/s, 262,144 rows 5,527 -> 5,604, 8,192 columns 5,153 -> 5,265).  XGPR_B200_CRES_CONTIG restores the ranges.
+    static const bool interleave = getenv("XGPR_B200_CRES_CONTIG") == nullptr;
+    if (!base_only && interleave && m == 16384)
+        return launch_cres<16, 1, true, true>(c, n, vs, w, scale, fit_intercept, skip, st);
+    if (!base_only && interleave && m == 8192)
+        return launch_cres<8, 1, true, true>(c, n, vs, w, scale, fit_intercept, skip, st);
     if (!base_only && m == 16384) return launch_cres<16, 1, true>(c, n, vs, w, scale, fit_intercept, skip, st);
     if (!base_only && m == 8192) return launch_cres<8, 1, true>(c, n, vs, w, scale, fit_intercept, skip, st);
     switch (m) {
