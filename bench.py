@@ -53,6 +53,8 @@ def parse():
     ap.add_argument("--fit-rows", type=int, default=1000000, help="GLOBAL rows of the strong-scaling fit (0 = skip)")
     ap.add_argument("--fit-rank", type=int, default=512)
     ap.add_argument("--save-fit-weights", action="store_true", help="N=1 only: (re)write tests/golden/cfg2_fit_w_n1.npy")
+    ap.add_argument("--nmll-rows", type=int, default=2000000,
+                    help="GLOBAL rows of the cfg5 approximate-NMLL evaluation (0 = skip)")
     ap.add_argument("--no-gram", action="store_true")
     ap.add_argument("--no-conv", action="store_true")
     return ap.parse_args()
@@ -369,6 +371,8 @@ def run_b200(args):
     gram = gram_headline(dev, rank) if not args.no_gram else None
     torch.cuda.empty_cache()
     fit = fit_headline(args, dev, rank, world) if args.fit_rows > 0 else None
+    torch.cuda.empty_cache()
+    nmll = nmll_headline(args, dev, rank, world) if args.nmll_rows > 0 else None
 
     vals = [dev_ms, e2e_ms, float(np.mean(kern_ms)), e2e_mat_ms, e2e_small_ms]
     vals += [conv["ms"], conv["e2e_ms"]] if conv else [0.0, 0.0]
@@ -425,6 +429,8 @@ def run_b200(args):
             line["gram"] = gram_record(gram, gram_ms, gram_gemm_ms, gram_dfma_ms)
         if fit:
             line["fit"] = fit
+        if nmll:
+            line["nmll"] = nmll
         if world == 1 and not args.no_cpu_baseline:
             try:
                 v, kind, cores, sample = cpu_rows_per_s(draw_params(), args.cpu_rows)
@@ -720,6 +726,82 @@ def fit_headline(args, dev, rank, world, chunk=32768, tol=1e-6, maxiter=200):
                "weights_vs_n1": {"max_abs_err_over_max_abs_w": w_err, "bound": 1e-6,
                                  "reference_vector": "tests/golden/cfg2_fit_w_n1.npy (this fit on 1 B200)"}}
     del x, y, ds, pre
+    torch.cuda.empty_cache()
+    return rec
+
+
+NMLL_DIM, NMLL_RFFS, NMLL_BLOCK = 128, 32768, 62500
+
+
+def nmll_dataset(n_global, rank, world, dev):
+    """cfg5's synthetic training set, identical at every N: defined in blocks of 62,500 rows, block b drawn on the device
+    from seed 1000 + b; a rank generates the blocks that overlap its row range [rank/N, (rank+1)/N) and slices them."""
+    import torch
+    lo, hi = (n_global * rank) // world, (n_global * (rank + 1)) // world
+    xs, ys = [], []
+    for b in range(lo // NMLL_BLOCK, (hi + NMLL_BLOCK - 1) // NMLL_BLOCK):
+        g = torch.Generator(device=dev)
+        g.manual_seed(1000 + b)
+        rows = min(NMLL_BLOCK, n_global - b * NMLL_BLOCK)
+        x = torch.randn((rows, NMLL_DIM), generator=g, device=dev, dtype=torch.float32)
+        y = torch.sin(x[:, :8].sum(1)) + 0.1 * torch.randn(rows, generator=g, device=dev)
+        a, e = max(lo - b * NMLL_BLOCK, 0), min(hi - b * NMLL_BLOCK, rows)
+        xs.append(x[a:e])
+        ys.append(y[a:e].double())
+    return torch.cat(xs).contiguous(), torch.cat(ys).contiguous()
+
+
+def nmll_headline(args, dev, rank, world, chunk=32768):
+    """cfg5 (BASELINE.json configs[4]): MiniARD split_points=[64], 2M x 128 -> 32,768 RFFs, ONE approximate-NMLL evaluation
+    (stochastic Lanczos quadrature: 25 probes + y = 26 right-hand sides through preconditioned CG to 1e-6, rank-512
+    "srht_2" Nystrom preconditioner) -- the objective the reference's tuning loop calls (xgp_regression.py
+    approximate_nmll -> approximate_nmll_calcs.py).  STRONG scaling: global rows fixed, rows sharded, fp64 all-reduces.
+    One small untimed evaluation first (cuSOLVER / cuBLAS handles, kernel attributes), then the full one timed with CUDA
+    events, max over ranks."""
+    import torch
+    import torch.distributed as dist
+    from xgpr_b200 import ext, fitting, scoring
+    from xgpr_b200.kernels import MiniARD
+    comm = fitting.RowShardComm()
+    sig = 0.358 / np.sqrt(NMLL_DIM) * 4.0
+    hp = np.log(np.asarray([np.sqrt(0.0767), sig, sig]))     # the hyperparameters of the round-1 record (tools/bench_nmll.py)
+    settings = {"max_rank": 512, "nsamples": 25, "nmll_tol": 1e-6, "nmll_iter": 500, "preconditioner_mode": "srht_2"}
+    kern = MiniARD((args.nmll_rows, NMLL_DIM), NMLL_RFFS, random_seed=123, device="cuda",
+                   kernel_spec_parms={"split_points": [NMLL_DIM // 2]})
+    x, y = nmll_dataset(args.nmll_rows, rank, world, dev)
+    warm_rows = min(x.shape[0], 8192)
+    ds_w = fitting.build_shard_dataset(x[:warm_rows].clone(), y[:warm_rows].clone(), None, chunk, comm)
+    scoring.approximate_nmll(hp.copy(), ds_w, kern, dict(settings), 123, comm)
+    del ds_w
+    ds = fitting.build_shard_dataset(x, y, None, chunk, comm)
+    torch.cuda.empty_cache()
+    comm.n_allreduce, comm.bytes_allreduce = 0, 0
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    torch.cuda.reset_peak_memory_stats()
+    l0 = ext.launch_count()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    val = scoring.approximate_nmll(hp.copy(), ds, kern, dict(settings), 123, comm)
+    b.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    secs = float(t[0]) * 1e-3
+    rec = None
+    if rank == 0:
+        rec = {"metric": "cfg5 approximate NMLL evaluation wall-clock (strong scaling)", "value": secs, "unit": "s",
+               "higher_is_better": False, "scaling": "strong",
+               "workload": f"MiniARD split_points=[64], {args.nmll_rows} x {NMLL_DIM} (global, same dataset at every N: "
+                           f"62,500-row blocks from seeds 1000 + block), num_rffs={NMLL_RFFS}, SLQ 25 probes + y, rank-512 "
+                           f"srht_2 preconditioner, CG tol 1e-6",
+               "n_gpus": world, "nmll": float(val), "rows_per_s": args.nmll_rows / secs,
+               "allreduces": int(comm.n_allreduce), "allreduce_bytes": int(comm.bytes_allreduce),
+               "gpu_launches": int(ext.launch_count() - l0),
+               "peak_mem_gb": torch.cuda.max_memory_allocated() / 1e9, "phases_rank0": dict(scoring.LAST_NMLL_INFO)}
+    del x, y, ds
     torch.cuda.empty_cache()
     return rec
 

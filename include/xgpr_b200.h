@@ -241,6 +241,12 @@ int xgpr_b200_atb_accum_f64(const double* a, const double* z, int64_t n, int64_t
 /* w (m, r) += Z^T (Z v) ;  v (m, r) row-major; scratch (n, r) f64 device workspace */
 int xgpr_b200_cg_matvec_accum_f64(const double* z, int64_t n, int64_t m, const double* v, int64_t r,
                                   double* w, double* scratch, void* stream);
+/* The same product from the lossless float32 encoding c of sine-cosine features (xgpr_b200_rbf_feature_gen_c32:
+ * Z[i, j] = double(c[i, j]) * scale; with fit_intercept the caller stores 1.0f in column 0, which then stands for
+ * Z[i, 0] = 1).  vs (m, r) = v with row j multiplied by scale (row 0 left as it is with fit_intercept).  Half the bytes
+ * per feature of the fp64 form for SLQ's 26 right-hand sides (cg_tools.py:42-44 with a matrix `vec`); m % 4 == 0. */
+int xgpr_b200_cg_matvec_accum_c32(const float* c, int64_t n, int64_t m, const double* vs, int64_t r, double* w,
+                                  double* scratch, double scale, int fit_intercept, void* stream);
 /* w (m, r) += Z^T (Z v) with NO caller workspace and no allocation of any kind: the (n, r) intermediate lives in a
  * file-scope device array of xgpr_b200_cg_matvec_static_max_elems() = 1,048,576 doubles (8 MiB, held by every GPU that
  * loads the library until exit).  No counterpart in the reference: added for callers

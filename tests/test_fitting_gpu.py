@@ -207,3 +207,97 @@ def test_fused_matvec_equals_materialised(case, dp):
     else:
         with pytest.raises(RuntimeError):
             k.fused_zzv(xs, v, torch.zeros(m, dtype=torch.float64, device="cuda"))
+
+
+@pytest.mark.parametrize("r", [1, 3, 24, 25, 26, 27, 32, 40, 58])
+@pytest.mark.parametrize("case", [(700, 64, 2048, True), (333, 20, 100, False), (2100, 128, 32768, True)])
+def test_encoded_multi_rhs_matvec_equals_fp64_matvec(case, r):
+    """xgpr_b200_cg_matvec_accum_c32 (DMMA kernels reading the float32 encoding of Z, 26-column tile for SLQ's 25 probes +
+    y) against xgpr_b200_cg_matvec_accum_f64 on transform_x's Z and against NumPy.  Z = double(C) * scale exactly, so the
+    only differences are where the scale is applied and the summation order: rtol 1e-11 of the result's scale."""
+    from xgpr_b200 import ext
+    from xgpr_b200.kernels import RBF
+    n, d, m, icpt = case
+    rng = np.random.default_rng(11)
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    kern = RBF(x.shape, m, random_seed=123, device="cuda")
+    kern.fit_intercept = icpt
+    kern.set_hyperparams(np.log(np.asarray([1.0, 0.3])), logspace=True)
+    assert kern.encoding_ok()
+    z = kern.transform_x(x)
+    c = torch.empty((n, m), dtype=torch.float32, device="cuda")
+    kern.resident_generate(x, c)
+    if icpt:
+        c[:, 0] = 1.0
+    scale = kern.feature_scale()
+    v = torch.from_numpy(rng.standard_normal((m, r))).cuda()
+    vs = v * scale
+    if icpt:
+        vs[0] = v[0]
+    w0 = torch.ones((m, r), dtype=torch.float64, device="cuda")
+    w1 = torch.ones((m, r), dtype=torch.float64, device="cuda")
+    ext.cg_matvec_accum(z, v, w0)
+    ext.cg_matvec_accum_c32(c, vs, w1, scale, icpt)
+    zh = z.cpu().numpy()
+    want = 1.0 + zh.T @ (zh @ v.cpu().numpy())
+    tol = 1e-11 * float(np.abs(want).max())
+    np.testing.assert_allclose(w0.cpu().numpy(), want, rtol=1e-10, atol=tol)
+    np.testing.assert_allclose(w1.cpu().numpy(), want, rtol=1e-10, atol=tol)
+
+
+def test_multi_rhs_tail_tile_equals_full_tile(monkeypatch):
+    """25 / 26 right-hand sides: the 24 + 2 tile (columns 24, 25 on DFMA) against NumPy, fp64 and encoded inputs, with a row
+    count and a feature count that are not multiples of the tile."""
+    from xgpr_b200 import ext
+    rng = np.random.default_rng(12)
+    for n, m, r in ((1000, 520, 26), (130, 4100, 25), (4096, 1024, 26)):
+        z = rng.standard_normal((n, m))
+        v = rng.standard_normal((m, r))
+        want = z.T @ (z @ v)
+        w = torch.zeros((m, r), dtype=torch.float64, device="cuda")
+        ext.cg_matvec_accum(torch.from_numpy(z).cuda(), torch.from_numpy(v).cuda(), w)
+        np.testing.assert_allclose(w.cpu().numpy(), want, rtol=1e-11, atol=1e-11 * float(np.abs(want).max()))
+        if m % 4 == 0:
+            zf = z.astype(np.float32)
+            wantf = 0.25 * (zf.astype(np.float64).T @ (zf.astype(np.float64) @ v))
+            w = torch.zeros((m, r), dtype=torch.float64, device="cuda")
+            ext.cg_matvec_accum_c32(torch.from_numpy(zf).cuda(), torch.from_numpy(v * 0.5).cuda(), w, 0.5, False)
+            np.testing.assert_allclose(w.cpu().numpy(), wantf, rtol=1e-11, atol=1e-11 * float(np.abs(wantf).max()))
+
+
+@pytest.mark.parametrize("kname", ["RBF", "MiniARD"])
+def test_multi_rhs_cg_encoded_chunks_match_fp64_chunks(kname, monkeypatch):
+    """A 26-RHS solve (the shape of approximate_nmll's) through (a) fp64 feature chunks, (b) the float32 encoding with every
+    chunk kept, (c) the encoding with room for only SOME chunks (the others regenerated per iteration), (d) nothing kept."""
+    from xgpr_b200 import fitting
+    from xgpr_b200.kernels import KERNEL_NAME_TO_CLASS
+    rng = np.random.default_rng(3)
+    n, d, m = 3000, 20, 512
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    y = np.sin(x[:, :3].sum(1)) + 0.1 * rng.standard_normal(n)
+    parms = {"split_points": [7]} if kname == "MiniARD" else {}
+    kern = KERNEL_NAME_TO_CLASS[kname](x.shape, m, random_seed=123, device="cuda", kernel_spec_parms=parms)
+    hp = [2.0, 0.4, 0.25] if kname == "MiniARD" else [2.0, 0.4]        # lambda = 2: unpreconditioned CG converges
+    kern.set_hyperparams(np.log(np.asarray(hp)), logspace=True)
+    ds = fitting.build_shard_dataset(x, y, None, chunk_size=250)
+    monkeypatch.setattr(fitting, "_work_rows", lambda kernel, budget_bytes=0, cap=0: 512)     # 6 work chunks
+    rhs = torch.from_numpy(rng.standard_normal((m, 26))).cuda()
+    outs = []
+    for mode in ("f64", "all", "some", "none"):
+        cg = fitting.ConjugateGrad()
+        cg.encoded_multi_rhs = mode != "f64"
+        if mode == "some":                       # room for the work buffer + 3 of the 6 chunks
+            cg.encoded_fraction = (4.5 * 512 * m * 4) / fitting._available_hbm(torch.device("cuda", torch.cuda.current_device()))
+        cg.keep_resident = mode != "none"
+        resid = torch.zeros((m, 2, 26), dtype=torch.float64, device="cuda")
+        resid[:, 0, :] = rhs
+        xk, conv, nit, _ = cg.fit(ds, kern, None, resid, maxiter=300, tol=1e-11, verbose=False)
+        assert conv, (mode, nit)
+        if mode != "f64":
+            kept = len(cg._encoded[1]["kept"])
+            assert kept == {"all": 6, "some": 3, "none": 0}[mode], (mode, kept)
+        outs.append(xk.cpu().numpy())
+    for o in outs[1:]:
+        # converged solutions of the same system: CG amplifies the rounding differences of the two forms by the condition
+        # number, so the bound is on the solution's scale (the north_star weight tolerance is 1e-6)
+        np.testing.assert_allclose(o, outs[0], rtol=0, atol=1e-8 * float(np.abs(outs[0]).max()))

@@ -58,8 +58,10 @@ def test_stream_many_chunks_no_reuse_hazard():
         assert torch.equal(a, b)
 
 
-def test_cg_resident_z_equals_regenerated():
-    """Multi-RHS CG matvec with the shard's Z kept in HBM across iterations == regenerating Z per iteration."""
+@pytest.mark.parametrize("encoded", [False, True])
+def test_cg_resident_z_equals_regenerated(encoded):
+    """Multi-RHS CG matvec with the shard's features kept in HBM across iterations == regenerating them per iteration, for
+    the fp64 chunks and for the float32 encoding (the default for float32-FHT kernels)."""
     from xgpr_b200 import fitting
     from xgpr_b200.kernels import RBF
     rng = np.random.default_rng(3)
@@ -73,10 +75,14 @@ def test_cg_resident_z_equals_regenerated():
     for keep in (True, False):
         cg = fitting.ConjugateGrad()
         cg.keep_resident = keep
+        cg.encoded_multi_rhs = encoded
         w = torch.zeros_like(vec)
         for _ in range(3):                              # second and third calls use the resident copy
             cg._matvec(ds, kern, vec, w)
-        assert (cg._resident is not None) == keep
+        if encoded:
+            assert cg._resident is None and (len(cg._encoded[1]["kept"]) > 0) == keep
+        else:
+            assert cg._encoded is None and (cg._resident is not None) == keep
         outs.append(w.clone())
     # same Z, same kernels; only the fp64 atomics' order differs between runs
     assert float((outs[0] - outs[1]).abs().max()) <= 1e-12 * float(outs[0].abs().max())

@@ -77,7 +77,8 @@ def main():
                           f"tol {args.tol}", "n_gpus": world, "rows": args.rows, "nmll": val,
                           "seconds": float(t[0]) * 1e-3, "rows_per_s": args.rows / (float(t[0]) * 1e-3),
                           "allreduces": comm.n_allreduce, "gpu_launches": ext.launch_count() - l0,
-                          "peak_mem_gb": torch.cuda.max_memory_allocated() / 1e9, "scaling": "strong"}), flush=True)
+                          "peak_mem_gb": torch.cuda.max_memory_allocated() / 1e9, "scaling": "strong",
+                          "phases_rank0": dict(scoring.LAST_NMLL_INFO)}), flush=True)
     if world > 1:
         dist.destroy_process_group()
 

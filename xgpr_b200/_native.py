@@ -60,6 +60,9 @@ for _name, _args in F64_ONLY.items():
     _fn.restype = _int
     EXPORTED.append(_name)
 
+lib.xgpr_b200_cg_matvec_accum_c32.argtypes = [_ptr, _i64, _i64, _ptr, _i64, _ptr, _ptr, _dbl, _int, _ptr]
+lib.xgpr_b200_cg_matvec_accum_c32.restype = _int
+EXPORTED.append("xgpr_b200_cg_matvec_accum_c32")
 lib.xgpr_b200_cg_matvec_static_max_elems.argtypes = []
 lib.xgpr_b200_cg_matvec_static_max_elems.restype = _i64
 EXPORTED.append("xgpr_b200_cg_matvec_static_max_elems")

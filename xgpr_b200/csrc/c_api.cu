@@ -113,6 +113,8 @@ int ztzq_accum_tc(const double* z, int64_t n, int64_t m, const double* q, int64_
                   int digit_bits, void* workspace, int64_t workspace_bytes, cudaStream_t st);
 int cg_matvec_accum(const double* z, int64_t n, int64_t m, const double* v, int64_t r, double* w,
                     double* scratch, cudaStream_t st);
+int cg_matvec_accum_c32(const float* c, int64_t n, int64_t m, const double* vs, int64_t r, double* w, double* scratch,
+                        double scale, int fit_intercept, cudaStream_t st);
 int64_t cg_matvec_static_max_elems();
 int cg_matvec_accum_static(const double* z, int64_t n, int64_t m, const double* v, int64_t r, double* w, cudaStream_t st);
 
@@ -289,6 +291,10 @@ int xgpr_b200_atb_accum_f64(const double* a, const double* b, int64_t n, int64_t
 int xgpr_b200_cg_matvec_accum_f64(const double* z, int64_t n, int64_t m, const double* v, int64_t r, double* w, double* scratch,
                                   void* s) {
     return cg_matvec_accum(z, n, m, v, r, w, scratch, ST(s));
+}
+int xgpr_b200_cg_matvec_accum_c32(const float* c, int64_t n, int64_t m, const double* vs, int64_t r, double* w,
+                                  double* scratch, double scale, int fit_intercept, void* s) {
+    return cg_matvec_accum_c32(c, n, m, vs, r, w, scratch, scale, fit_intercept, ST(s));
 }
 int64_t xgpr_b200_cg_matvec_static_max_elems(void) { return cg_matvec_static_max_elems(); }
 int xgpr_b200_cg_matvec_accum_static_f64(const double* z, int64_t n, int64_t m, const double* v, int64_t r, double* w, void* s) {

@@ -559,29 +559,57 @@ __device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
 }
 
 // fragment coordinates (PTX ISA, m8n8k4 .f64): g = lane >> 2, t = lane & 3;  A[g][t], B[t][g], C[g][2t], C[g][2t+1]
+//
+// ZT = double: Z itself.  ZT = float: the lossless float32 encoding C of sine-cosine features (Z = double(C) * scale, column
+// 0 = 1 with an intercept, written into C by the caller): half the bytes per feature, widened after the LDS (one F2F per A
+// element against 3 - 4 DMMAs: 3 % of the issue slots).  The float tiles keep the conflict-free strides: row stride == 4
+// words (mod 32) for the row-major tile, == 8 words for the [k][column] tile.
+// TAIL (24 < rcount <= 26, SLQ's 25 probes + y): column fragments 0..2 on DMMA, columns 24 and 25 as two DFMAs per A element
+// with per-lane partial sums over k = t (mod 4), reduced over the four t lanes at the end -- 12 DMMA + 8 DFMA instead of
+// 16 DMMA per k4 step, i.e. 52 instead of 64 units of fp64-pipe work.
+template <typename ZT> struct m3_tile {
+    static constexpr int ZV_LD = sizeof(ZT) == 8 ? M3_ZV_LD : M3_KC + 4;          // 20 doubles | 20 floats
+    static constexpr int ZT_LD = M3_ZT_LD;                                        // 136 doubles | 136 floats
+    static constexpr int PER16 = 16 / sizeof(ZT);                                 // elements per 16-byte piece
+    // doubles per stage (the ZT tile rounded up to whole doubles) for the two kernels
+    static constexpr int ZV_A = (M2_ROWS * ZV_LD * (int)sizeof(ZT) + 7) / 8;
+    static constexpr int ZT_A = (M3_KC * ZT_LD * (int)sizeof(ZT) + 7) / 8;
+    static constexpr int ZV_STAGE = ZV_A + M3_KC * M3_B_LD;
+    static constexpr int ZT_STAGE = ZT_A + M3_KC * M3_B_LD;
+    static constexpr int ZV_SMEM = 2 * ZV_STAGE * 8, ZT_SMEM = 2 * ZT_STAGE * 8;
+};
+static_assert(m3_tile<double>::ZV_SMEM == M3_ZV_SMEM && m3_tile<double>::ZT_SMEM == M3_ZT_SMEM, "fp64 tile sizes");
+
+template <typename ZT, bool TAIL>
 __global__ void __launch_bounds__(128, 4)
-zv_mma_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double* __restrict__ v, int64_t ldv,
+zv_mma_kernel(const ZT* __restrict__ z, int64_t n, int64_t m, const double* __restrict__ v, int64_t ldv,
               int r0, int rcount, double* __restrict__ tt, int64_t ldt, int64_t k_per, int atomic_out) {
+    using TL = m3_tile<ZT>;
+    constexpr int NB = TAIL ? 3 : 4;
+    constexpr int PER16 = TL::PER16;
     extern __shared__ __align__(16) double m2_smem[];
     const int64_t row0 = (int64_t)blockIdx.x * M2_ROWS;
     const int64_t kbeg = (int64_t)blockIdx.y * k_per;
     const int64_t kend = (kbeg + k_per < m) ? kbeg + k_per : m;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
-    double acc[4][4][2];
+    double acc[4][NB][2];
+    double tl[4][2];
 #pragma unroll
-    for (int a = 0; a < 4; ++a)
+    for (int a = 0; a < 4; ++a) {
 #pragma unroll
-        for (int b = 0; b < 4; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+        for (int b = 0; b < NB; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+        tl[a][0] = tl[a][1] = 0.0;
+    }
     auto load = [&](int stage, int64_t k0) {
-        double* zs = m2_smem + stage * M3_ZV_STAGE;
-        double* vs = zs + M2_ROWS * M3_ZV_LD;
+        ZT* zs = reinterpret_cast<ZT*>(m2_smem + stage * TL::ZV_STAGE);
+        double* vs = m2_smem + stage * TL::ZV_STAGE + TL::ZV_A;
 #pragma unroll
-        for (int i = 0; i < M3_KC / 2; ++i) {                    // 128 rows x 8 pieces of 16 bytes
+        for (int i = 0; i < M3_KC / PER16; ++i) {                // 128 rows x (KC / PER16) pieces of 16 bytes
             const int p = i * 128 + threadIdx.x;
-            const int rr = p / (M3_KC / 2), j = p % (M3_KC / 2);
-            const int64_t row = row0 + rr, k = k0 + 2 * j;
+            const int rr = p / (M3_KC / PER16), j = p % (M3_KC / PER16);
+            const int64_t row = row0 + rr, k = k0 + PER16 * j;
             const bool ok = row < n && k < kend;
-            cp_async16(zs + rr * M3_ZV_LD + 2 * j, ok ? z + row * m + k : z, ok);
+            cp_async16(zs + rr * TL::ZV_LD + PER16 * j, ok ? z + row * m + k : z, ok);
         }
 #pragma unroll
         for (int i = 0; i < M3_KC / 4; ++i) {
@@ -600,29 +628,46 @@ zv_mma_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double* 
         cp_async_commit();
         cp_async_wait<1>();
         __syncthreads();
-        const double* zs = m2_smem + s * M3_ZV_STAGE + (warp * 32 + g) * M3_ZV_LD + t;
-        const double* vs = m2_smem + s * M3_ZV_STAGE + M2_ROWS * M3_ZV_LD + t * M3_B_LD + g;
+        const ZT* zs = reinterpret_cast<const ZT*>(m2_smem + s * TL::ZV_STAGE) + (warp * 32 + g) * TL::ZV_LD + t;
+        const double* vs = m2_smem + s * TL::ZV_STAGE + TL::ZV_A + t * M3_B_LD;
 #pragma unroll
         for (int k4 = 0; k4 < M3_KC / 4; ++k4) {
-            double fa[4], fb[4];
+            double fa[4], fb[NB];
 #pragma unroll
-            for (int a = 0; a < 4; ++a) fa[a] = zs[a * 8 * M3_ZV_LD + 4 * k4];
+            for (int a = 0; a < 4; ++a) fa[a] = (double)zs[a * 8 * TL::ZV_LD + 4 * k4];
 #pragma unroll
-            for (int b = 0; b < 4; ++b) fb[b] = vs[4 * k4 * M3_B_LD + 8 * b];
+            for (int b = 0; b < NB; ++b) fb[b] = vs[4 * k4 * M3_B_LD + 8 * b + g];
 #pragma unroll
             for (int a = 0; a < 4; ++a)
 #pragma unroll
-                for (int b = 0; b < 4; ++b) dmma884(acc[a][b], fa[a], fb[b]);
+                for (int b = 0; b < NB; ++b) dmma884(acc[a][b], fa[a], fb[b]);
+            if (TAIL) {
+                const double2 vt = *reinterpret_cast<const double2*>(vs + 4 * k4 * M3_B_LD + 24);
+#pragma unroll
+                for (int a = 0; a < 4; ++a) {
+                    tl[a][0] = fma(fa[a], vt.x, tl[a][0]);
+                    tl[a][1] = fma(fa[a], vt.y, tl[a][1]);
+                }
+            }
         }
         __syncthreads();
     }
     cp_async_wait<0>();
+    if (TAIL) {
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                tl[a][e] += __shfl_xor_sync(0xffffffffu, tl[a][e], 1);
+                tl[a][e] += __shfl_xor_sync(0xffffffffu, tl[a][e], 2);
+            }
+    }
 #pragma unroll
     for (int a = 0; a < 4; ++a) {
         const int64_t row = row0 + warp * 32 + a * 8 + g;
         if (row >= n) continue;
 #pragma unroll
-        for (int b = 0; b < 4; ++b)
+        for (int b = 0; b < NB; ++b)
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
                 const int cc = b * 8 + 2 * t + e;
@@ -631,32 +676,49 @@ zv_mma_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double* 
                 if (atomic_out) atomicAdd(dst, acc[a][b][e]);
                 else *dst = acc[a][b][e];
             }
+        if (TAIL && t < 2 && 24 + t < rcount) {                  // lane t = 0 / 1 writes column 24 / 25
+            double* dst = tt + row * ldt + r0 + 24 + t;
+            const double val = t == 0 ? tl[a][0] : tl[a][1];
+            if (atomic_out) atomicAdd(dst, val);
+            else *dst = val;
+        }
     }
 }
 
+// w (m, r) += diag(s) Z'^T T: out_scale / icpt describe s for the float32 encoding (s_j = out_scale, s_0 = 1 with an
+// intercept); the fp64 instantiation ignores them.
+template <typename ZT, bool TAIL>
 __global__ void __launch_bounds__(128, 4)
-ztt_mma_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double* __restrict__ tt, int64_t ldt,
-               int r0, int rcount, double* __restrict__ w, int64_t ldw, int64_t k_per) {
+ztt_mma_kernel(const ZT* __restrict__ z, int64_t n, int64_t m, const double* __restrict__ tt, int64_t ldt,
+               int r0, int rcount, double* __restrict__ w, int64_t ldw, int64_t k_per, double out_scale, int icpt) {
+    using TL = m3_tile<ZT>;
+    constexpr int NB = TAIL ? 3 : 4;
+    constexpr int PER16 = TL::PER16;
+    constexpr bool ENC = sizeof(ZT) == 4;
     extern __shared__ __align__(16) double m2_smem[];
     const int64_t c0 = (int64_t)blockIdx.x * M2_ROWS;
     const int64_t kbeg = (int64_t)blockIdx.y * k_per;
     const int64_t kend = (kbeg + k_per < n) ? kbeg + k_per : n;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
-    double acc[4][4][2];
+    double acc[4][NB][2];
+    double tl[4][2];
 #pragma unroll
-    for (int a = 0; a < 4; ++a)
+    for (int a = 0; a < 4; ++a) {
 #pragma unroll
-        for (int b = 0; b < 4; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+        for (int b = 0; b < NB; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+        tl[a][0] = tl[a][1] = 0.0;
+    }
     auto load = [&](int stage, int64_t k0) {
-        double* zs = m2_smem + stage * M3_ZT_STAGE;
-        double* ts = zs + M3_KC * M3_ZT_LD;
+        ZT* zs = reinterpret_cast<ZT*>(m2_smem + stage * TL::ZT_STAGE);
+        double* ts = m2_smem + stage * TL::ZT_STAGE + TL::ZT_A;
+        constexpr int PPR = M2_ROWS / PER16;                     // 16-byte pieces per k row
 #pragma unroll
-        for (int i = 0; i < M3_KC / 2; ++i) {                    // 16 rows x 64 pieces of 16 bytes
+        for (int i = 0; i < M3_KC * PPR / 128; ++i) {
             const int p = i * 128 + threadIdx.x;
-            const int kk = p >> 6, j = p & 63;
-            const int64_t row = k0 + kk, col = c0 + 2 * j;
+            const int kk = p / PPR, j = p % PPR;
+            const int64_t row = k0 + kk, col = c0 + PER16 * j;
             const bool ok = row < kend && col < m;
-            cp_async16(zs + kk * M3_ZT_LD + 2 * j, ok ? z + row * m + col : z, ok);
+            cp_async16(zs + kk * TL::ZT_LD + PER16 * j, ok ? z + row * m + col : z, ok);
         }
 #pragma unroll
         for (int i = 0; i < M3_KC / 4; ++i) {
@@ -675,38 +737,64 @@ ztt_mma_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double*
         cp_async_commit();
         cp_async_wait<1>();
         __syncthreads();
-        const double* zs = m2_smem + s * M3_ZT_STAGE + t * M3_ZT_LD + warp * 32 + g;
-        const double* ts = m2_smem + s * M3_ZT_STAGE + M3_KC * M3_ZT_LD + t * M3_B_LD + g;
+        const ZT* zs = reinterpret_cast<const ZT*>(m2_smem + s * TL::ZT_STAGE) + t * TL::ZT_LD + warp * 32 + g;
+        const double* ts = m2_smem + s * TL::ZT_STAGE + TL::ZT_A + t * M3_B_LD;
 #pragma unroll
         for (int k4 = 0; k4 < M3_KC / 4; ++k4) {
-            double fa[4], fb[4];
+            double fa[4], fb[NB];
 #pragma unroll
-            for (int a = 0; a < 4; ++a) fa[a] = zs[4 * k4 * M3_ZT_LD + 8 * a];
+            for (int a = 0; a < 4; ++a) fa[a] = (double)zs[4 * k4 * TL::ZT_LD + 8 * a];
 #pragma unroll
-            for (int b = 0; b < 4; ++b) fb[b] = ts[4 * k4 * M3_B_LD + 8 * b];
+            for (int b = 0; b < NB; ++b) fb[b] = ts[4 * k4 * M3_B_LD + 8 * b + g];
 #pragma unroll
             for (int a = 0; a < 4; ++a)
 #pragma unroll
-                for (int b = 0; b < 4; ++b) dmma884(acc[a][b], fa[a], fb[b]);
+                for (int b = 0; b < NB; ++b) dmma884(acc[a][b], fa[a], fb[b]);
+            if (TAIL) {
+                const double2 vt = *reinterpret_cast<const double2*>(ts + 4 * k4 * M3_B_LD + 24);
+#pragma unroll
+                for (int a = 0; a < 4; ++a) {
+                    tl[a][0] = fma(fa[a], vt.x, tl[a][0]);
+                    tl[a][1] = fma(fa[a], vt.y, tl[a][1]);
+                }
+            }
         }
         __syncthreads();
     }
     cp_async_wait<0>();
+    if (TAIL) {
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                tl[a][e] += __shfl_xor_sync(0xffffffffu, tl[a][e], 1);
+                tl[a][e] += __shfl_xor_sync(0xffffffffu, tl[a][e], 2);
+            }
+    }
     const bool atomic_out = gridDim.y > 1;
 #pragma unroll
     for (int a = 0; a < 4; ++a) {
         const int64_t col = c0 + warp * 32 + a * 8 + g;
         if (col >= m) continue;
+        const double sc = ENC ? ((icpt && col == 0) ? 1.0 : out_scale) : 1.0;
 #pragma unroll
-        for (int b = 0; b < 4; ++b)
+        for (int b = 0; b < NB; ++b)
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
                 const int cc = b * 8 + 2 * t + e;
                 if (cc >= rcount) continue;
                 double* dst = w + col * ldw + r0 + cc;
-                if (atomic_out) atomicAdd(dst, acc[a][b][e]);
-                else *dst += acc[a][b][e];
+                const double val = ENC ? acc[a][b][e] * sc : acc[a][b][e];
+                if (atomic_out) atomicAdd(dst, val);
+                else *dst += val;
             }
+        if (TAIL && t < 2 && 24 + t < rcount) {
+            double* dst = w + col * ldw + r0 + 24 + t;
+            double val = t == 0 ? tl[a][0] : tl[a][1];
+            if (ENC) val *= sc;
+            if (atomic_out) atomicAdd(dst, val);
+            else *dst += val;
+        }
     }
 }
 
@@ -771,6 +859,32 @@ int ztz_accum(const double* z, int64_t n, int64_t m, double* ztz, cudaStream_t s
     return check_launch("ztz_kernel");
 }
 
+// The DMMA pair over one block of right-hand sides, Z given as fp64 or as its float32 encoding.  XGPR_B200_MATVEC_NOTAIL
+// keeps 25 / 26 columns on the 32-column tile (A/B switch).
+template <typename ZT>
+static void launch_mma_pair(const ZT* z, int64_t n, int64_t m, const double* v, int64_t r, double* w, double* scratch,
+                            int r0, int rc, dim3 gz, dim3 gt, int64_t kz, int64_t kt, int atomic_t, double out_scale,
+                            int icpt, cudaStream_t st) {
+    using TL = m3_tile<ZT>;
+    static const bool notail = getenv("XGPR_B200_MATVEC_NOTAIL") != nullptr;
+    if (rc > 24 && rc <= 26 && !notail) {
+        zv_mma_kernel<ZT, true><<<gz, 128, TL::ZV_SMEM, st>>>(z, n, m, v, r, r0, rc, scratch, r, kz, atomic_t);
+        ztt_mma_kernel<ZT, true><<<gt, 128, TL::ZT_SMEM, st>>>(z, n, m, scratch, r, r0, rc, w, r, kt, out_scale, icpt);
+    } else {
+        zv_mma_kernel<ZT, false><<<gz, 128, TL::ZV_SMEM, st>>>(z, n, m, v, r, r0, rc, scratch, r, kz, atomic_t);
+        ztt_mma_kernel<ZT, false><<<gt, 128, TL::ZT_SMEM, st>>>(z, n, m, scratch, r, r0, rc, w, r, kt, out_scale, icpt);
+    }
+}
+
+template <typename ZT>
+static void mma_pair_attrs() {
+    using TL = m3_tile<ZT>;
+    cudaFuncSetAttribute(zv_mma_kernel<ZT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::ZV_SMEM);
+    cudaFuncSetAttribute(ztt_mma_kernel<ZT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::ZT_SMEM);
+    cudaFuncSetAttribute(zv_mma_kernel<ZT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::ZV_SMEM);
+    cudaFuncSetAttribute(ztt_mma_kernel<ZT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TL::ZT_SMEM);
+}
+
 int cg_matvec_accum(const double* z, int64_t n, int64_t m, const double* v, int64_t r, double* w,
                     double* scratch, cudaStream_t st) {
     XB_REQUIRE(n > 0 && m > 0 && r > 0, "no datapoints");
@@ -802,8 +916,7 @@ int cg_matvec_accum(const double* z, int64_t n, int64_t m, const double* v, int6
         if (!attr_done) {
             cudaFuncSetAttribute(zv_tile2_kernel<16, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ZV16);
             cudaFuncSetAttribute(ztt_tile2_kernel<16, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, ZT16);
-            cudaFuncSetAttribute(zv_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, M3_ZV_SMEM);
-            cudaFuncSetAttribute(ztt_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, M3_ZT_SMEM);
+            mma_pair_attrs<double>();
             attr_done = true;
         }
         const int64_t slots = 148 * (dfma ? 3 : 4);
@@ -818,8 +931,7 @@ int cg_matvec_accum(const double* z, int64_t n, int64_t m, const double* v, int6
                 zv_tile2_kernel<16, 3><<<gz, 128, ZV16, st>>>(z, n, m, v, r, r0, rc, scratch, r, kz, sz > 1 ? 1 : 0);
                 ztt_tile2_kernel<16, 3><<<gt, 128, ZT16, st>>>(z, n, m, scratch, r, r0, rc, w, r, kt);
             } else {
-                zv_mma_kernel<<<gz, 128, M3_ZV_SMEM, st>>>(z, n, m, v, r, r0, rc, scratch, r, kz, sz > 1 ? 1 : 0);
-                ztt_mma_kernel<<<gt, 128, M3_ZT_SMEM, st>>>(z, n, m, scratch, r, r0, rc, w, r, kt);
+                launch_mma_pair<double>(z, n, m, v, r, w, scratch, r0, rc, gz, gt, kz, kt, sz > 1 ? 1 : 0, 1.0, 0, st);
             }
             count_launch(2);
         }
@@ -832,6 +944,40 @@ int cg_matvec_accum(const double* z, int64_t n, int64_t m, const double* v, int6
         count_launch(2);
     }
     return check_launch("cg_matvec");
+}
+
+// w (m, r) += Z^T (Z v) from the float32 encoding: Z[i, j] = double(c[i, j]) * scale, and with fit_intercept column 0 of
+// c holds 1.0f and stands for Z[i, 0] = 1 (the caller writes it).  vs = v with its rows scaled the same way (vs[j, :] =
+// v[j, :] * scale, vs[0, :] = v[0, :]): then T = c vs = Z v, and w += diag(s) c^T T = Z^T T.  Any r >= 1.
+int cg_matvec_accum_c32(const float* c, int64_t n, int64_t m, const double* vs, int64_t r, double* w, double* scratch,
+                        double scale, int fit_intercept, cudaStream_t st) {
+    XB_REQUIRE(n > 0 && m > 0 && r > 0, "no datapoints");
+    XB_REQUIRE(c && vs && w && scratch, "null pointer");
+    XB_REQUIRE(m % 4 == 0, "float32 encoding: the number of features must be a multiple of 4");
+    XB_REQUIRE(reinterpret_cast<uintptr_t>(c) % 16 == 0, "float32 encoding must be 16-byte aligned");
+    XB_REQUIRE(scale > 0.0, "scale must be positive");
+    static bool attr_done_dev[64] = {};
+    static std::mutex mu;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        bool& attr_done = attr_done_dev[current_device() & 63];
+        if (!attr_done) {
+            mma_pair_attrs<float>();
+            attr_done = true;
+        }
+    }
+    const int64_t slots = 148 * 4;
+    const int64_t rt = (n + M2_ROWS - 1) / M2_ROWS, ct = (m + M2_ROWS - 1) / M2_ROWS;
+    const int64_t kz = m2_k_per(rt, m, slots), kt = m2_k_per(ct, n, slots);
+    const unsigned sz = (unsigned)((m + kz - 1) / kz), stt = (unsigned)((n + kt - 1) / kt);
+    if (sz > 1) cudaMemsetAsync(scratch, 0, sizeof(double) * (size_t)n * (size_t)r, st);
+    const dim3 gz((unsigned)rt, sz), gt((unsigned)ct, stt);
+    for (int r0 = 0; r0 < r; r0 += M2_COLS) {
+        const int rc = (int)((r - r0 < M2_COLS) ? (r - r0) : M2_COLS);
+        launch_mma_pair<float>(c, n, m, vs, r, w, scratch, r0, rc, gz, gt, kz, kt, sz > 1 ? 1 : 0, scale, fit_intercept, st);
+        count_launch(2);
+    }
+    return check_launch("cg_matvec_c32");
 }
 
 // ---- allocation-free variant (no counterpart in the reference) ----------

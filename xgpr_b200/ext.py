@@ -474,4 +474,22 @@ def cg_matvec_accum(z, v, w, scratch=None):
                                             w.data_ptr(), scratch.data_ptr(), _stream()))
 
 
+def cg_matvec_accum_c32(c, vs, w, scale, fit_intercept, scratch=None):
+    """w (m, r) += Z^T (Z v) from the float32 encoding c of Z (Z = double(c) * scale; column 0 of c holds 1.0f with an
+    intercept); vs = v with rows scaled like Z's columns.  See include/xgpr_b200.h."""
+    c = _dev(c, "c", (torch.float32,), 2)
+    vs = _dev(vs, "vs", (torch.float64,), 2)
+    w = _dev(w, "w", (torch.float64,), 2)
+    if vs.shape[0] != c.shape[1] or w.shape != vs.shape:
+        raise RuntimeError("wrong array sizes")
+    if scratch is None:
+        scratch = torch.empty((c.shape[0], vs.shape[1]), dtype=torch.float64, device=c.device)
+    scratch = _dev(scratch, "scratch", (torch.float64,), 2)
+    if scratch.shape[0] < c.shape[0] or scratch.shape[1] != vs.shape[1]:
+        raise RuntimeError("wrong array sizes")
+    check(lib.xgpr_b200_cg_matvec_accum_c32(c.data_ptr(), c.shape[0], c.shape[1], vs.data_ptr(), vs.shape[1],
+                                            w.data_ptr(), scratch.data_ptr(), float(scale), int(bool(fit_intercept)),
+                                            _stream()))
+
+
 launch_count = _native.launch_count

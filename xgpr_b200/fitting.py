@@ -345,7 +345,11 @@ class ConjugateGrad:
         self._staged = None
         self._resident = None
         self._resident_c = None
+        self._encoded = None
         self.keep_resident = True
+        # several right-hand sides: stream the float32 encoding of Z (4 bytes per feature) instead of fp64 Z
+        self.encoded_multi_rhs = os.environ.get("XGPR_B200_MULTIRHS_F64", "0") == "0"
+        self.encoded_fraction = 0.75             # share of the free HBM the kept chunks of the encoding may take
         self.one_pass = True
         # one right-hand side on the GPU: scalar recurrences on the device, no per-iteration host sync (_fit_device)
         self.device_cg = os.environ.get("XGPR_B200_DEVICE_CG", "1") != "0"
@@ -403,11 +407,22 @@ class ConjugateGrad:
             self.comm.all_reduce_(matvec)
             matvec.add_(vec, alpha=kernel.get_lambda() ** 2)
             return
-        for z in self._feature_chunks(dataset, kernel):
+        encoded = (self.encoded_multi_rhs and self.ops is _cuda_ops and kernel.device == "cuda"
+                   and getattr(kernel, "encoding_ok", lambda: False)())
+        if encoded:
+            # Z = double(C) * scale exactly (column 0 = 1 with an intercept): C v_s with v_s = diag(s) v, then diag(s) C^T t
+            scale = kernel.feature_scale()
+            vs = vec * scale
+            if kernel.fit_intercept:
+                vs[0] = vec[0]
+        for z in (self._encoded_chunks(dataset, kernel) if encoded else self._feature_chunks(dataset, kernel)):
             if self._scratch is None or self._scratch.shape[0] < z.shape[0] or self._scratch.shape[1] != vec.shape[1] \
                     or self._scratch.device != z.device:
                 self._scratch = torch.empty((z.shape[0], vec.shape[1]), dtype=torch.float64, device=z.device)
-            self.ops.cg_matvec_accum(z, vec, matvec, self._scratch)
+            if encoded:
+                self.ops.cg_matvec_accum_c32(z, vs, matvec, scale, kernel.fit_intercept, self._scratch)
+            else:
+                self.ops.cg_matvec_accum(z, vec, matvec, self._scratch)
         self.comm.all_reduce_(matvec)
         matvec.add_(vec, alpha=kernel.get_lambda() ** 2)
 
@@ -469,6 +484,45 @@ class ConjugateGrad:
             yield z
         if keep is not None:
             self._resident = (key, keep)
+
+    def _encoded_chunks(self, dataset, kernel):
+        """The shard's features for the multi-RHS matvec as chunks of the float32 encoding C (4 M bytes per row, half of
+        fp64 Z; lossless for the float32-FHT kernels).  C does not change during a solve: the first pass keeps every
+        chunk it can within `fraction` of the free HBM (cfg5 on one GPU: 2M x 32,768 = 262 GB, so about half the rows
+        stay; on 8 GPUs all of them), the others are regenerated per iteration into one reusable buffer."""
+        key = (_token(dataset), _token(kernel), tuple(np.asarray(kernel.get_hyperparams(logspace=False)).tolist()))
+        if self._encoded is None or self._encoded[0] != key:
+            self._encoded = None
+            dev = _device_of(kernel)
+            row_bytes = kernel.get_num_rffs() * 4
+            work_bytes = min(_work_rows(kernel), dataset.get_local_ndatapoints()) * row_bytes
+            budget = self.encoded_fraction * _available_hbm(dev) - work_bytes if self.keep_resident else 0
+            self._encoded = (key, {"kept": {}, "budget": budget, "work": None})
+        state = self._encoded[1]
+        m = kernel.get_num_rffs()
+        for idx, (xdata, _) in enumerate(_x_chunks(dataset, kernel)):
+            c = state["kept"].get(idx)
+            if c is not None:
+                yield c
+                continue
+            rows = xdata.shape[0]
+            out = None
+            if state["budget"] >= rows * m * 4:
+                try:
+                    out = torch.empty((rows, m), dtype=torch.float32, device=_device_of(kernel))
+                    state["kept"][idx] = out
+                    state["budget"] -= rows * m * 4
+                except torch.cuda.OutOfMemoryError:              # fragmented pool: stop keeping chunks
+                    state["budget"] = 0
+            if out is None:
+                work = state["work"]
+                if work is None or work.shape[0] < rows:
+                    state["work"] = work = torch.empty((rows, m), dtype=torch.float32, device=_device_of(kernel))
+                out = work[:rows]
+            kernel.resident_generate(xdata, out)
+            if kernel.fit_intercept:
+                out[:, 0] = 1.0
+            yield out
 
     def prepare_async(self, dataset, kernel):
         """Start building the resident float32 encoding of the shard's features on a SIDE stream and return at once.

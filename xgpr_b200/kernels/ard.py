@@ -79,6 +79,22 @@ class MiniARD(KernelBaseclass):
         ext.cudaRBFFeatureGen(xtrans, output_x, self.radem_diag, self.chi_arr, self.fit_intercept)
         return output_x
 
+    # ---- float32 encoding of Z for the multi-RHS matvec (xgpr_b200 extension, as SORFKernelBaseclass.resident_generate)
+    def feature_scale(self):
+        f = float(self.num_freqs)
+        s = np.sqrt(1.0 / (f - 0.5)) if self.fit_intercept else np.sqrt(1.0 / f)
+        return float(s if self.double_precision else np.float32(s))
+
+    def encoding_ok(self):
+        return (not self.double_precision) and self._xdim[-1] <= 1024 and self.num_rffs % 4 == 0
+
+    def resident_generate(self, input_x, out):
+        """out (float32, rows x num_rffs) <- the unscaled cos / sin values of transform_x(input_x)."""
+        xin = self._stage_input(input_x)
+        xtrans = ext.scale_input_(xin, col_weights=self.full_ard_weights)
+        ext.cudaRBFFeatureGenC32(xtrans, out, self.radem_diag, self.chi_arr)
+        return out
+
     def precompute_weights(self):
         """W (F, D) = rows of chi * (H D3 H D2 H D1) restricted to the first D inputs (mini_ard.py:208-258)."""
         if self.device != "cuda":

@@ -93,6 +93,10 @@ class SORFKernelBaseclass(KernelBaseclass):
     def resident_ok(self):
         return (not self.double_precision) and ext.cres_zzv_supported(self.num_rffs)
 
+    def encoding_ok(self):
+        """resident_generate / feature_scale describe Z exactly (float32 FHT, <= 1024 inputs, 16-byte rows)."""
+        return (not self.double_precision) and self._xdim[-1] <= 1024 and self.num_rffs % 4 == 0
+
     def resident_encode(self, z, out):
         """out (float32) <- the unscaled cos / sin values of the feature chunk z: lossless, since z = double(c) * scale."""
         return ext.unscale_to_f32(z, self.feature_scale(), out)

@@ -264,6 +264,10 @@ def autoselect_preconditioner(dataset, kernel, min_rank=512, max_rank=3000, incr
     return fitting.RandNysPreconditioner(kernel, dataset, rank, False, random_seed, method, comm, ops, compressor_cls)
 
 
+# phases of the last approximate_nmll call on this process (device time, CUDA events): for bench.py / tools
+LAST_NMLL_INFO = {}
+
+
 def approximate_nmll(hyperparams, dataset, kernel, manual_settings=None, random_seed=123, comm=None, ops=_cuda_ops,
                      compressor_cls=None):
     """xgp_regression.py:264-377: preconditioned CG on nsamples + 1 right-hand sides (Z^T y / N and the probes), log det by
@@ -272,6 +276,10 @@ def approximate_nmll(hyperparams, dataset, kernel, manual_settings=None, random_
     kernel.set_hyperparams(hyperparams, logspace=True)
     settings = dict(DEFAULT_NMLL_PARAMS)
     m = kernel.get_num_rffs()
+    timed = kernel.device == "cuda" and torch.cuda.is_available()
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if timed else None
+    if timed:
+        marks[0].record()
     if manual_settings is not None:
         for key in settings:
             if key in manual_settings:
@@ -286,6 +294,8 @@ def approximate_nmll(hyperparams, dataset, kernel, manual_settings=None, random_
                                                    compressor_cls=compressor_cls)
     z_trans_y, y_trans_y = preconditioner.get_zty(), preconditioner.get_yty()
     dev = z_trans_y.device
+    if timed:
+        marks[1].record()
     resid = torch.zeros((m, 2, settings["nsamples"] + 1), dtype=torch.float64, device=dev)
     resid[:, 0, 0] = z_trans_y / dataset.get_ndatapoints()
     resid[:, 0, 1:] = generate_normal_probes(settings["nsamples"], m, random_seed, preconditioner, dev)
@@ -293,6 +303,16 @@ def approximate_nmll(hyperparams, dataset, kernel, manual_settings=None, random_
     x_k, alphas, betas = cg_operator.fit(dataset, kernel, preconditioner, resid, settings["nmll_iter"],
                                          settings["nmll_tol"], verbose=False, nmll_settings=True)
     x_k[:, 0] *= dataset.get_ndatapoints()
+    if timed:
+        marks[2].record()
+        marks[2].synchronize()
+        enc = cg_operator._encoded[1] if getattr(cg_operator, "_encoded", None) else None
+        LAST_NMLL_INFO.clear()
+        LAST_NMLL_INFO.update({"precond_s": marks[0].elapsed_time(marks[1]) * 1e-3,
+                               "cg_s": marks[1].elapsed_time(marks[2]) * 1e-3, "cg_iters": int(alphas.shape[0]),
+                               "rhs": int(resid.shape[2]),
+                               "encoded_rows_kept": None if enc is None else int(sum(c.shape[0] for c in enc["kept"].values())),
+                               "rows_local": int(dataset.get_local_ndatapoints())})
     logdet = estimate_logdet(alphas, betas, m, preconditioner)
     nll1 = float(0.5 * (y_trans_y - z_trans_y @ x_k[:, 0]))
     negloglik, _ = optimize_alpha_beta(kernel.get_lambda(), np.array([nll1, 0.5 * logdet]),
