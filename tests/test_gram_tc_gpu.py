@@ -5,6 +5,8 @@ Bars, stated per test: inputs that are exactly representable in the digit planes
 |error| <= n * 2^(-7 s + 2) * colmax_i * colmax_j for s planes (6 planes: ~1e-12 of the column scale, i.e. the level of
 DGEMM's own rounding); fitted weights through the tensor-core Gram -> the north_star's 1e-6 against the reference
 fixture (tests/test_fitting_gpu.py runs with gram="tc" by default)."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -243,3 +245,20 @@ def test_tc_gram_propagates_non_finite_input(bad):
     acc = torch.zeros((64, 512), dtype=torch.float64, device="cuda")
     ext.atb_accum_tc(a, z, acc)
     assert not bool(torch.isfinite(acc[:, 45]).any()) and bool(torch.isfinite(acc[:, keep]).all())
+
+
+def test_cta_pair_kernel_in_its_own_process():
+    """tc_gram_pair_kernel (cta_group::2: two CTAs of a cluster share each column tile, the leader issues M = 256 MMAs for
+    both) is opt-in through XGPR_B200_TC_PAIR=1, read once per process: rerun the bit-exact and error-bound cases of this
+    file with it set.  The same cases, so the same bounds."""
+    import subprocess
+    import sys
+    if os.environ.get("XGPR_B200_TC_PAIR"):
+        pytest.skip("already running with the pair kernel selected")
+    env = dict(os.environ, XGPR_B200_TC_PAIR="1")
+    here = os.path.abspath(__file__)
+    res = subprocess.run([sys.executable, "-m", "pytest", here, "-x", "-q", "-m", "gpu", "-k",
+                          "dyadic or error_bound or row_passes or matches_dfma or base256 or ztzq_general"],
+                         env=env, capture_output=True, text=True, timeout=600, cwd=os.path.dirname(os.path.dirname(here)))
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-2000:]
+    assert " passed" in res.stdout

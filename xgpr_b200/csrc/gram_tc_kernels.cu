@@ -261,6 +261,7 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 // is what bounds this kernel (the int8 pipe outruns L2), hence the large tile.
 struct TcSched {
     int num_slices, n_kblocks, tiles, num_tiles, full_waves, split_remainder, symmetric, digit_bits, max_kb_acc, supertile;
+    int pair_rows;      // tc_gram_pair_kernel: 512-row pair rows (num_tiles then counts pair tiles)
 };
 struct TcSeg { int tile, kb0, kb1; };
 
@@ -495,6 +496,256 @@ tc_gram_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     }
 }
 
+// ------------------------------------------------------------------ the GEMM on CTA pairs (cta_group::2)
+// Same segments, weight groups and epilogue as tc_gram_kernel, on clusters of two CTAs (one TPC).  A pair owns two
+// vertically adjacent 256 x 256 tiles (tile rows 2I and 2I + 1, tile column tj): CTA r holds the 256 plane rows of ITS tile
+// (two 128-row A halves) and HALF of the column tile's plane rows (128 of 256) in shared memory, and each
+// tcgen05.mma.cta_group::2 (M = 256 = 128 rows of either CTA, N = 256) reads the B half of both CTAs.  Per 128-byte K block a
+// CTA fills 48 KB instead of 64 KB for the same 2 x 4 MMAs' worth of tensor work -- shared-memory fill is what bounds the
+// single-CTA kernel -- and the freed 16 KB buy a fourth pipeline stage.  Protocol (CUTLASS's 2-SM pipeline):
+//   full[s]   lives in the leader (rank 0): its producer arrives with expect_tx for BOTH CTAs' bytes; every TMA of either
+//             CTA completes its bytes there (cp.async.bulk.tensor ... .cta_group::2 with the leader's barrier address);
+//   empty[s]  one per CTA, released by the leader's tcgen05.commit multicast to both CTAs;
+//   tfull     one per CTA, same multicast commit: both epilogues drain their own 128 TMEM lanes x 512 columns;
+//   tempty    in the leader, 2 x 8 epilogue warps arrive (the peer's remotely).
+// Symmetric mode walks pair rows I and tile columns tj >= 2I; the tile (2I + 1, 2I) below the diagonal is computed and not
+// written (T / 2 wasted tiles out of T (T + 1) / 2: 3 % at 8,192 features).
+constexpr int TC2_STAGES = 4;
+constexpr int TC2_STAGE_BYTES = 3 * 16384;           // A rows 0-127, A rows 128-255 of the CTA's tile; its half of B
+constexpr int TC2_SMEM_BYTES = TC2_STAGES * TC2_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ +
+                               TC_EPI_WARPS * TC_EPI_STAGE_WORDS * 4;
+constexpr uint32_t TC2_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+
+__device__ __forceinline__ uint32_t cluster_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t addr, uint32_t rank) {      // shared::cta -> shared::cluster of `rank`
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_pair(uint32_t dst, const CUtensorMap* map, uint32_t leader_bar, int c0, int c1,
+                                                 int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(dst), "l"(map), "r"(leader_bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar) {      // arrives on `bar` in BOTH CTAs of the pair
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void tc_mma_i8_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                               uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+// linear pair-tile index -> (pair row I, tile column tj).  sc.tiles = tile columns, sc.pair_rows = pair rows.
+__device__ __forceinline__ void tc_pair_coords(const TcSched& sc, int lin, int& pi, int& tj) {
+    if (!sc.symmetric) {
+        pi = lin / sc.tiles;
+        tj = lin - pi * sc.tiles;
+        return;
+    }
+    const int T = sc.tiles, P = sc.pair_rows, SB = sc.supertile, SBP = sc.supertile / 2;
+    for (int r0 = 0; r0 < P; r0 += SBP) {
+        const int h = (r0 + SBP < P) ? SBP : P - r0;
+        for (int c0 = 2 * r0; c0 < T; c0 += SB) {
+            const int w = (c0 + SB < T) ? SB : T - c0;
+            if (c0 == 2 * r0) {
+                for (int i = 0; i < h; ++i) {
+                    const int len = w - 2 * i;
+                    if (len <= 0) break;
+                    if (lin < len) { pi = r0 + i; tj = c0 + 2 * i + lin; return; }
+                    lin -= len;
+                }
+            } else {
+                const int cnt = h * w;
+                if (lin < cnt) { pi = r0 + lin / w; tj = c0 + lin % w; return; }
+                lin -= cnt;
+            }
+        }
+    }
+    pi = tj = 0;    // not reached
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
+tc_gram_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const TcSched sc,
+                    int64_t ma, int64_t mb, const double* __restrict__ scale_a, const double* __restrict__ scale_b,
+                    double* __restrict__ g_out) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_base = smem_base + TC2_STAGES * TC2_STAGE_BYTES;
+    auto full_bar   = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar  = [&](int s) { return bar_base + 8u * (TC2_STAGES + s); };
+    const uint32_t tfull_bar = bar_base + 8u * (2 * TC2_STAGES);
+    const uint32_t tempty_bar = bar_base + 8u * (2 * TC2_STAGES + 1);
+    const uint32_t tmem_slot = bar_base + 8u * (2 * TC2_STAGES + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_rank();
+    const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < TC2_STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        mbar_init(tfull_bar, 1);
+        mbar_init(tempty_bar, 2 * TC_EPI_WARPS);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    }
+    if (warp == 1) {   // one warp of EACH CTA: all 512 columns of both SMs
+        const uint32_t ncols = 512;
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(ncols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    cluster_sync_all();                                  // barriers of both CTAs initialised, TMEM allocated
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+    if (warp == 0) {
+        // ---------------------------------------------------------------- TMA producer (both CTAs)
+        if (lane == 0) {
+            uint32_t ks = 0;
+            for (int si = 0; si < sc.full_waves + 2; ++si) {
+                const TcSeg sg = tc_segment(sc, si, pair, npairs);
+                if (sg.kb1 <= sg.kb0) continue;
+                int pi, tj;
+                tc_pair_coords(sc, sg.tile, pi, tj);
+                const int arow = (2 * pi + (int)rank) * TC_TILE;
+                const int brow = tj * TC_TILE + (int)rank * 128;
+                for (int g = sc.num_slices - 1; g >= 0; --g) {
+                  const int step = sc.max_kb_acc / (g + 1);
+                  for (int sb = sg.kb0; sb < sg.kb1; sb += step) {
+                    const int se = (sb + step < sg.kb1) ? sb + step : sg.kb1;
+                    for (int k = 0; k <= g; ++k) {
+                        const int l = g - k;
+                        for (int kb = sb; kb < se; ++kb, ++ks) {
+                            const int st = ks % TC2_STAGES;
+                            mbar_wait(empty_bar(st), ((ks / TC2_STAGES) & 1) ^ 1);
+                            const uint32_t dst = smem_base + st * TC2_STAGE_BYTES;
+                            if (rank == 0) mbar_expect_tx(full_bar(st), 2 * TC2_STAGE_BYTES);
+                            const uint32_t lbar = map_to_cta(full_bar(st), 0);
+                            tma_load_3d_pair(dst,             &map_a, lbar, kb * TC_BK, arow,       k);
+                            tma_load_3d_pair(dst + 16384,     &map_a, lbar, kb * TC_BK, arow + 128, k);
+                            tma_load_3d_pair(dst + 2 * 16384, &map_b, lbar, kb * TC_BK, brow,       l);
+                        }
+                    }
+                  }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ---------------------------------------------------------------- MMA issuer (one thread of the leader CTA)
+        if (lane == 0 && rank == 0) {
+            uint32_t ks = 0, it = 0;
+            for (int si = 0; si < sc.full_waves + 2; ++si) {
+                const TcSeg sg = tc_segment(sc, si, pair, npairs);
+                if (sg.kb1 <= sg.kb0) continue;
+                for (int g = sc.num_slices - 1; g >= 0; --g) {
+                  const int step = sc.max_kb_acc / (g + 1);
+                  for (int sb = sg.kb0; sb < sg.kb1; sb += step, ++it) {
+                    const int se = (sb + step < sg.kb1) ? sb + step : sg.kb1;
+                    mbar_wait(tempty_bar, (it & 1) ^ 1);                 // both epilogues have drained the accumulators
+                    tc_fence_after();
+                    const int nblk = (g + 1) * (se - sb);
+                    for (int b = 0; b < nblk; ++b, ++ks) {
+                        const int st = ks % TC2_STAGES;
+                        mbar_wait(full_bar(st), (ks / TC2_STAGES) & 1);
+                        tc_fence_after();
+                        const uint32_t a_addr = smem_base + st * TC2_STAGE_BYTES;
+                        const uint64_t da0 = tc_smem_desc(a_addr), da1 = tc_smem_desc(a_addr + 16384),
+                                       db = tc_smem_desc(a_addr + 2 * 16384);
+#pragma unroll
+                        for (int kk = 0; kk < TC_BK / 32; ++kk) {
+                            const uint32_t accum = (b > 0 || kk > 0) ? 1u : 0u;
+                            tc_mma_i8_pair(tmem_base,        da0 + (uint64_t)(kk * 2), db + (uint64_t)(kk * 2), TC2_IDESC, accum);
+                            tc_mma_i8_pair(tmem_base + 256u, da1 + (uint64_t)(kk * 2), db + (uint64_t)(kk * 2), TC2_IDESC, accum);
+                        }
+                        tc_commit_pair(empty_bar(st));                  // the slot is free in both CTAs once these retire
+                    }
+                    tc_commit_pair(tfull_bar);                          // accumulators complete, both CTAs
+                  }
+                }
+            }
+        }
+    } else {
+        // ---------------------------------------------------------------- epilogue (both CTAs), as in tc_gram_kernel
+        const int quad = warp & 3;
+        const int half = (warp - 2) >> 2;
+        int* stage = reinterpret_cast<int*>(smem_raw + (bar_base + 256u - smem_u32(smem_raw))) +
+                     (warp - 2) * TC_EPI_STAGE_WORDS;
+        const uint32_t tempty_leader = map_to_cta(tempty_bar, 0);
+        uint32_t it = 0;
+        for (int si = 0; si < sc.full_waves + 2; ++si) {
+            const TcSeg sg = tc_segment(sc, si, pair, npairs);
+            if (sg.kb1 <= sg.kb0) continue;
+            int pi, tj;
+            tc_pair_coords(sc, sg.tile, pi, tj);
+            const int64_t wrow0 = (int64_t)(2 * pi + (int)rank) * TC_TILE + half * 128 + quad * 32;
+            const int64_t col0 = (int64_t)tj * TC_TILE;
+            const double rs = (wrow0 + lane < ma) ? scale_a[wrow0 + lane] : 0.0;
+            const int64_t diag = sc.symmetric ? wrow0 : 0;
+            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 256);
+            for (int g = sc.num_slices - 1; g >= 0; --g) {
+              const int step = sc.max_kb_acc / (g + 1);
+              const double wg = exp2(-(double)(sc.digit_bits * (g + 2)));
+              for (int sb = sg.kb0; sb < sg.kb1; sb += step, ++it) {
+                mbar_wait(tfull_bar, it & 1);
+                tc_fence_after();
+#pragma unroll 1
+                for (int c = 0; c < TC_TILE / 32; ++c) {
+                    const int64_t cb = col0 + c * 32;
+                    if (cb + 31 < diag || cb >= mb || wrow0 >= ma) continue;
+                    uint32_t acc[32];
+                    tmem_ld32(taddr + c * 32, acc);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int uu = 0; uu < 32; ++uu) stage[lane * 33 + uu] = (int)acc[uu];
+                    __syncwarp();
+                    const int64_t col = cb + lane;
+                    const double cs = (col < mb) ? __ldg(scale_b + col) * wg : 0.0;
+#pragma unroll 4
+                    for (int r = 0; r < 32; ++r) {
+                        const int64_t row = wrow0 + r;
+                        const double rsr = __shfl_sync(0xffffffffu, rs, r);
+                        const int val = stage[r * 33 + lane];
+                        if (row < ma && col < mb && (!sc.symmetric || col >= row)) {
+                            const double v = (double)val * (rsr * cs);
+                            atomicAdd(g_out + row * mb + col, v);
+                        }
+                    }
+                    __syncwarp();
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(tempty_leader);
+              }
+            }
+        }
+    }
+    tc_fence_before();
+    cluster_sync_all();                                  // no CTA leaves (or frees TMEM) while its peer may still signal it
+    if (warp == 1) {
+        tc_fence_after();
+        const uint32_t ncols = 512;
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(ncols) : "memory");
+    }
+}
+
 // ------------------------------------------------------------------ lower triangle <- upper triangle (32 x 32 tiles through smem)
 __global__ void __launch_bounds__(256)
 tc_mirror_kernel(double* __restrict__ g, int64_t m) {
@@ -607,6 +858,9 @@ static int tc_setup(int& sms) {
     if (!smem_set) {
         if (cudaFuncSetAttribute(tc_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES) != cudaSuccess)
             return check_launch("tc_gram_kernel smem attribute");
+        if (cudaFuncSetAttribute(tc_gram_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC2_SMEM_BYTES) !=
+            cudaSuccess)
+            return check_launch("tc_gram_pair_kernel smem attribute");
         smem_set = 1;
     }
     int dev = 0;
@@ -649,6 +903,34 @@ static int tc_launch_gemm(const TcOperand& a, const TcOperand& b, int64_t rows, 
     sc.symmetric = symmetric;
     sc.tiles = (int)((mb + TC_TILE - 1) / TC_TILE);
     const int tiles_i = (int)((ma + TC_TILE - 1) / TC_TILE);
+    sc.pair_rows = 0;
+    // CTA pairs (tc_gram_pair_kernel, cta_group::2) are opt-in: XGPR_B200_TC_PAIR=1.  Measured on B200 at 32,768 x 8,192, 5 x 8
+    // bits (profiles/r02p_gram_pair_ab.jsonl, r02p_tc_gram_pair_full.md): 12.36 - 12.94 ms against 12.22 - 12.46 ms for the
+    // single-CTA kernel.  Both are bound by the tensor pipe (92.7 % / 90.5 % active under ncu) at the power-limited clock --
+    // 0.97 - 0.99 of the sustained cuBLAS bf16 rate x 2 -- so the 25 % smaller shared-memory fill of the pair buys nothing and
+    // its below-diagonal tile per pair row costs 3 %.
+    static const int pair_env = getenv("XGPR_B200_TC_PAIR") ? atoi(getenv("XGPR_B200_TC_PAIR")) : 0;
+    const bool use_pair = pair_env != 0 && sms >= 2;
+    if (use_pair) {
+        sc.supertile &= ~1;
+        if (sc.supertile < 2) sc.supertile = 2;
+        sc.pair_rows = (tiles_i + 1) / 2;
+        long long npt = 0;
+        if (symmetric) for (int i = 0; i < sc.pair_rows; ++i) npt += sc.tiles - 2 * i;
+        else npt = (long long)sc.pair_rows * sc.tiles;
+        sc.num_tiles = (int)npt;
+        long long pairs = npt * sc.n_kblocks;
+        if (pairs > sms / 2) pairs = sms / 2;
+        sc.full_waves = sc.num_tiles / (int)pairs;
+        const int rem2 = sc.num_tiles - sc.full_waves * (int)pairs;
+        sc.split_remainder = (rem2 > 0 && rem2 * 4 < (int)pairs * 3) ? 1 : 0;
+        if (g_tc_profile) cudaEventRecord(g_tc_ev0, st);
+        tc_gram_pair_kernel<<<(unsigned)(2 * pairs), TC_THREADS, TC2_SMEM_BYTES, st>>>(a.map, b.map, sc, ma, mb, a.colscale,
+                                                                                     b.colscale, c);
+        if (g_tc_profile) { cudaEventRecord(g_tc_ev1, st); g_tc_ev_valid = 1; }
+        count_launch();
+        return check_launch("tc_gram_pair_kernel");
+    }
     sc.num_tiles = symmetric ? sc.tiles * (sc.tiles + 1) / 2 : tiles_i * sc.tiles;
     // grid: all SMs, unless the whole problem has fewer K blocks than that
     long long grid = (long long)sc.num_tiles * sc.n_kblocks;
