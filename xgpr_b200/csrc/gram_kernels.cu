@@ -547,7 +547,9 @@ ztt_tile2_kernel(const double* __restrict__ z, int64_t n, int64_t m, const doubl
 // each of the 4 warps owns 32 rows x 32 columns = 4 x 4 fragments (16 DMMA per 8 conflict-free LDS.64).
 constexpr int M3_KC = 16;                                        // K chunk per stage
 constexpr int M3_ZV_LD = M3_KC + 4;                              // row-major Z tile: row stride == 8 words (mod 32)
-constexpr int M3_B_LD = M2_COLS + 8;                             // V / T tile: row stride == 16 words (mod 32)
+constexpr int M3_B_LD = M2_COLS + 4;                             // V / T tile: row stride 72 words == 8 (mod 32): the 16 lanes
+                                                                 // of an LDS.64 half-warp (4 g x 4 t) land on 4 x 8 distinct banks
+                                                                 // (ncu r02o: stride 80 was a 2-way conflict on every B load)
 constexpr int M3_ZT_LD = M2_ROWS + 8;                            // Z^T operand read from a [k][column] tile
 constexpr int M3_ZV_STAGE = M2_ROWS * M3_ZV_LD + M3_KC * M3_B_LD;
 constexpr int M3_ZT_STAGE = M3_KC * M3_ZT_LD + M3_KC * M3_B_LD;
@@ -576,9 +578,14 @@ template <typename ZT> struct m3_tile {
     static constexpr int ZT_A = (M3_KC * ZT_LD * (int)sizeof(ZT) + 7) / 8;
     static constexpr int ZV_STAGE = ZV_A + M3_KC * M3_B_LD;
     static constexpr int ZT_STAGE = ZT_A + M3_KC * M3_B_LD;
-    static constexpr int ZV_SMEM = 2 * ZV_STAGE * 8, ZT_SMEM = 2 * ZT_STAGE * 8;
+    // pipeline depth: the float tiles are half the size, which buys a third stage at 4 CTAs per SM (one barrier per K
+    // chunk either way: chunk it + STAGES - 1 is issued right after the barrier that retires chunk it - 1)
+    static constexpr int STAGES = sizeof(ZT) == 8 ? 2 : 3;
+    static constexpr int ZV_SMEM = STAGES * ZV_STAGE * 8, ZT_SMEM = STAGES * ZT_STAGE * 8;
 };
-static_assert(m3_tile<double>::ZV_SMEM == M3_ZV_SMEM && m3_tile<double>::ZT_SMEM == M3_ZT_SMEM, "fp64 tile sizes");
+static_assert(4 * (m3_tile<double>::ZV_SMEM + 1024) <= 227 * 1024 && 4 * (m3_tile<float>::ZV_SMEM + 1024) <= 227 * 1024 &&
+              4 * (m3_tile<double>::ZT_SMEM + 1024) <= 227 * 1024 && 4 * (m3_tile<float>::ZT_SMEM + 1024) <= 227 * 1024,
+              "four CTAs per SM");
 
 template <typename ZT, bool TAIL>
 __global__ void __launch_bounds__(128, 4)
@@ -620,14 +627,18 @@ zv_mma_kernel(const ZT* __restrict__ z, int64_t n, int64_t m, const double* __re
             cp_async8(vs + kk * M3_B_LD + cc, ok ? v + k * ldv + r0 + cc : v, ok);
         }
     };
-    load(0, kbeg);
-    cp_async_commit();
-    int s = 0;
-    for (int64_t k0 = kbeg; k0 < kend; k0 += M3_KC, s ^= 1) {
-        if (k0 + M3_KC < kend) load(s ^ 1, k0 + M3_KC);
+    constexpr int NS = TL::STAGES;
+#pragma unroll
+    for (int p = 0; p < NS - 1; ++p) {                           // prologue: chunks 0 .. NS - 2
+        if (kbeg + (int64_t)p * M3_KC < kend) load(p, kbeg + (int64_t)p * M3_KC);
         cp_async_commit();
-        cp_async_wait<1>();
-        __syncthreads();
+    }
+    int s = 0, sn = NS - 1;                                      // stage being consumed / stage the next load goes to
+    for (int64_t k0 = kbeg; k0 < kend; k0 += M3_KC) {
+        cp_async_wait<NS - 2>();                                 // this thread's pieces of chunk k0 have landed
+        __syncthreads();                                         // ... everyone's; and everyone is done with stage sn
+        if (k0 + (int64_t)(NS - 1) * M3_KC < kend) load(sn, k0 + (int64_t)(NS - 1) * M3_KC);
+        cp_async_commit();
         const ZT* zs = reinterpret_cast<const ZT*>(m2_smem + s * TL::ZV_STAGE) + (warp * 32 + g) * TL::ZV_LD + t;
         const double* vs = m2_smem + s * TL::ZV_STAGE + TL::ZV_A + t * M3_B_LD;
 #pragma unroll
@@ -650,7 +661,8 @@ zv_mma_kernel(const ZT* __restrict__ z, int64_t n, int64_t m, const double* __re
                 }
             }
         }
-        __syncthreads();
+        s = (s + 1 == NS) ? 0 : s + 1;
+        sn = (sn + 1 == NS) ? 0 : sn + 1;
     }
     cp_async_wait<0>();
     if (TAIL) {
@@ -729,14 +741,18 @@ ztt_mma_kernel(const ZT* __restrict__ z, int64_t n, int64_t m, const double* __r
             cp_async8(ts + kk * M3_B_LD + cc, ok ? tt + row * ldt + r0 + cc : tt, ok);
         }
     };
-    load(0, kbeg);
-    cp_async_commit();
-    int s = 0;
-    for (int64_t k0 = kbeg; k0 < kend; k0 += M3_KC, s ^= 1) {
-        if (k0 + M3_KC < kend) load(s ^ 1, k0 + M3_KC);
+    constexpr int NS = TL::STAGES;
+#pragma unroll
+    for (int p = 0; p < NS - 1; ++p) {
+        if (kbeg + (int64_t)p * M3_KC < kend) load(p, kbeg + (int64_t)p * M3_KC);
         cp_async_commit();
-        cp_async_wait<1>();
+    }
+    int s = 0, sn = NS - 1;
+    for (int64_t k0 = kbeg; k0 < kend; k0 += M3_KC) {
+        cp_async_wait<NS - 2>();
         __syncthreads();
+        if (k0 + (int64_t)(NS - 1) * M3_KC < kend) load(sn, k0 + (int64_t)(NS - 1) * M3_KC);
+        cp_async_commit();
         const ZT* zs = reinterpret_cast<const ZT*>(m2_smem + s * TL::ZT_STAGE) + t * TL::ZT_LD + warp * 32 + g;
         const double* ts = m2_smem + s * TL::ZT_STAGE + TL::ZT_A + t * M3_B_LD;
 #pragma unroll
@@ -759,7 +775,8 @@ ztt_mma_kernel(const ZT* __restrict__ z, int64_t n, int64_t m, const double* __r
                 }
             }
         }
-        __syncthreads();
+        s = (s + 1 == NS) ? 0 : s + 1;
+        sn = (sn + 1 == NS) ? 0 : sn + 1;
     }
     cp_async_wait<0>();
     if (TAIL) {
