@@ -83,6 +83,46 @@ z_times_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double*
     }
 }
 
+// ------------------------------------------------------------------ one right-hand side, 16-byte loads
+// zt_times_kernel<1> issues 8-byte loads four deep between two CTA barriers per 64 rows and measured 3.6 TB/s on a 4.3 GB
+// chunk (1.19 ms per 32,768 x 16,384 Z^T y).  This form (even m, 16-byte aligned Z) loads double2, eight rows in flight per
+// thread, no shared memory, t through the read-only path: 0.59 ms = 7.3 TB/s of reads (profiles/r02s_zty_ab.jsonl); same
+// fp64 FMAs, another summation order.
+__global__ void __launch_bounds__(256)
+zty_vec2_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double* __restrict__ t, int64_t ldt,
+                double* __restrict__ w, int64_t ldw, int64_t rows_per_block) {
+    const int64_t col = 2 * ((int64_t)blockIdx.x * blockDim.x + threadIdx.x);
+    const int64_t n0 = (int64_t)blockIdx.y * rows_per_block;
+    const int64_t n1 = (n0 + rows_per_block < n) ? n0 + rows_per_block : n;
+    if (col >= m) return;
+    double a0 = 0.0, a1 = 0.0, b0 = 0.0, b1 = 0.0;
+    const double* zp = z + n0 * m + col;
+    int64_t row = n0;
+    for (; row + 8 <= n1; row += 8, zp += 8 * m) {
+        double2 q[8];
+        double tv[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) q[i] = *reinterpret_cast<const double2*>(zp + (int64_t)i * m);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) tv[i] = __ldg(t + (row + i) * ldt);
+#pragma unroll
+        for (int i = 0; i < 8; i += 2) {
+            a0 = fma(q[i].x, tv[i], a0);
+            a1 = fma(q[i].y, tv[i], a1);
+            b0 = fma(q[i + 1].x, tv[i + 1], b0);
+            b1 = fma(q[i + 1].y, tv[i + 1], b1);
+        }
+    }
+    for (; row < n1; ++row, zp += m) {
+        const double2 q = *reinterpret_cast<const double2*>(zp);
+        const double tv = __ldg(t + row * ldt);
+        a0 = fma(q.x, tv, a0);
+        a1 = fma(q.y, tv, a1);
+    }
+    atomicAdd(w + col * ldw, a0 + b0);
+    atomicAdd(w + (col + 1) * ldw, a1 + b1);
+}
+
 // ------------------------------------------------------------------ ztz += Z^T Z  (upper tiles, mirrored)
 // 64x64 output tile per CTA, 256 threads, 4x4 register micro-tile, k-chunks of 16 rows staged in smem.
 constexpr int GT = 64, GK = 16;
@@ -846,6 +886,17 @@ int atb_accum(const double* a, const double* b, int64_t n, int64_t r, int64_t m,
     return check_launch("atb_kernel");
 }
 
+// grid of the 16-byte single-RHS Z^T t kernel: 512 columns per CTA, rows split so that ~8 CTAs per SM are in flight
+static void launch_zty_vec2(const double* z, int64_t n, int64_t m, const double* t, int64_t ldt, double* w, int64_t ldw,
+                            cudaStream_t st) {
+    const int64_t colblocks = (m / 2 + 255) / 256;
+    int64_t splits = (148 * 8 + colblocks - 1) / colblocks;
+    int64_t rows_per = (n + splits - 1) / splits;
+    rows_per = ((rows_per + 7) / 8) * 8;
+    splits = (n + rows_per - 1) / rows_per;
+    zty_vec2_kernel<<<dim3((unsigned)colblocks, (unsigned)splits), 256, 0, st>>>(z, n, m, t, ldt, w, ldw, rows_per);
+}
+
 int zty_accum(const double* z, int64_t n, int64_t m, const double* y, double* zty, cudaStream_t st) {
     XB_REQUIRE(n > 0 && m > 0, "no datapoints");
     XB_REQUIRE(z && y && zty, "null pointer");
@@ -855,6 +906,12 @@ int zty_accum(const double* z, int64_t n, int64_t m, const double* y, double* zt
     rows_per = ((rows_per + 63) / 64) * 64;
     splits = (n + rows_per - 1) / rows_per;
     dim3 grid((unsigned)colblocks, (unsigned)splits);
+    static const bool v1 = getenv("XGPR_B200_ZTY_V1") != nullptr;
+    if (!v1 && m % 2 == 0 && reinterpret_cast<uintptr_t>(z) % 16 == 0) {
+        launch_zty_vec2(z, n, m, y, 1, zty, 1, st);
+        count_launch();
+        return check_launch("zty_vec2_kernel");
+    }
     zt_times_kernel<1><<<grid, 256, 0, st>>>(z, n, m, y, 1, 0, 1, zty, 1, rows_per);
     count_launch();
     return check_launch("zt_times_kernel");
@@ -915,8 +972,14 @@ int cg_matvec_accum(const double* z, int64_t n, int64_t m, const double* v, int6
     int64_t wblocks = (n + 7) / 8;
     if (wblocks > 148 * 16) wblocks = 148 * 16;
     if (r == 1) {
+        static const bool v1 = getenv("XGPR_B200_ZTY_V1") != nullptr;
+        // t = Z v: the warp-per-row kernel already streams at 6 TB/s (a double2 variant measured slower); w += Z^T t
+        // through the 16-byte-load kernel
         z_times_kernel<1><<<(unsigned)wblocks, 256, 0, st>>>(z, n, m, v, r, 0, 1, scratch, r);
-        zt_times_kernel<1><<<grid2, 256, 0, st>>>(z, n, m, scratch, r, 0, 1, w, r, rows_per);
+        if (!v1 && m % 2 == 0 && reinterpret_cast<uintptr_t>(z) % 16 == 0)
+            launch_zty_vec2(z, n, m, scratch, r, w, r, st);
+        else
+            zt_times_kernel<1><<<grid2, 256, 0, st>>>(z, n, m, scratch, r, 0, 1, w, r, rows_per);
         count_launch(2);
         return check_launch("cg_matvec");
     }
