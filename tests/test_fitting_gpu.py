@@ -301,3 +301,46 @@ def test_multi_rhs_cg_encoded_chunks_match_fp64_chunks(kname, monkeypatch):
         # converged solutions of the same system: CG amplifies the rounding differences of the two forms by the condition
         # number, so the bound is on the solution's scale (the north_star weight tolerance is 1e-6)
         np.testing.assert_allclose(o, outs[0], rtol=0, atol=1e-8 * float(np.abs(outs[0]).max()))
+
+
+def _guarded(shape, fill=0.0, pad=2048):
+    """A float64 CUDA view of `shape` with NaN guard bands on both sides of its storage."""
+    n = int(np.prod(shape))
+    buf = torch.full((n + 2 * pad,), float("nan"), dtype=torch.float64, device="cuda")
+    view = buf[pad:pad + n].view(shape)
+    view.fill_(fill)
+    return buf, view, pad, n
+
+
+@pytest.mark.parametrize("shape", [(130, 4100, 25), (1000, 520, 26), (257, 132, 3), (33, 8, 1), (4097, 260, 32), (64, 16388, 26)])
+def test_consumer_outputs_stay_inside_their_arrays(shape):
+    """Guard bands around every array the multi-RHS / single-RHS consumers WRITE (w, the (n, r) intermediate, Z^T y): no
+    element outside the arrays may change, for row / feature / RHS counts that are not multiples of any tile.  (The pool's
+    compute-sanitizer is closed, so out-of-bounds stores are looked for this way.)"""
+    from xgpr_b200 import ext
+    n, m, r = shape
+    rng = np.random.default_rng(21)
+    zf = rng.standard_normal((n, m)).astype(np.float32)
+    z = torch.from_numpy(zf.astype(np.float64)).cuda()
+    c = torch.from_numpy(zf).cuda()
+    v = torch.from_numpy(rng.standard_normal((m, r))).cuda()
+    y = torch.from_numpy(rng.standard_normal(n)).cuda()
+    want = zf.astype(np.float64).T @ (zf.astype(np.float64) @ v.cpu().numpy())
+    tol = dict(rtol=1e-10, atol=1e-11 * float(np.abs(want).max()))
+    for which in ("f64", "c32"):
+        wb, w, pad, cnt = _guarded((m, r))
+        sb, s, spad, scnt = _guarded((n, r), fill=7.0)
+        if which == "f64":
+            ext.cg_matvec_accum(z, v, w, s)
+        else:
+            ext.cg_matvec_accum_c32(c, v, w, 1.0, False, s)
+        torch.cuda.synchronize()
+        np.testing.assert_allclose(w.cpu().numpy(), want, **tol)
+        for buf, p, k in ((wb, pad, cnt), (sb, spad, scnt)):
+            assert bool(torch.isnan(buf[:p]).all()) and bool(torch.isnan(buf[p + k:]).all()), (which, shape)
+    tb, t, pad, cnt = _guarded((m,))
+    ext.zty_accum(z, y, t)
+    torch.cuda.synchronize()
+    wanty = zf.astype(np.float64).T @ y.cpu().numpy()
+    np.testing.assert_allclose(t.cpu().numpy(), wanty, rtol=1e-10, atol=1e-11 * float(np.abs(wanty).max()))
+    assert bool(torch.isnan(tb[:pad]).all()) and bool(torch.isnan(tb[pad + cnt:]).all())
