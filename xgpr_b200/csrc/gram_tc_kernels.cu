@@ -940,6 +940,10 @@ static int tc_launch_gemm(const TcOperand& a, const TcOperand& b, int64_t rows, 
     // the shared row blocks): measured to pay off only when that wave would leave > 1/4 of the SMs idle.
     const int rem = sc.num_tiles - sc.full_waves * (int)grid;
     sc.split_remainder = (rem > 0 && rem * 4 < (int)grid * 3) ? 1 : 0;
+    // XGPR_B200_TC_SPLIT=0/1 forces the choice (A/B switch; the sketch GEMM A^T Z, 128 tiles on 148 SMs: whole tiles 5.65 ms,
+    // split 5.84 ms per 32,768 x 16,384 chunk, profiles/r02s_tc_split_ab.jsonl)
+    static const int split_env = getenv("XGPR_B200_TC_SPLIT") ? atoi(getenv("XGPR_B200_TC_SPLIT")) : -1;
+    if (split_env >= 0) sc.split_remainder = (rem > 0 && split_env != 0) ? 1 : 0;
     if (g_tc_profile) cudaEventRecord(g_tc_ev0, st);
     tc_gram_kernel<<<(unsigned)grid, TC_THREADS, TC_SMEM_BYTES, st>>>(a.map, b.map, sc, ma, mb, a.colscale, b.colscale, c);
     if (g_tc_profile) { cudaEventRecord(g_tc_ev1, st); g_tc_ev_valid = 1; }
