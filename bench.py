@@ -698,7 +698,8 @@ def fit_headline(args, dev, rank, world, chunk=32768, tol=1e-6, maxiter=200):
     cg_op = {"op": fitting.ConjugateGrad(comm)}
     pre, t_pre = timed(lambda: fitting.RandNysPreconditioner(
         kern, ds, args.fit_rank, False, 123, "srht", comm,
-        overlap_hook=lambda: cg_op["op"].prepare_async(ds, kern)))
+        overlap_hook=lambda: cg_op["op"].prepare_async(ds, kern),
+        encoded_source=lambda: cg_op["op"].resident_for_preconditioner(ds, kern)))
 
     def run_cg():
         return fitting.cg_fit_lib_internal(kern, ds, tol, maxiter, pre, False, comm, cg_operator=cg_op["op"])

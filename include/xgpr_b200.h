@@ -241,6 +241,18 @@ int xgpr_b200_atb_accum_f64(const double* a, const double* z, int64_t n, int64_t
 /* w (m, r) += Z^T (Z v) ;  v (m, r) row-major; scratch (n, r) f64 device workspace */
 int xgpr_b200_cg_matvec_accum_f64(const double* z, int64_t n, int64_t m, const double* v, int64_t r,
                                   double* w, double* scratch, void* stream);
+/* The preconditioner's accumulation pass (rand_nys_constructors.py:96-123) fed from the float32 encoding c of Z instead of
+ * fp64 Z (Z[i, j] = double(c[i, j]) * scale, formed in the kernels exactly as the feature kernels form it; column 0 of c
+ * = 1.0f stands for the intercept): Z^T y, the fused SRHT sample (fp64 butterflies, bit-identical to
+ * xgpr_b200_srht_sample_f64 on Z) and the tensor-core sketch product acc (r, m) += A^T Z.  Half the bytes per feature on
+ * every pass, and the encoding is the one the solve keeps resident anyway.  m % 4 == 0 for zty. */
+int xgpr_b200_zty_accum_c32(const float* c, int64_t n, int64_t m, const double* y, double* zty, double scale,
+                            int fit_intercept, void* stream);
+int xgpr_b200_srht_sample_c32(const float* c, int64_t n, int64_t m, const int8_t* radem, int64_t p_full, const int32_t* cols,
+                              int64_t rank, double* out, double scale, int fit_intercept, void* stream);
+int xgpr_b200_atb_accum_tc_c32(const double* a, const float* c, int64_t n, int64_t r, int64_t m, double* acc, double scale,
+                               int fit_intercept, int num_slices, int digit_bits, void* workspace,
+                               int64_t workspace_bytes, void* stream);
 /* The same product from the lossless float32 encoding c of sine-cosine features (xgpr_b200_rbf_feature_gen_c32:
  * Z[i, j] = double(c[i, j]) * scale; with fit_intercept the caller stores 1.0f in column 0, which then stands for
  * Z[i, 0] = 1).  vs (m, r) = v with row j multiplied by scale (row 0 left as it is with fit_intercept).  Half the bytes

@@ -344,3 +344,67 @@ def test_consumer_outputs_stay_inside_their_arrays(shape):
     wanty = zf.astype(np.float64).T @ y.cpu().numpy()
     np.testing.assert_allclose(t.cpu().numpy(), wanty, rtol=1e-10, atol=1e-11 * float(np.abs(wanty).max()))
     assert bool(torch.isnan(tb[:pad]).all()) and bool(torch.isnan(tb[pad + cnt:]).all())
+
+
+@pytest.mark.parametrize("icpt", [True, False])
+@pytest.mark.parametrize("shape", [(700, 64, 2048, 64), (2100, 20, 4096, 512), (333, 128, 16384, 512), (150, 8, 1024, 100)])
+def test_encoded_preconditioner_steps_equal_fp64_steps(shape, icpt):
+    """The preconditioner's accumulation pass fed from the float32 encoding of Z (xgpr_b200_zty_accum_c32,
+    xgpr_b200_srht_sample_c32, xgpr_b200_atb_accum_tc_c32) against the same steps on fp64 Z = transform_x(x): the SRHT sample
+    is bit-identical (same values into the same butterflies), Z^T y and the sketch product agree to rounding."""
+    from xgpr_b200 import ext
+    from xgpr_b200.kernels import RBF, SRHTCompressor
+    n, d, m, rank = shape
+    rng = np.random.default_rng(31)
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    y = torch.from_numpy(rng.standard_normal(n)).cuda()
+    kern = RBF(x.shape, m, random_seed=123, device="cuda")
+    kern.fit_intercept = icpt
+    kern.set_hyperparams(np.log(np.asarray([1.0, 0.3])), logspace=True)
+    z = kern.transform_x(x)
+    c = torch.empty((n, m), dtype=torch.float32, device="cuda")
+    kern.resident_generate(x, c)
+    if icpt:
+        c[:, 0] = 1.0
+    scale = kern.feature_scale()
+    comp = SRHTCompressor(rank, m, random_seed=123, device="cuda")
+    s64 = comp.transform_x(z)
+    s32 = comp.transform_encoded(c, scale, icpt)
+    assert s32 is not None and torch.equal(s64, s32)
+    t64 = torch.zeros(m, dtype=torch.float64, device="cuda")
+    t32 = torch.zeros(m, dtype=torch.float64, device="cuda")
+    ext.zty_accum(z, y, t64)
+    ext.zty_accum_c32(c, y, t32, scale, icpt)
+    np.testing.assert_allclose(t32.cpu().numpy(), t64.cpu().numpy(), rtol=1e-12, atol=1e-13 * float(t64.abs().max()))
+    a64 = torch.zeros((rank, m), dtype=torch.float64, device="cuda")
+    a32 = torch.zeros((rank, m), dtype=torch.float64, device="cuda")
+    ext.atb_accum_tc(s64, z, a64)
+    ext.atb_accum_tc_c32(s64, c, a32, scale, icpt)
+    want = s64.cpu().numpy().T @ z.cpu().numpy()
+    tol = 1e-10 * float(np.abs(want).max())
+    np.testing.assert_allclose(a64.cpu().numpy(), want, rtol=0, atol=tol)
+    np.testing.assert_allclose(a32.cpu().numpy(), want, rtol=0, atol=tol)
+
+
+def test_fit_cg_with_encoded_preconditioner_pass_matches_fp64_pass(monkeypatch):
+    """fitting.fit_cg end to end with the preconditioner's accumulation pass reading the resident float32 encoding (default
+    when the solve keeps it) against XGPR_B200_PRECOND_F64=1: same ratio, iteration count and weights."""
+    from xgpr_b200 import fitting
+    from xgpr_b200.kernels import RBF
+    rng = np.random.default_rng(41)
+    n, d, m = 6000, 20, 4096
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    y = np.sin(x[:, :3].sum(1)) + 0.1 * rng.standard_normal(n)
+    outs = []
+    for f64 in ("1", "0"):
+        monkeypatch.setenv("XGPR_B200_PRECOND_F64", f64)
+        kern = RBF(x.shape, m, random_seed=123, device="cuda")
+        kern.set_hyperparams(np.log(np.asarray([0.3, 0.4])), logspace=True)
+        ds = fitting.build_shard_dataset(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda(), None, chunk_size=2000)
+        w, nit, _, pre = fitting.fit_cg(kern, ds, 256, "srht", 1e-8, 300, 123, False)
+        outs.append((w.cpu().numpy(), nit, float(pre.achieved_ratio), pre.get_zty().cpu().numpy()))
+    (w0, n0, r0, t0), (w1, n1, r1, t1) = outs
+    assert abs(n0 - n1) <= 1
+    np.testing.assert_allclose(r1, r0, rtol=1e-7)
+    np.testing.assert_allclose(t1, t0, rtol=1e-12, atol=1e-13 * float(np.abs(t0).max()))
+    np.testing.assert_allclose(w1, w0, rtol=0, atol=1e-7 * float(np.abs(w0).max()))

@@ -38,5 +38,14 @@ cz, res["srht_sample_ms"] = timed(lambda: comp.transform_x(z))
 acc = torch.zeros((rank, m), dtype=torch.float64, device="cuda")
 _, res["atb_tc_ms"] = timed(lambda: ext.atb_accum_tc(cz, z, acc))
 res["sum_ms"] = res["featurise_ms"] + res["zty_ms"] + res["srht_sample_ms"] + res["atb_tc_ms"]
+# the same steps fed from the float32 encoding of Z (what the pass reads when the solve keeps the encoding resident)
+c = torch.empty((rows, m), dtype=torch.float32, device="cuda")
+_, res["encode_ms"] = timed(lambda: kern.resident_generate(x, c))
+c[:, 0] = 1.0
+scale = kern.feature_scale()
+_, res["zty_c32_ms"] = timed(lambda: ext.zty_accum_c32(c, y, zty, scale, True))
+cz2, res["srht_sample_c32_ms"] = timed(lambda: comp.transform_encoded(c, scale, True))
+_, res["atb_tc_c32_ms"] = timed(lambda: ext.atb_accum_tc_c32(cz2, c, acc, scale, True))
+res["sum_c32_ms"] = res["zty_c32_ms"] + res["srht_sample_c32_ms"] + res["atb_tc_c32_ms"]
 res["chunk_GB"] = rows * m * 8 / 1e9
 print(json.dumps(res))

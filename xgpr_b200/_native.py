@@ -60,6 +60,13 @@ for _name, _args in F64_ONLY.items():
     _fn.restype = _int
     EXPORTED.append(_name)
 
+lib.xgpr_b200_zty_accum_c32.argtypes = [_ptr, _i64, _i64, _ptr, _ptr, _dbl, _int, _ptr]
+lib.xgpr_b200_zty_accum_c32.restype = _int
+lib.xgpr_b200_srht_sample_c32.argtypes = [_ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _dbl, _int, _ptr]
+lib.xgpr_b200_srht_sample_c32.restype = _int
+lib.xgpr_b200_atb_accum_tc_c32.argtypes = [_ptr, _ptr, _i64, _i64, _i64, _ptr, _dbl, _int, _int, _int, _ptr, _i64, _ptr]
+lib.xgpr_b200_atb_accum_tc_c32.restype = _int
+EXPORTED += ["xgpr_b200_zty_accum_c32", "xgpr_b200_srht_sample_c32", "xgpr_b200_atb_accum_tc_c32"]
 lib.xgpr_b200_cg_matvec_accum_c32.argtypes = [_ptr, _i64, _i64, _ptr, _i64, _ptr, _ptr, _dbl, _int, _ptr]
 lib.xgpr_b200_cg_matvec_accum_c32.restype = _int
 EXPORTED.append("xgpr_b200_cg_matvec_accum_c32")

@@ -65,6 +65,13 @@ template <typename T>
 int srht_sample(const T* z, int64_t n, int64_t m, const int8_t* radem, int64_t p_full, const int32_t* cols,
                 int64_t rank, T* out, cudaStream_t st);
 int srht_sample_supported(int64_t p_full, int elem_bytes);
+int srht_sample_c32(const float* c, int64_t n, int64_t m, const int8_t* radem, int64_t p_full, const int32_t* cols,
+                    int64_t rank, double* out, double scale, int fit_intercept, cudaStream_t st);
+int zty_accum_c32(const float* c, int64_t n, int64_t m, const double* y, double* zty, double scale, int fit_intercept,
+                  cudaStream_t st);
+int atb_accum_tc_c32(const double* a, const float* c, int64_t n, int64_t r, int64_t m, double* acc, double scale,
+                     int fit_intercept, int num_slices, int digit_bits, void* workspace, int64_t workspace_bytes,
+                     cudaStream_t st);
 template <typename T>
 int scale_input(T* x, int64_t n, int64_t d, const double* w, double sigma, cudaStream_t st);
 template <typename T, bool GRAD>
@@ -234,6 +241,20 @@ int xgpr_b200_conv1d_grad_f64(const double* x, int64_t n, int64_t m, int64_t c, 
     return conv_dispatch<double, 1>(x, n, m, c, out, num_rffs, grad, radem, rl, chi, nf, sl, sigma, cw, stype, ST(s));
 }
 
+int xgpr_b200_zty_accum_c32(const float* c, int64_t n, int64_t m, const double* y, double* zty, double scale,
+                            int fit_intercept, void* s) {
+    return zty_accum_c32(c, n, m, y, zty, scale, fit_intercept, ST(s));
+}
+int xgpr_b200_srht_sample_c32(const float* c, int64_t n, int64_t m, const int8_t* radem, int64_t p_full, const int32_t* cols,
+                              int64_t rank, double* out, double scale, int fit_intercept, void* s) {
+    return srht_sample_c32(c, n, m, radem, p_full, cols, rank, out, scale, fit_intercept, ST(s));
+}
+int xgpr_b200_atb_accum_tc_c32(const double* a, const float* c, int64_t n, int64_t r, int64_t m, double* acc, double scale,
+                               int fit_intercept, int num_slices, int digit_bits, void* workspace,
+                               int64_t workspace_bytes, void* s) {
+    return atb_accum_tc_c32(a, c, n, r, m, acc, scale, fit_intercept, num_slices, digit_bits, workspace, workspace_bytes,
+                            ST(s));
+}
 int xgpr_b200_zty_accum_f64(const double* z, int64_t n, int64_t m, const double* y, double* zty, void* s) {
     return zty_accum(z, n, m, y, zty, ST(s));
 }

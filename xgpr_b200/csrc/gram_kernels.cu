@@ -123,6 +123,50 @@ zty_vec2_kernel(const double* __restrict__ z, int64_t n, int64_t m, const double
     atomicAdd(w + (col + 1) * ldw, a1 + b1);
 }
 
+// Z^T t from the float32 encoding c of Z (Z = double(c) * scale, column 0 = 1 with an intercept): float4 loads, four
+// columns per thread, each product formed as the feature kernel forms Z (one double multiply) before the FMA.
+__global__ void __launch_bounds__(256)
+zty_c32_kernel(const float* __restrict__ c, int64_t n, int64_t m, const double* __restrict__ t, int64_t ldt,
+               double* __restrict__ w, int64_t ldw, int64_t rows_per_block, double scale, int icpt) {
+    const int64_t col = 4 * ((int64_t)blockIdx.x * blockDim.x + threadIdx.x);
+    const int64_t n0 = (int64_t)blockIdx.y * rows_per_block;
+    const int64_t n1 = (n0 + rows_per_block < n) ? n0 + rows_per_block : n;
+    if (col >= m) return;
+    const double s0 = (icpt && col == 0) ? 1.0 : scale;
+    double a[4] = {0.0, 0.0, 0.0, 0.0}, b[4] = {0.0, 0.0, 0.0, 0.0};
+    const float* cp = c + n0 * m + col;
+    int64_t row = n0;
+    for (; row + 8 <= n1; row += 8, cp += 8 * m) {
+        float4 q[8];
+        double tv[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) q[i] = *reinterpret_cast<const float4*>(cp + (int64_t)i * m);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) tv[i] = __ldg(t + (row + i) * ldt);
+#pragma unroll
+        for (int i = 0; i < 8; i += 2) {
+            a[0] = fma(__dmul_rn((double)q[i].x, s0), tv[i], a[0]);
+            a[1] = fma(__dmul_rn((double)q[i].y, scale), tv[i], a[1]);
+            a[2] = fma(__dmul_rn((double)q[i].z, scale), tv[i], a[2]);
+            a[3] = fma(__dmul_rn((double)q[i].w, scale), tv[i], a[3]);
+            b[0] = fma(__dmul_rn((double)q[i + 1].x, s0), tv[i + 1], b[0]);
+            b[1] = fma(__dmul_rn((double)q[i + 1].y, scale), tv[i + 1], b[1]);
+            b[2] = fma(__dmul_rn((double)q[i + 1].z, scale), tv[i + 1], b[2]);
+            b[3] = fma(__dmul_rn((double)q[i + 1].w, scale), tv[i + 1], b[3]);
+        }
+    }
+    for (; row < n1; ++row, cp += m) {
+        const float4 q = *reinterpret_cast<const float4*>(cp);
+        const double tv = __ldg(t + row * ldt);
+        a[0] = fma(__dmul_rn((double)q.x, s0), tv, a[0]);
+        a[1] = fma(__dmul_rn((double)q.y, scale), tv, a[1]);
+        a[2] = fma(__dmul_rn((double)q.z, scale), tv, a[2]);
+        a[3] = fma(__dmul_rn((double)q.w, scale), tv, a[3]);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) atomicAdd(w + (col + j) * ldw, a[j] + b[j]);
+}
+
 // ------------------------------------------------------------------ ztz += Z^T Z  (upper tiles, mirrored)
 // 64x64 output tile per CTA, 256 threads, 4x4 register micro-tile, k-chunks of 16 rows staged in smem.
 constexpr int GT = 64, GK = 16;
@@ -915,6 +959,24 @@ int zty_accum(const double* z, int64_t n, int64_t m, const double* y, double* zt
     zt_times_kernel<1><<<grid, 256, 0, st>>>(z, n, m, y, 1, 0, 1, zty, 1, rows_per);
     count_launch();
     return check_launch("zt_times_kernel");
+}
+
+// zty (m) += Z^T y from the float32 encoding of Z; m % 4 == 0, c 16-byte aligned
+int zty_accum_c32(const float* c, int64_t n, int64_t m, const double* y, double* zty, double scale, int fit_intercept,
+                  cudaStream_t st) {
+    XB_REQUIRE(n > 0 && m > 0, "no datapoints");
+    XB_REQUIRE(c && y && zty, "null pointer");
+    XB_REQUIRE(m % 4 == 0 && reinterpret_cast<uintptr_t>(c) % 16 == 0, "float32 encoding: m % 4 == 0 and 16-byte alignment");
+    XB_REQUIRE(scale > 0.0, "scale must be positive");
+    const int64_t colblocks = (m / 4 + 255) / 256;
+    int64_t splits = (148 * 8 + colblocks - 1) / colblocks;
+    int64_t rows_per = (n + splits - 1) / splits;
+    rows_per = ((rows_per + 7) / 8) * 8;
+    splits = (n + rows_per - 1) / rows_per;
+    zty_c32_kernel<<<dim3((unsigned)colblocks, (unsigned)splits), 256, 0, st>>>(c, n, m, y, 1, zty, 1, rows_per, scale,
+                                                                              fit_intercept);
+    count_launch();
+    return check_launch("zty_c32_kernel");
 }
 
 int ztz_accum(const double* z, int64_t n, int64_t m, double* ztz, cudaStream_t st) {

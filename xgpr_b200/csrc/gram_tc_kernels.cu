@@ -41,10 +41,20 @@ constexpr int TC_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + 1024 /*align*/ + 256 
 constexpr int TC_THREADS = 64 + 32 * TC_EPI_WARPS;   // warp 0: TMA, warp 1: MMA, warps 2-9: epilogue
 constexpr int64_t TC_MAX_ROWS = 65536;   // int32 exactness bound for s <= 7
 
+// The element Z[row, col] from its stored form: fp64 Z itself, or the float32 encoding of sine-cosine features
+// (Z = double(c) * scale exactly, one double product as the feature kernels form it; with an intercept column 0 of c holds
+// 1.0f and stands for 1).  enc_scale <= 0 means "not encoded".
+struct ZForm { double scale; int icpt; };
+__device__ __forceinline__ double z_value(double x, int64_t, const ZForm&) { return x; }
+__device__ __forceinline__ double z_value(float c, int64_t col, const ZForm& f) {
+    return (double)c * ((f.icpt && col == 0) ? 1.0 : f.scale);
+}
+
 // ------------------------------------------------------------------ column max |Z|  (bits of a non-negative double order as u64)
+template <typename ZT>
 __global__ void __launch_bounds__(256)
-tc_colmax_kernel(const double* __restrict__ z, int64_t n, int64_t m, unsigned long long* __restrict__ cmax,
-                 int64_t rows_per_block) {
+tc_colmax_kernel(const ZT* __restrict__ z, int64_t n, int64_t m, unsigned long long* __restrict__ cmax,
+                 int64_t rows_per_block, ZForm form) {
     const int64_t col = (int64_t)blockIdx.x * 256 + threadIdx.x;
     if (col >= m) return;
     const int64_t n0 = (int64_t)blockIdx.y * rows_per_block;
@@ -52,10 +62,10 @@ tc_colmax_kernel(const double* __restrict__ z, int64_t n, int64_t m, unsigned lo
     // the maximum is taken on the BIT PATTERNS of |z| (they order like the values for non-negative doubles, with
     // Inf and NaN above every finite number): fmax would drop a NaN and the Gram of corrupt input would come out finite
     unsigned long long mx = 0ull;
-    const double* p = z + n0 * m + col;
+    const ZT* p = z + n0 * m + col;
 #pragma unroll 8
     for (int64_t r = n0; r < n1; ++r, p += m) {
-        const unsigned long long b = (unsigned long long)__double_as_longlong(fabs(*p));
+        const unsigned long long b = (unsigned long long)__double_as_longlong(fabs(z_value(*p, col, form)));
         mx = b > mx ? b : mx;
     }
     atomicMax(cmax + col, mx);
@@ -81,10 +91,10 @@ __global__ void tc_exponent_kernel(const unsigned long long* __restrict__ cmax, 
 
 // ------------------------------------------------------------------ fp64 -> s int8 digit planes, transposed
 // Tile: 128 rows (n) x 32 columns (m).  planes[k][col][row], row contiguous (K-major), row stride n_pad.
-template <int S, int BITS>
+template <int S, int BITS, typename ZT>
 __global__ void __launch_bounds__(256)
-tc_slice_kernel(const double* __restrict__ z, int64_t n, int64_t m, int64_t n_pad,
-                const double* __restrict__ colscale, int8_t* __restrict__ planes) {
+tc_slice_kernel(const ZT* __restrict__ z, int64_t n, int64_t m, int64_t n_pad,
+                const double* __restrict__ colscale, int8_t* __restrict__ planes, ZForm form) {
     constexpr int LD = 132;   // bytes per (plane, col) row in smem: 33 words -> conflict-free transposed byte stores
     __shared__ __align__(16) int8_t dig[S][32][LD];
     const int64_t m0 = (int64_t)blockIdx.x * 32, n0 = (int64_t)blockIdx.y * 128;
@@ -98,7 +108,7 @@ tc_slice_kernel(const double* __restrict__ z, int64_t n, int64_t m, int64_t n_pa
         const int row = r * 8 + wrp;
         const int64_t gr = n0 + row;
         double v = 0.0;
-        if (gr < n && col < m) v = z[gr * m + col];
+        if (gr < n && col < m) v = z_value(z[gr * m + col], col, form);
         long long X = __double2ll_rn(v * mul);
 #pragma unroll
         for (int k = S - 1; k >= 1; --k) {
@@ -805,17 +815,18 @@ int64_t atb_tc_workspace_bytes(int64_t n, int64_t r, int64_t m, int num_slices) 
     return tc_operand_bytes(n, r, num_slices) + tc_operand_bytes(n, m, num_slices);
 }
 
-template <int S>
-static void launch_slice(const double* z, int64_t n, int64_t m, int64_t n_pad, const double* cs, int8_t* planes,
-                         int digit_bits, cudaStream_t st) {
+template <int S, typename ZT>
+static void launch_slice(const ZT* z, int64_t n, int64_t m, int64_t n_pad, const double* cs, int8_t* planes,
+                         int digit_bits, ZForm form, cudaStream_t st) {
     dim3 grid((unsigned)((m + 31) / 32), (unsigned)(n_pad / 128));
-    if (digit_bits == 8) tc_slice_kernel<S, 8><<<grid, 256, 0, st>>>(z, n, m, n_pad, cs, planes);
-    else                 tc_slice_kernel<S, 7><<<grid, 256, 0, st>>>(z, n, m, n_pad, cs, planes);
+    if (digit_bits == 8) tc_slice_kernel<S, 8, ZT><<<grid, 256, 0, st>>>(z, n, m, n_pad, cs, planes, form);
+    else                 tc_slice_kernel<S, 7, ZT><<<grid, 256, 0, st>>>(z, n, m, n_pad, cs, planes, form);
 }
 
 // column exponents + digit planes + tensor map of one fp64 operand chunk z (rows, m); 3 launches
-static int tc_prepare_operand(TcOperand& op, uint8_t* ws, const double* z, int64_t rows, int64_t m, int num_slices,
-                              int digit_bits, int sms, cudaStream_t st) {
+template <typename ZT>
+static int tc_prepare_operand(TcOperand& op, uint8_t* ws, const ZT* z, int64_t rows, int64_t m, int num_slices,
+                              int digit_bits, int sms, cudaStream_t st, ZForm form = ZForm{0.0, 0}) {
     const int64_t n_pad = round_up(rows, TC_BK);
     op.cmax = (unsigned long long*)ws;
     op.colscale = (double*)(ws + round_up(m * 8, 1024));
@@ -826,15 +837,15 @@ static int tc_prepare_operand(TcOperand& op, uint8_t* ws, const double* z, int64
     int64_t rows_per = (rows + splits - 1) / splits;
     if (rows_per < 16) rows_per = 16;
     splits = (rows + rows_per - 1) / rows_per;
-    tc_colmax_kernel<<<dim3((unsigned)colblocks, (unsigned)splits), 256, 0, st>>>(z, rows, m, op.cmax, rows_per);
+    tc_colmax_kernel<ZT><<<dim3((unsigned)colblocks, (unsigned)splits), 256, 0, st>>>(z, rows, m, op.cmax, rows_per, form);
     tc_exponent_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(op.cmax, m, op.colscale, digit_bits);
     switch (num_slices) {
-        case 2: launch_slice<2>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, st); break;
-        case 3: launch_slice<3>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, st); break;
-        case 4: launch_slice<4>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, st); break;
-        case 5: launch_slice<5>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, st); break;
-        case 6: launch_slice<6>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, st); break;
-        default: launch_slice<7>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, st); break;
+        case 2: launch_slice<2, ZT>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, form, st); break;
+        case 3: launch_slice<3, ZT>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, form, st); break;
+        case 4: launch_slice<4, ZT>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, form, st); break;
+        case 5: launch_slice<5, ZT>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, form, st); break;
+        case 6: launch_slice<6, ZT>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, form, st); break;
+        default: launch_slice<7, ZT>(z, rows, m, n_pad, op.colscale, op.planes, digit_bits, form, st); break;
     }
     count_launch(3);
     EncodeTiledFn encode = encode_tiled_fn();
@@ -998,6 +1009,37 @@ int atb_accum_tc(const double* a, const double* z, int64_t n, int64_t r, int64_t
         rc = tc_prepare_operand(oa, ws_a, a + r0 * r, rows, r, num_slices, digit_bits, sms, st);
         if (rc != XGPR_B200_OK) return rc;
         rc = tc_prepare_operand(ob, ws_b, z + r0 * m, rows, m, num_slices, digit_bits, sms, st);
+        if (rc != XGPR_B200_OK) return rc;
+        rc = tc_launch_gemm(oa, ob, rows, r, m, 0, num_slices, digit_bits, acc, sms, st);
+        if (rc != XGPR_B200_OK) return rc;
+    }
+    return XGPR_B200_OK;
+}
+
+// The same sketch product with Z given as its float32 encoding c (Z = double(c) * scale; column 0 of c = 1.0f stands for the
+// intercept): the exponent and digit-plane passes read 4 bytes per feature instead of 8, the planes and the GEMM are the same.
+int atb_accum_tc_c32(const double* a, const float* c, int64_t n, int64_t r, int64_t m, double* acc, double scale,
+                     int fit_intercept, int num_slices, int digit_bits, void* workspace, int64_t workspace_bytes,
+                     cudaStream_t st) {
+    XB_REQUIRE(digit_bits == 7 || digit_bits == 8, "digit_bits must be 7 or 8");
+    XB_REQUIRE(n > 0 && m > 0 && r > 0, "no datapoints");
+    XB_REQUIRE(a && c && acc && workspace, "null pointer");
+    XB_REQUIRE(scale > 0.0, "scale must be positive");
+    XB_REQUIRE(num_slices >= 2 && num_slices <= 7, "num_slices must be in [2, 7]");
+    XB_REQUIRE(workspace_bytes >= atb_tc_workspace_bytes(n, r, m, num_slices), "workspace too small");
+    XB_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+    int sms, rc = tc_setup(sms);
+    if (rc != XGPR_B200_OK) return rc;
+    uint8_t* ws_a = (uint8_t*)workspace;
+    uint8_t* ws_b = ws_a + tc_operand_bytes(n, r, num_slices);
+    const int64_t max_rows = tc_max_rows(digit_bits);
+    const ZForm form{scale, fit_intercept};
+    for (int64_t r0 = 0; r0 < n; r0 += max_rows) {
+        const int64_t rows = (n - r0 < max_rows) ? (n - r0) : max_rows;
+        TcOperand oa, ob;
+        rc = tc_prepare_operand(oa, ws_a, a + r0 * r, rows, r, num_slices, digit_bits, sms, st);
+        if (rc != XGPR_B200_OK) return rc;
+        rc = tc_prepare_operand(ob, ws_b, c + r0 * m, rows, m, num_slices, digit_bits, sms, st, form);
         if (rc != XGPR_B200_OK) return rc;
         rc = tc_launch_gemm(oa, ob, rows, r, m, 0, num_slices, digit_bits, acc, sms, st);
         if (rc != XGPR_B200_OK) return rc;

@@ -474,6 +474,46 @@ def cg_matvec_accum(z, v, w, scratch=None):
                                             w.data_ptr(), scratch.data_ptr(), _stream()))
 
 
+def zty_accum_c32(c, y, zty, scale, fit_intercept):
+    """zty (m) += Z^T y with Z given as its float32 encoding c (Z = double(c) * scale; column 0 of c = 1.0f with an intercept)."""
+    c = _dev(c, "c", (torch.float32,), 2)
+    y = _dev(y, "y", (torch.float64,), 1)
+    zty = _dev(zty, "zty", (torch.float64,), 1)
+    if y.shape[0] != c.shape[0] or zty.shape[0] != c.shape[1]:
+        raise RuntimeError("wrong array sizes")
+    check(lib.xgpr_b200_zty_accum_c32(c.data_ptr(), c.shape[0], c.shape[1], y.data_ptr(), zty.data_ptr(), float(scale),
+                                      int(bool(fit_intercept)), _stream()))
+
+
+def srht_sample_c32(c, radem, cols, out, scale, fit_intercept):
+    """srht_sample on Z = double(c) * scale given as the float32 encoding c; out (n, rank) float64."""
+    c = _dev(c, "c", (torch.float32,), 2)
+    r = _dev(radem, "radem", (torch.int8,), 1)
+    k = _dev(cols, "cols", (torch.int32,), 1)
+    o = _dev(out, "out", (torch.float64,), 2)
+    if o.shape[0] != c.shape[0] or o.shape[1] != k.shape[0] or c.shape[1] > r.shape[0]:
+        raise RuntimeError("wrong array sizes")
+    check(lib.xgpr_b200_srht_sample_c32(c.data_ptr(), c.shape[0], c.shape[1], r.data_ptr(), r.shape[0], k.data_ptr(),
+                                        k.shape[0], o.data_ptr(), float(scale), int(bool(fit_intercept)), _stream()))
+    return out
+
+
+def atb_accum_tc_c32(a, c, acc, scale, fit_intercept, num_slices=5, digit_bits=8):
+    """acc (r, m) += a^T Z on the tensor cores with Z given as its float32 encoding c."""
+    a = _dev(a.contiguous(), "a", (torch.float64,), 2)
+    c = _dev(c, "c", (torch.float32,), 2)
+    acc = _dev(acc, "acc", (torch.float64,), 2)
+    if a.shape[0] != c.shape[0] or acc.shape[0] != a.shape[1] or acc.shape[1] != c.shape[1]:
+        raise RuntimeError("wrong array sizes")
+    need = lib.xgpr_b200_atb_tc_workspace_bytes(c.shape[0], a.shape[1], c.shape[1], int(num_slices))
+    if need < 0:
+        raise RuntimeError("num_slices must be in [2, 7]")
+    ws = _tc_workspace(c.device, need)
+    check(lib.xgpr_b200_atb_accum_tc_c32(a.data_ptr(), c.data_ptr(), c.shape[0], a.shape[1], c.shape[1], acc.data_ptr(),
+                                         float(scale), int(bool(fit_intercept)), int(num_slices), int(digit_bits),
+                                         ws.data_ptr(), ws.numel(), _stream()))
+
+
 def cg_matvec_accum_c32(c, vs, w, scale, fit_intercept, scratch=None):
     """w (m, r) += Z^T (Z v) from the float32 encoding c of Z (Z = double(c) * scale; column 0 of c holds 1.0f with an
     intercept); vs = v with rows scaled like Z's columns.  See include/xgpr_b200.h."""

@@ -459,6 +459,10 @@ class ConjugateGrad:
                 kernel.resident_encode(z, c[lo:lo + z.shape[0]])
                 lo += z.shape[0]
                 del z
+        if kernel.fit_intercept:
+            # column 0 stands for the intercept: the one-pass matvec substitutes 1 for it on the fly, the other readers of
+            # the encoding (the preconditioner's accumulation pass) expect the stored value to be 1.0f
+            c[:, 0] = 1.0
         self._resident_c = (key, c)
         return c
 
@@ -523,6 +527,17 @@ class ConjugateGrad:
             if kernel.fit_intercept:
                 out[:, 0] = 1.0
             yield out
+
+    def resident_for_preconditioner(self, dataset, kernel):
+        """The shard's resident float32 encoding, built NOW on the current stream, when the solve that follows will use it
+        (same conditions as prepare_async) -- so that the preconditioner's accumulation pass can read it instead of
+        generating fp64 features a second time; None otherwise.  XGPR_B200_PRECOND_F64=1 keeps the fp64 pass."""
+        if os.environ.get("XGPR_B200_PRECOND_F64", "0") != "0":
+            return None
+        if not (self.device_cg and self.ops is _cuda_ops and kernel.device == "cuda" and _fused_ok(kernel, self.ops)
+                and self.keep_resident and getattr(kernel, "resident_ok", lambda: False)()):
+            return None
+        return self._resident_encoding(dataset, kernel)
 
     def prepare_async(self, dataset, kernel):
         """Start building the resident float32 encoding of the shard's features on a SIDE stream and return at once.
@@ -765,7 +780,8 @@ def fit_cg(kernel, dataset, max_rank=512, method="srht", cg_tol=1e-6, max_iter=5
     comm = comm or RowShardComm()
     op = ConjugateGrad(comm, ops)
     pre = RandNysPreconditioner(kernel, dataset, max_rank, verbose, random_state, method, comm, ops,
-                                overlap_hook=lambda: op.prepare_async(dataset, kernel))
+                                overlap_hook=lambda: op.prepare_async(dataset, kernel),
+                                encoded_source=lambda: op.resident_for_preconditioner(dataset, kernel))
     weights, n_iter, losses = cg_fit_lib_internal(kernel, dataset, cg_tol, max_iter, pre, verbose, comm, ops, op)
     return weights, n_iter, losses, pre
 
@@ -780,6 +796,28 @@ def _single_pass_srht_zty(dataset, kernel, compressor, acc_results, z_trans_y, o
         ops.zty_accum(z, y, z_trans_y)
         y_trans_y += y @ y
         atb(compressor.transform_x(z), z, acc_results)
+    return y_trans_y
+
+
+def _single_pass_srht_zty_encoded(dataset, kernel, compressor, acc_results, z_trans_y, ops, c_mat):
+    """_single_pass_srht_zty fed from the shard's resident float32 encoding C (rows in dataset order; Z = double(C) * scale
+    exactly): no second featurise, and Z^T y, the SRHT sample and the digit-plane passes of the tensor-core sketch read 4
+    bytes per feature.  Returns None when a step is not available for this shape (the caller falls back to fp64 Z)."""
+    scale, icpt = kernel.feature_scale(), bool(kernel.fit_intercept)
+    if not hasattr(compressor, "transform_encoded") or not hasattr(ops, "atb_accum_tc_c32") or c_mat.shape[1] % 4:
+        return None
+    if compressor.transform_encoded(c_mat[:1], scale, icpt) is None:
+        return None
+    y_trans_y = _new((1,), acc_results.device)
+    lo = 0
+    for _, yin, _ in _xy_chunks(dataset, kernel):
+        from .kernels.base import to_device
+        y = to_device(_as_f64(yin), torch.float64)
+        c = c_mat[lo:lo + y.shape[0]]
+        lo += y.shape[0]
+        ops.zty_accum_c32(c, y, z_trans_y, scale, icpt)
+        y_trans_y += y @ y
+        ops.atb_accum_tc_c32(compressor.transform_encoded(c, scale, icpt), c, acc_results, scale, icpt)
     return y_trans_y
 
 
@@ -828,14 +866,24 @@ def _tall_svd(mat):
     return u, s
 
 
-def initialize_srht(dataset, rank, kernel, random_state, comm, ops, compressor_cls, overlap_hook=None):
+def initialize_srht(dataset, rank, kernel, random_state, comm, ops, compressor_cls, overlap_hook=None,
+                    encoded_source=None):
     """rand_nys_constructors.py:221-296 (single pass).  `overlap_hook` is called once, after the accumulation pass and its
-    all-reduces have been issued and before the serial factorisation (see ConjugateGrad.prepare_async)."""
+    all-reduces have been issued and before the serial factorisation (see ConjugateGrad.prepare_async).
+    `encoded_source()` -> the shard's resident float32 encoding of Z or None (ConjugateGrad.resident_for_preconditioner): when
+    the solve that follows keeps it anyway, the accumulation pass reads it instead of generating fp64 features again."""
     dev = _device_of(kernel)
     m = kernel.get_num_rffs()
     acc_results, z_trans_y = _new((rank, m), dev), _new((m,), dev)
     compressor = compressor_cls(rank, m, random_seed=random_state, device=kernel.device)
-    y_trans_y = _single_pass_srht_zty(dataset, kernel, compressor, acc_results, z_trans_y, ops)
+    y_trans_y = None
+    c_mat = encoded_source() if encoded_source is not None else None
+    if c_mat is not None:
+        y_trans_y = _single_pass_srht_zty_encoded(dataset, kernel, compressor, acc_results, z_trans_y, ops, c_mat)
+    if y_trans_y is None:
+        acc_results.zero_()
+        z_trans_y.zero_()
+        y_trans_y = _single_pass_srht_zty(dataset, kernel, compressor, acc_results, z_trans_y, ops)
     comm.all_reduce_(acc_results)
     comm.all_reduce_(z_trans_y, y_trans_y)
     if overlap_hook is not None:
@@ -895,7 +943,7 @@ class RandNysPreconditioner:
     """rand_nys_preconditioners.py:14-72."""
 
     def __init__(self, kernel, dataset, max_rank, verbose=False, random_state=123, method="srht", comm=None,
-                 ops=_cuda_ops, compressor_cls=None, overlap_hook=None):
+                 ops=_cuda_ops, compressor_cls=None, overlap_hook=None, encoded_source=None):
         if method not in ["srht_2", "srht_3", "srht"]:
             raise RuntimeError("Unknown method supplied for tuning preconditioner construction.")
         comm = comm or RowShardComm()
@@ -907,7 +955,7 @@ class RandNysPreconditioner:
                 overlap_hook)
         else:
             self.u_mat, self.eig, self.z_trans_y, self.y_trans_y = initialize_srht(
-                dataset, max_rank, kernel, random_state, comm, ops, compressor_cls, overlap_hook)
+                dataset, max_rank, kernel, random_state, comm, ops, compressor_cls, overlap_hook, encoded_source)
         lambda_ = kernel.get_lambda()
         min_eig = float(self.eig.min())
         self.eig = self.eig + lambda_ ** 2

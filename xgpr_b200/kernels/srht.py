@@ -56,6 +56,19 @@ class SRHTCompressor:
             return xfeatures[:, self.col_sampler]
         return xfeatures[:, self.truncated_sampler]
 
+    def transform_encoded(self, c, scale, fit_intercept):
+        """transform_x(Z) for Z given as its float32 encoding c (Z = double(c) * scale, column 0 = 1 with an intercept):
+        the same fp64 butterflies on the same values, read at 4 bytes per feature.  None when the fused kernel does not
+        cover this width (the caller then materialises Z)."""
+        if self.device != "cuda" or not self.double_precision or c.shape[1] != self.input_size \
+                or not ext.srht_sample_supported(self.padded_dims, torch.float64):
+            return None
+        cols = getattr(self, "_cols_i32", None)
+        if cols is None or cols.device != c.device:
+            cols = self._cols_i32 = self.truncated_sampler.to(device=c.device, dtype=torch.int32).contiguous()
+        out = torch.empty((c.shape[0], self.compression_size), dtype=torch.float64, device=c.device)
+        return ext.srht_sample_c32(c, self.radem, cols, out, scale, fit_intercept)
+
     @property
     def device(self):
         return self.device_
