@@ -349,7 +349,7 @@ class ConjugateGrad:
         self.keep_resident = True
         # several right-hand sides: stream the float32 encoding of Z (4 bytes per feature) instead of fp64 Z
         self.encoded_multi_rhs = os.environ.get("XGPR_B200_MULTIRHS_F64", "0") == "0"
-        self.encoded_fraction = 0.75             # share of the free HBM the kept chunks of the encoding may take
+        self.encoded_fraction = float(os.environ.get("XGPR_B200_ENCODED_FRACTION", "0.85"))   # share of the free HBM the kept chunks of the encoding may take
         self.one_pass = True
         # one right-hand side on the GPU: scalar recurrences on the device, no per-iteration host sync (_fit_device)
         self.device_cg = os.environ.get("XGPR_B200_DEVICE_CG", "1") != "0"
