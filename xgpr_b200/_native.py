@@ -7,7 +7,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libxgpr_b200.so")
+LIB_PATH = os.environ.get("XGPR_B200_LIB") or os.path.join(_HERE, "lib", "libxgpr_b200.so")   # override: A/B of two builds
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(
