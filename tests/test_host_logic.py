@@ -73,3 +73,23 @@ def test_row_shard_comm_single_and_counters():
     t = torch.ones(3, dtype=torch.float64)
     c.all_reduce_(t)
     assert c.world == 1 and c.n_allreduce == 0 and c.bytes_allreduce == 0 and float(t.sum()) == 3.0
+
+
+def test_bench_nmll_dataset_is_the_same_at_every_world_size():
+    """bench.py's cfg5 dataset is defined in 62,500-row blocks drawn from per-block seeds, so the rows a rank holds do not
+    depend on how many ranks there are: the rank slices for N = 2 / 3 / 8 concatenate to the N = 1 dataset (CPU generator
+    here; the bench uses the device generator with the same construction)."""
+    import importlib.util
+    import os
+    import torch
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(root, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    n = 3 * bench.NMLL_BLOCK + 1234
+    dev = torch.device("cpu")
+    x1, y1 = bench.nmll_dataset(n, 0, 1, dev)
+    assert x1.shape == (n, bench.NMLL_DIM) and y1.shape == (n,)
+    for world in (2, 3, 8):
+        xs, ys = zip(*(bench.nmll_dataset(n, r, world, dev) for r in range(world)))
+        assert torch.equal(torch.cat(xs), x1) and torch.equal(torch.cat(ys), y1)
